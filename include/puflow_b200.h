@@ -1,0 +1,141 @@
+/*
+ * puflow_b200 -- C-ABI of the B200-native kernels for PU-Flow's discrete x4 upsampling hot path.
+ *
+ * Drop-in boundary.  The reference has exactly one in-tree native FFI, the
+ * pybind11 module `chamfer_3D` (forward(xyz1, xyz2, dist1, dist2, idx1, idx2) -> int,
+ * /root/reference/metric/PyTorchCD/chamfer3D/chamfer_cuda.cpp:17-33); everything else on the path is
+ * reached through third-party Python packages (pytorch3d.ops.knn_points / knn_gather, knn_cuda.KNN,
+ * pointnet2_ops furthest_point_sample / gather_operation) and ATen.  The functions below are what a
+ * binding for this path calls instead.  Conventions, all functions:
+ *
+ *   - plain C: raw DEVICE pointers + explicit sizes, no torch types; the caller owns every buffer
+ *     (outputs and workspaces are pre-allocated by the caller, like chamfer_3D.forward's out-params,
+ *     /root/reference/metric/PyTorchCD/chamfer3D/dist_chamfer_3D.py:40-52); nothing is allocated,
+ *     freed or synchronised inside;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream, which is what the
+ *     reference launches on, chamfer3D.cu:142-143);
+ *   - return value 0 = success; otherwise a cudaError_t value or PF_EINVAL / PF_ENOMEM, with a
+ *     message available from pf_last_error() (the reference returns 1/0 and printf()s,
+ *     chamfer3D.cu:145-151 -- the Python binding raises instead);
+ *   - tensors are dense row-major fp32 unless noted; indices are int32 (the Python wrappers widen to
+ *     int64 where the replaced API returns int64);
+ *   - "k-major" weights: W[k][o] = the layer's weight for input channel k and output channel o
+ *     (the transpose of torch's (out, in) layout), produced by puflow_b200/packing.py.
+ */
+#ifndef PUFLOW_B200_H
+#define PUFLOW_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PF_API __attribute__((visibility("default")))
+#else
+#define PF_API
+#endif
+
+#define PF_ABI_VERSION 1
+#define PF_EINVAL 10001
+#define PF_ENOMEM 10002
+
+/* activation codes of pf_linear */
+#define PF_ACT_NONE 0
+#define PF_ACT_RELU 1
+#define PF_ACT_LRELU 2
+
+PF_API int pf_abi_version(void);
+/* message of the last failing call on this host thread ("" if none) */
+PF_API const char* pf_last_error(void);
+
+/* ---- (1) kNN top-k ---------------------------------------------------------------------------
+ * Replaces pytorch3d.ops.knn_points(p1, p2, K) at
+ * /root/reference/modules/discrete/interpflow.py:104 (K=8), :228, :328 (K=16).
+ * q[B][nq][3], p[B][np][3] -> idx[B][nq][K] int32 (and dist[B][nq][K] squared L2 if dist != NULL),
+ * sorted ascending by (distance, index).  1 <= K <= 32, K <= np. */
+PF_API int pf_knn_topk(const float* q, const float* p, int B, int nq, int np, int K, int32_t* idx, float* dist,
+                void* stream);
+
+/* ---- (5) Chamfer nearest-neighbour distance ----------------------------------------------------
+ * Replaces chamfer_3D.forward / NmDistanceKernel,
+ * /root/reference/metric/PyTorchCD/chamfer3D/chamfer3D.cu:12-154 (both directions, one call).
+ * a[B][n][3], b[B][m][3] -> dist1[B][n], idx1[B][n] (nearest in b), dist2[B][m], idx2[B][m]
+ * (nearest in a); squared distances; the lowest index wins ties (strict <, chamfer3D.cu:36-69,126). */
+PF_API int pf_chamfer_nn(const float* a, int n, const float* b, int m, int B, float* dist1, int32_t* idx1, float* dist2,
+                  int32_t* idx2, void* stream);
+
+/* ---- per-point linear layer ----------------------------------------------------------------------
+ * out[m][0:N] = act(A[m][0:K] . W[K][N] + bias[N]); row strides lda / ldo in floats.  Replaces the
+ * ATen Linear / 1x1 Conv2d calls that act on per-POINT tensors: FeatMergeUnit
+ * (/root/reference/modules/discrete/interpflow.py:251-258), the first layers of LinearA1D
+ * (:22-43), and the per-point projections the fused EdgeConv kernels gather from.
+ * N % 4 == 0, lda % 4 == 0 unless K < 4, ldo % 4 == 0, 16-byte aligned pointers. */
+PF_API int pf_linear(const float* A, int64_t lda, const float* W, const float* bias, float* out, int64_t ldo, int64_t M,
+              int K, int N, int act, float slope, void* stream);
+
+/* ---- (2) fused EdgeConv block -----------------------------------------------------------------
+ * Replaces FeatureExtractUnit.forward (/root/reference/modules/discrete/interpflow.py:223-248):
+ * neighbour gather + 4-layer dense block (1x1 conv + eval-BN + LeakyReLU + concat) + conv_out + max
+ * over the K neighbours, for one block.  The 3C-wide edge-feature part of every conv is linear in
+ * (x_i, x_j) and arrives pre-projected per point:
+ *   pq[Bp*N][2R], R = 4G + C_out: columns [0,R) = P (own-point term incl. all biases),
+ *   [R,2R) = Q (neighbour term); column order inside R: layer0 | layer1 | layer2 | layer3 | conv_out.
+ *   idx[Bp*N][K] int32 neighbour index inside the patch;  wd: hidden-to-hidden weights of layers
+ *   1..3, k-major [l*G][G] concatenated;  wo: [4G][C_out] k-major;  out[Bp*N][C_out].
+ * (G, C_out) in {(8,32), (16,64), (32,128)}; K in {8,16,32}; slope = LeakyReLU slope (0.05). */
+PF_API int pf_edgeconv(const float* pq, const int32_t* idx, const float* wd, const float* wo, float* out, int Bp, int N,
+                int K, int G, int C_out, float slope, void* stream);
+
+/* ---- (3) flow stack ---------------------------------------------------------------------------------
+ * FlowBlock.forward / inverse x6 (/root/reference/modules/discrete/interpflow.py:66-82,302-321):
+ * ActNorm (modules/flows/normalize.py:30-43), InvertibleConv1x1_1D (permutate.py:117-126), additive
+ * spatial coupling (coupling.py:55-58,82-85,108-118), channel reverse (permutate.py:75-80), affine
+ * injector (coupling.py:127-151).
+ *
+ * Conditioning is per INPUT point and shared by the forward pass and all R inverse copies:
+ *   raw[nblocks][M][192] = cs_i . [W1c | Ws0 | Wb0]  (from pf_linear; no activation):
+ *        [0,64) first-layer term of coupling1.bias_net, [64,128) / [128,192) first layers of
+ *        coupling2.scale_net / bias_net;
+ *   pf_flow_cond finishes the two coupling2 nets: sb[nblocks][M][8] = (s0,s1,s2,b0,b1,b2,0,0);
+ *   cond_w[nblocks][PF_COND_BLOB] and flow_w[nblocks][PF_FLOW_BLOB]: packed small weights
+ *   (layouts in puflow_b200/packing.py).
+ * pf_flow_fwd: x[M][3] -> z[M][3]; ssum[M] = sum over blocks and channels of s (for the log-det).
+ * pf_flow_inv: zin[M*R][3] (row n*R + r belongs to input point n) -> x[M*R][3]. */
+#define PF_COND_BLOB 8840
+#define PF_FLOW_BLOB 4480
+PF_API int pf_flow_cond(const float* raw, const float* cond_w, float* sb, int64_t M, int nblocks, void* stream);
+PF_API int pf_flow_fwd(const float* x, const float* raw, const float* sb, const float* flow_w, float* z, float* ssum,
+                int64_t M, int nblocks, void* stream);
+PF_API int pf_flow_inv(const float* zin, const float* raw, const float* sb, const float* flow_w, float* x, int64_t M,
+                int R, int nblocks, void* stream);
+
+/* ---- (4) latent interpolation -------------------------------------------------------------------------
+ * Replaces InterpolationModule.forward (/root/reference/modules/discrete/interpflow.py:162-186) with
+ * KnnContextEncoder (:123-134), DistanceEncoder (:85-120) and WeightEstimationUnit (:137-159) fused:
+ * per edge (k = 8 neighbours) context MLPs -> R logits -> softmax over the 8 neighbours -> weighted
+ * sum of the neighbours' latents.
+ *   xyz[Bp*N][3], z[Bp*N][3]; idx: int32, row stride ldidx (first 8 entries of each row are used);
+ *   pq[Bp*N][640] per-point projections (P | Q, 320 each: dist-enc layer 0 (64) | dense layers (128) |
+ *   composed context term (128)); w: packed weights, PF_INTERP_BLOB floats (puflow_b200/packing.py);
+ *   out[Bp][N*R][3], row n*R + r (the order PointInterpFlow.g expects, interpflow.py:316).
+ * 1 <= R <= 32. */
+#define PF_INTERP_BLOB 46304
+PF_API int pf_interp(const float* xyz, const float* z, const int32_t* idx, int ldidx, const float* pq, const float* w,
+              float* out, int Bp, int N, int R, void* stream);
+
+/* ---- caller side ("next" rows of SURVEY.md section 8f) ---------------------------------------------------
+ * pf_fps replaces pointnet2_ops.furthest_point_sample (/root/reference/modules/utils/patch.py:102,156)
+ * with the semantics of the reference's own modules/utils/fps.py:40-73: start at index 0, running
+ * min squared distance initialised to 1e10, arg-max with the first index winning ties.
+ *   xyz[B][n][3] -> idx[B][npoint] int32;  work: >= B*n floats of scratch.
+ * pf_knn_patch replaces knn_cuda.KNN(k)(ref, query) (patch.py:33,107): for each of the nq queries the
+ * k nearest of the np points, ascending by (distance, index); idx[B][nq][k] int32.  k <= 1024. */
+PF_API int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
+PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PUFLOW_B200_H */

@@ -1,0 +1,60 @@
+"""ctypes binding of the C-ABI in include/puflow_b200.h.
+
+The shared library is built in-tree (puflow_b200/_lib/libpuflow_b200.so) by
+`make -C puflow_b200/csrc` / `__graft_entry__.build()`.  Importing this module without the library
+raises ImportError -- there is deliberately no fallback implementation.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "libpuflow_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()' "
+        f"or make -C {os.path.join(_HERE, 'csrc')}). puflow_b200 has no CPU / PyTorch fallback."
+    )
+
+lib = ctypes.CDLL(LIB_PATH)
+
+_vp, _i, _i64, _f = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float
+
+# name -> argtypes; every function returns int status except pf_last_error
+SIGNATURES = {
+    "pf_abi_version": [],
+    "pf_knn_topk": [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
+    "pf_chamfer_nn": [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "pf_linear": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
+    "pf_edgeconv": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
+    "pf_flow_cond": [_vp, _vp, _vp, _i64, _i, _vp],
+    "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
+    "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
+    "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
+    "pf_knn_patch": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+}
+for _name, _args in SIGNATURES.items():
+    _fn = getattr(lib, _name)
+    _fn.argtypes = _args
+    _fn.restype = ctypes.c_int
+lib.pf_last_error.argtypes = []
+lib.pf_last_error.restype = ctypes.c_char_p
+
+PF_ABI_VERSION = 1
+PF_COND_BLOB = 8840
+PF_FLOW_BLOB = 4480
+PF_INTERP_BLOB = 46304
+ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
+
+if lib.pf_abi_version() != PF_ABI_VERSION:
+    raise ImportError(f"{LIB_PATH}: ABI version {lib.pf_abi_version()} != {PF_ABI_VERSION}; rebuild")
+
+
+class PuflowError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        raise PuflowError(f"{what} failed (status {rc}): {lib.pf_last_error().decode(errors='replace')}")

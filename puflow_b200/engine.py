@@ -1,0 +1,121 @@
+"""The hot path -- PointInterpFlow.forward (/root/reference/modules/discrete/interpflow.py:327-337) -- as a
+fixed sequence of puflow_b200 kernel launches on the current CUDA stream.
+
+    (1) knn_topk K=16                                     interpflow.py:328
+    (2) 6 x [pf_linear (P|Q projection) -> pf_edgeconv -> pf_linear x2 (FeatMergeUnit)
+             -> pf_linear (conditioning first layers)]    interpflow.py:292-300, 22-43
+        pf_flow_cond                                       coupling2 nets, once per input point
+    (3) pf_flow_fwd                                        interpflow.py:302-313, 339-345
+    (4) pf_linear (K=3) -> pf_interp                       interpflow.py:173-186
+    (5) pf_flow_inv on R x N points                        interpflow.py:315-321
+
+`PUFlowEngine` owns the packed weights of one checkpoint on one device.  modules/discrete/interpflow.py
+(the drop-in PointInterpFlow) delegates to it.
+"""
+import math
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+from ._native import ACT_NONE, ACT_RELU
+from .packing import FEAT_CFG, NUM_BLOCKS, pack_state_dict
+
+K_MAIN, K_INTERP = 16, 8          # interpflow.py:270 (num_neighbors), :167 (hard-coded k = 8)
+LOG_2PI = math.log(2.0 * math.pi)
+
+
+class PUFlowEngine:
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError(f"PUFlowEngine needs a CUDA device, got {self.device} (no CPU fallback)")
+        self.w = pack_state_dict(state_dict, self.device)
+
+    # ---- stages (each usable on its own; the drop-in module methods call these) -------------------
+    def knn(self, xyz: torch.Tensor, K: int = K_MAIN):
+        return ops.knn_topk(xyz, xyz, K, return_dist=False)[1]
+
+    def edgeconv_block(self, i: int, c: torch.Tensor, idx: torch.Tensor, Bp: int, N: int):
+        """FeatureExtractUnit i on c[Bp*N, C_in] -> [Bp*N, C_out]."""
+        f = self.w["feat"][i]
+        _, g, Co = FEAT_CFG[i]
+        pq = ops.linear(c, f["wpq"], f["bpq"])
+        return ops.edgeconv(pq, idx, f["wd"], f["wo"], Bp, N, g, Co, 0.05)
+
+    def merge(self, i: int, c: torch.Tensor):
+        """FeatMergeUnit i (interpflow.py:251-258)."""
+        m = self.w["merge"][i]
+        h = ops.linear(c, m["w1"], m["b1"], ACT_RELU)
+        return ops.linear(h, m["w2"])
+
+    def feat_extract(self, xyz: torch.Tensor, idx: torch.Tensor, return_feats: bool = False):
+        """PointInterpFlow.feat_extract (interpflow.py:292-300) -> list of cs[i] [Bp, N, cond_i]."""
+        Bp, N, _ = xyz.shape
+        c = xyz.reshape(Bp * N, 3)
+        cs, feats = [], []
+        for i in range(NUM_BLOCKS):
+            c = self.edgeconv_block(i, c, idx, Bp, N)
+            feats.append(c.view(Bp, N, -1))
+            cs.append(self.merge(i, c).view(Bp, N, -1))
+        return (cs, feats) if return_feats else cs
+
+    def conditioning(self, cs: List[torch.Tensor]):
+        """Everything the flow needs from cs, per INPUT point: raw[6, M, 192], sb[6, M, 8]."""
+        M = cs[0].shape[0] * cs[0].shape[1]
+        raw = torch.empty((NUM_BLOCKS, M, 192), dtype=torch.float32, device=self.device)
+        for i in range(NUM_BLOCKS):
+            ops.linear(cs[i].reshape(M, -1), self.w["wc"][i], None, ACT_NONE, out=raw[i])
+        sb = ops.flow_cond(raw, self.w["cond"])
+        return raw, sb
+
+    def f(self, xyz: torch.Tensor, cond):
+        """PointInterpFlow.f (interpflow.py:302-313) -> (z[Bp,N,3], log_det_J[Bp])."""
+        Bp, N, _ = xyz.shape
+        raw, sb = cond
+        z, ssum = ops.flow_fwd(xyz.reshape(Bp * N, 3), raw, sb, self.w["flow"])
+        logdet = self.w["logdet_const"] * N - ssum.view(Bp, N).sum(1)
+        return z.view(Bp, N, 3), logdet
+
+    def log_prob(self, xyz: torch.Tensor, cond):
+        """PointInterpFlow.log_prob (interpflow.py:339-345; standard_logp, modules/utils/probs.py:87-93)."""
+        z, logdet = self.f(xyz, cond)
+        logp = (-0.5 * (z * z + LOG_2PI)).flatten(1).sum(1)
+        return z, -torch.mean(logp + logdet)
+
+    def interp(self, z: torch.Tensor, xyz: torch.Tensor, upratio: int, idx: Optional[torch.Tensor] = None):
+        """InterpolationModule.forward (interpflow.py:173-186) -> [Bp, N*R, 3], row n*R + r.
+        `idx`: any [Bp,N,>=8] sorted kNN list over xyz (the K=16 list is re-used: same metric)."""
+        Bp, N, _ = xyz.shape
+        if idx is None:
+            idx = self.knn(xyz, K_INTERP)
+        wi = self.w["interp"]
+        pq = ops.linear(xyz.reshape(Bp * N, 3), wi["wpq"], wi["bpq"])
+        return ops.interp(xyz, z, idx, pq, wi["blob"], upratio)
+
+    def g(self, zup: torch.Tensor, cond, upratio: int):
+        """PointInterpFlow.g (interpflow.py:315-321) on zup[Bp, N*R, 3] (row n*R + r)."""
+        raw, sb = cond
+        Bp = zup.shape[0]
+        x = ops.flow_inv(zup.reshape(-1, 3), raw, sb, self.w["flow"], upratio)
+        return x.view(Bp, -1, 3)
+
+    # ---- whole path ----------------------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, xyz: torch.Tensor, upratio: int = 4, return_all: bool = False):
+        """xyz[Bp,N,3] fp32 CUDA -> (x[Bp, N*R, 3], logp_x scalar)."""
+        if xyz.dim() != 3 or xyz.shape[2] != 3:
+            raise ValueError(f"expected xyz[B,N,3], got {tuple(xyz.shape)}")
+        xyz = xyz.contiguous().float()
+        idx = self.knn(xyz, K_MAIN)
+        cs, feats = self.feat_extract(xyz, idx, return_feats=True)
+        cond = self.conditioning(cs)
+        z, logp_x = self.log_prob(xyz, cond)
+        zup = self.interp(z, xyz, upratio, idx)
+        x = self.g(zup, cond, upratio)
+        if return_all:
+            return dict(knn_idx=idx, feats=feats, cs=cs, z=z, logp_x=logp_x, zup=zup, x=x)
+        return x, logp_x
+
+    def sample(self, xyz: torch.Tensor, upratio: int = 4):
+        return self.forward(xyz, upratio)[0]

@@ -1,0 +1,188 @@
+"""torch.Tensor wrappers over the C-ABI (include/puflow_b200.h).
+
+Each wrapper checks device / dtype / contiguity, allocates the outputs with torch (the caller-owns-
+memory convention of the reference's chamfer_3D binding,
+/root/reference/metric/PyTorchCD/chamfer3D/dist_chamfer_3D.py:40-52), and launches on torch's
+current CUDA stream.  CPU tensors are rejected: there is no fallback path.
+"""
+import torch
+
+from . import _native as N
+
+lib = N.lib
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: torch.Tensor, name: str, dtype=torch.float32):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name}: expected a torch.Tensor")
+    if not t.is_cuda:
+        raise N.PuflowError(f"{name}: tensor is on {t.device}; puflow_b200 runs on CUDA only (no CPU fallback)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name}: tensor must be contiguous")
+    return t
+
+
+def _dev(t):
+    return torch.cuda.device(t.device)
+
+
+# ---- (1) kNN -------------------------------------------------------------------------------------
+def knn_topk(q: torch.Tensor, p: torch.Tensor, K: int, return_dist: bool = True):
+    """q[B,nq,3], p[B,np,3] -> (dist[B,nq,K] squared L2 or None, idx[B,nq,K] int32), sorted ascending by
+    (distance, index).  pytorch3d.ops.knn_points semantics (interpflow.py:104,228,328)."""
+    _chk(q, "q"), _chk(p, "p")
+    if q.dim() != 3 or p.dim() != 3 or q.shape[2] != 3 or p.shape[2] != 3 or q.shape[0] != p.shape[0]:
+        raise ValueError(f"knn_topk: expected q[B,nq,3], p[B,np,3]; got {tuple(q.shape)}, {tuple(p.shape)}")
+    B, nq, _ = q.shape
+    np_ = p.shape[1]
+    idx = torch.empty((B, nq, K), dtype=torch.int32, device=q.device)
+    dist = torch.empty((B, nq, K), dtype=torch.float32, device=q.device) if return_dist else None
+    with _dev(q):
+        for b0 in range(0, max(B, 1), 65535):
+            b1 = min(B, b0 + 65535)
+            N.check(lib.pf_knn_topk(q[b0:b1].data_ptr(), p[b0:b1].data_ptr(), b1 - b0, nq, np_, K,
+                                    idx[b0:b1].data_ptr(), dist[b0:b1].data_ptr() if return_dist else None,
+                                    _stream()), "pf_knn_topk")
+    return dist, idx
+
+
+# ---- (5) Chamfer ---------------------------------------------------------------------------------
+def chamfer_nn(a: torch.Tensor, b: torch.Tensor):
+    """a[B,n,3], b[B,m,3] -> (dist1[B,n], dist2[B,m], idx1 int32, idx2 int32); chamfer_3DDist forward
+    (metric/PyTorchCD/chamfer3D/dist_chamfer_3D.py:29-81)."""
+    _chk(a, "a"), _chk(b, "b")
+    if a.dim() != 3 or b.dim() != 3 or a.shape[2] != 3 or b.shape[2] != 3 or a.shape[0] != b.shape[0]:
+        raise ValueError(f"chamfer_nn: expected a[B,n,3], b[B,m,3]; got {tuple(a.shape)}, {tuple(b.shape)}")
+    B, n, _ = a.shape
+    m = b.shape[1]
+    d1 = torch.empty((B, n), dtype=torch.float32, device=a.device)
+    d2 = torch.empty((B, m), dtype=torch.float32, device=a.device)
+    i1 = torch.empty((B, n), dtype=torch.int32, device=a.device)
+    i2 = torch.empty((B, m), dtype=torch.int32, device=a.device)
+    with _dev(a):
+        N.check(lib.pf_chamfer_nn(a.data_ptr(), n, b.data_ptr(), m, B, d1.data_ptr(), i1.data_ptr(), d2.data_ptr(),
+                                  i2.data_ptr(), _stream()), "pf_chamfer_nn")
+    return d1, d2, i1, i2
+
+
+# ---- per-point linear ----------------------------------------------------------------------------
+def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = N.ACT_NONE, slope: float = 0.0, out=None):
+    """out[M,N] = act(a[M,K] @ w[K,N] + bias).  `a` may be a row-strided 2-D view (stride(1) == 1)."""
+    if a.dim() != 2 or a.stride(1) != 1 or not a.is_cuda or a.dtype != torch.float32:
+        raise ValueError("linear: a must be a 2-D fp32 CUDA tensor with unit inner stride")
+    _chk(w, "w")
+    M, K = a.shape
+    if w.shape[0] != K:
+        raise ValueError(f"linear: a is [M,{K}] but w is {tuple(w.shape)}")
+    Nn = w.shape[1]
+    if bias is not None:
+        _chk(bias, "bias")
+    if out is None:
+        out = torch.empty((M, Nn), dtype=torch.float32, device=a.device)
+    lda = a.stride(0) if M > 1 else max(K, a.stride(0))
+    with _dev(a):
+        N.check(lib.pf_linear(a.data_ptr(), lda, w.data_ptr(), bias.data_ptr() if bias is not None else None,
+                              out.data_ptr(), out.stride(0), M, K, Nn, act, float(slope), _stream()), "pf_linear")
+    return out
+
+
+# ---- (2) EdgeConv --------------------------------------------------------------------------------
+def edgeconv(pq: torch.Tensor, idx: torch.Tensor, wd: torch.Tensor, wo: torch.Tensor, Bp: int, Npts: int, G: int,
+             C_out: int, slope: float = 0.05):
+    """pq[Bp*N, 2(4G+C_out)], idx[Bp,N,K] int32 -> out[Bp*N, C_out] (FeatureExtractUnit.forward)."""
+    _chk(pq, "pq"), _chk(idx, "idx", torch.int32), _chk(wd, "wd"), _chk(wo, "wo")
+    K = idx.shape[-1]
+    R = 4 * G + C_out
+    if pq.shape != (Bp * Npts, 2 * R) or idx.numel() != Bp * Npts * K:
+        raise ValueError(f"edgeconv: pq {tuple(pq.shape)} / idx {tuple(idx.shape)} do not match Bp={Bp} N={Npts} R={R}")
+    if wd.numel() != 6 * G * G or wo.numel() != 4 * G * C_out:
+        raise ValueError("edgeconv: packed weight sizes do not match (G, C_out)")
+    out = torch.empty((Bp * Npts, C_out), dtype=torch.float32, device=pq.device)
+    with _dev(pq):
+        N.check(lib.pf_edgeconv(pq.data_ptr(), idx.data_ptr(), wd.data_ptr(), wo.data_ptr(), out.data_ptr(), Bp, Npts,
+                                K, G, C_out, float(slope), _stream()), "pf_edgeconv")
+    return out
+
+
+# ---- (3) flow ------------------------------------------------------------------------------------
+def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
+    """raw[nb, M, 192] -> sb[nb, M, 8] = (s0,s1,s2,b0,b1,b2,0,0): coupling2 scale/bias per input point."""
+    _chk(raw, "raw"), _chk(cond_w, "cond_w")
+    nb, M, w = raw.shape
+    if w != 192 or cond_w.shape != (nb, N.PF_COND_BLOB):
+        raise ValueError("flow_cond: bad shapes")
+    sb = torch.empty((nb, M, 8), dtype=torch.float32, device=raw.device)
+    with _dev(raw):
+        N.check(lib.pf_flow_cond(raw.data_ptr(), cond_w.data_ptr(), sb.data_ptr(), M, nb, _stream()), "pf_flow_cond")
+    return sb
+
+
+def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor):
+    """x[M,3] -> (z[M,3], ssum[M]); FlowBlock.forward x nb (interpflow.py:66-74,302-313)."""
+    _chk(x, "x"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w")
+    nb, M, _ = raw.shape
+    if x.shape != (M, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_BLOB):
+        raise ValueError("flow_fwd: bad shapes")
+    z = torch.empty_like(x)
+    ssum = torch.empty((M,), dtype=torch.float32, device=x.device)
+    with _dev(x):
+        N.check(lib.pf_flow_fwd(x.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
+                                ssum.data_ptr(), M, nb, _stream()), "pf_flow_fwd")
+    return z, ssum
+
+
+def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor, R: int):
+    """zin[M*R,3] (row n*R+r conditioned by input point n) -> x[M*R,3]; FlowBlock.inverse x nb."""
+    _chk(zin, "zin"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w")
+    nb, M, _ = raw.shape
+    if zin.shape != (M * R, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_BLOB):
+        raise ValueError("flow_inv: bad shapes")
+    x = torch.empty_like(zin)
+    with _dev(zin):
+        N.check(lib.pf_flow_inv(zin.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(), M, R,
+                                nb, _stream()), "pf_flow_inv")
+    return x
+
+
+# ---- (4) interpolation ---------------------------------------------------------------------------
+def interp(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, pq: torch.Tensor, w: torch.Tensor, R: int):
+    """xyz[Bp,N,3], z[Bp,N,3], idx[Bp,N,>=8] int32, pq[Bp*N,640] -> out[Bp, N*R, 3] (row n*R + r)."""
+    _chk(xyz, "xyz"), _chk(z, "z"), _chk(idx, "idx", torch.int32), _chk(pq, "pq"), _chk(w, "w")
+    Bp, Npts, _ = xyz.shape
+    if z.shape != xyz.shape or pq.shape != (Bp * Npts, 640) or w.numel() != N.PF_INTERP_BLOB:
+        raise ValueError("interp: bad shapes")
+    if idx.shape[:2] != (Bp, Npts) or idx.shape[2] < 8:
+        raise ValueError("interp: idx must be [Bp, N, >=8]")
+    out = torch.empty((Bp, Npts * R, 3), dtype=torch.float32, device=xyz.device)
+    with _dev(xyz):
+        N.check(lib.pf_interp(xyz.data_ptr(), z.data_ptr(), idx.data_ptr(), idx.shape[2], pq.data_ptr(), w.data_ptr(),
+                              out.data_ptr(), Bp, Npts, R, _stream()), "pf_interp")
+    return out
+
+
+# ---- caller side ---------------------------------------------------------------------------------
+def fps(xyz: torch.Tensor, npoint: int):
+    """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0)."""
+    _chk(xyz, "xyz")
+    B, n, _ = xyz.shape
+    idx = torch.empty((B, npoint), dtype=torch.int32, device=xyz.device)
+    with _dev(xyz):
+        N.check(lib.pf_fps(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), None, _stream()), "pf_fps")
+    return idx
+
+
+def knn_patch(q: torch.Tensor, p: torch.Tensor, k: int):
+    """q[B,nq,3], p[B,np,3] -> idx[B,nq,k] int32 ascending by (distance, index) (knn_cuda.KNN, patch.py:107)."""
+    _chk(q, "q"), _chk(p, "p")
+    B, nq, _ = q.shape
+    idx = torch.empty((B, nq, k), dtype=torch.int32, device=q.device)
+    with _dev(q):
+        N.check(lib.pf_knn_patch(q.data_ptr(), p.data_ptr(), B, nq, p.shape[1], k, idx.data_ptr(), _stream()),
+                "pf_knn_patch")
+    return idx

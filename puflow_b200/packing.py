@@ -1,0 +1,196 @@
+"""One-time weight packing: reference checkpoint layout (408-key state_dict of PointInterpFlow,
+/root/reference/modules/discrete/interpflow.py:262-290) -> the k-major fp32 blobs the
+kernels consume.  All algebra is done in float64 and rounded to fp32 once.
+
+What is folded / composed here (each is exact algebra, so only fp32 summation order changes):
+
+* eval-mode BatchNorm2d (eps 1e-5) into the preceding 1x1 conv:  W' = W g/sqrt(v+eps),
+  b' = (b-mean) g/sqrt(v+eps) + beta                                   (interpflow.py:91-98,144-151,203-221)
+* the edge feature [x_i, x_j, x_j - x_i] (interpflow.py:223-232) is linear in (x_i, x_j):
+  W.[x_i; x_j; x_j-x_i] = (W1-W3).x_i + (W2+W3).x_j  -> per-point projections P (own point, carries
+  every bias) and Q (neighbour) for all five convs of a dense block at once;
+  likewise the distance encoder's [x_i, x_j, x_i-x_j, |.|] (interpflow.py:106-114);
+* DistanceEncoder.mlp.6, feat_conv.conv_out and WeightEstimationUnit.mlp.0 (+BN) have no activation
+  between them (interpflow.py:98,133-134,145-146,242) and are composed into one 192->128 layer;
+* InvertibleConv1x1_1D's inverse is computed once (float64) instead of torch.inverse per call
+  (/root/reference/modules/flows/permutate.py:122-126); exp(+-logs) of ActNorm likewise
+  (/root/reference/modules/flows/normalize.py:30-43).
+"""
+from typing import Dict
+
+import torch
+
+from ._native import PF_COND_BLOB, PF_FLOW_BLOB, PF_INTERP_BLOB
+
+BN_EPS = 1e-5
+NUM_BLOCKS = 6
+# (C_in, growth, C_out) of feat_convs[i] and cond dim of merge_convs[i]  (interpflow.py:273-275)
+FEAT_CFG = [(3, 8, 32), (32, 16, 64), (64, 32, 128), (128, 32, 128), (128, 32, 128), (128, 32, 128)]
+
+
+def _f64(t):
+    return t.detach().to("cpu", torch.float64)
+
+
+def _conv_bn(sd, conv: str, bn: str = None):
+    """(W[O,I], b[O]) of a 1x1 conv, with the following eval-mode BN folded in when `bn` is given."""
+    W = _f64(sd[conv + ".weight"])
+    W = W.reshape(W.shape[0], W.shape[1])
+    b = _f64(sd[conv + ".bias"])
+    if bn is not None:
+        s = _f64(sd[bn + ".weight"]) / torch.sqrt(_f64(sd[bn + ".running_var"]) + BN_EPS)
+        W = W * s[:, None]
+        b = (b - _f64(sd[bn + ".running_mean"])) * s + _f64(sd[bn + ".bias"])
+    return W, b
+
+
+def _split_edge(W, C):
+    """Columns [x_i | x_j | x_j - x_i | hidden] -> (A: coeff of x_i, B: coeff of x_j, Wh)."""
+    W1, W2, W3, Wh = W[:, :C], W[:, C:2 * C], W[:, 2 * C:3 * C], W[:, 3 * C:]
+    return W1 - W3, W2 + W3, Wh
+
+
+def pack_edgeconv(sd, prefix: str, C: int, g: int, C_out: int, layers: int = 4):
+    """FeatureExtractUnit (interpflow.py:190-248) -> dict(wpq[C,2R], bpq[2R], wd[...], wo[layers*g, C_out])."""
+    A_rows, B_rows, biases, wd = [], [], [], []
+    for l in range(layers):
+        W, b = _conv_bn(sd, f"{prefix}.convs.{l}.0", f"{prefix}.convs.{l}.1")
+        assert W.shape == (g, 3 * C + g * l), (prefix, l, W.shape)
+        A, B, Wh = _split_edge(W, C)
+        A_rows.append(A), B_rows.append(B), biases.append(b)
+        if l > 0:
+            wd.append(Wh.t().contiguous().reshape(-1))          # [g*l][g] k-major
+    W, b = _conv_bn(sd, f"{prefix}.conv_out")
+    assert W.shape == (C_out, 3 * C + g * layers)
+    A, B, Wh = _split_edge(W, C)
+    A_rows.append(A), B_rows.append(B), biases.append(b)
+    A_all, B_all, b_all = torch.cat(A_rows), torch.cat(B_rows), torch.cat(biases)     # [R, C], [R]
+    R = A_all.shape[0]
+    return dict(
+        wpq=torch.cat([A_all.t(), B_all.t()], dim=1).contiguous(),                   # [C, 2R]
+        bpq=torch.cat([b_all, torch.zeros(R, dtype=torch.float64)]),
+        wd=torch.cat(wd),
+        wo=Wh.t().contiguous(),                                                       # [layers*g, C_out]
+    )
+
+
+def pack_interp(sd):
+    """InterpolationModule (interpflow.py:85-186) -> dict(wpq[3,640], bpq[640], blob[PF_INTERP_BLOB])."""
+    p = "interp.knn_context.distance_encoder.mlp"
+    Wd0, bd0 = _conv_bn(sd, p + ".0", p + ".1")            # [64,10] on [x_i, x_j, x_i-x_j, dist]
+    Wd3, bd3 = _conv_bn(sd, p + ".3", p + ".4")            # [64,64]
+    Wd6, bd6 = _conv_bn(sd, p + ".6")                      # [128,64]
+    Pd, Qd, wdist = Wd0[:, 0:3] + Wd0[:, 6:9], Wd0[:, 3:6] - Wd0[:, 6:9], Wd0[:, 9]
+
+    e = pack_edgeconv(sd, "interp.knn_context.feat_conv", 3, 16, 128, layers=8)
+    # e["wpq"]: [3, 2*256] with R = 8*16 + 128: columns [dense 128 | conv_out 128] for P then Q
+    Ae, Be = e["wpq"][:, :256].t(), e["wpq"][:, 256:].t()  # [256,3]
+    be = e["bpq"][:256]
+    Wout_h = e["wo"].t()                                   # [128 out, 128 hidden]
+
+    q = "interp.weight_unit.mlp"
+    W0, b0 = _conv_bn(sd, q + ".0", q + ".1")              # [128,256] on [dist feats 128 | context feats 128]
+    W3, b3 = _conv_bn(sd, q + ".3", q + ".4")              # [64,128]
+    W6, b6 = _conv_bn(sd, q + ".6")                        # [32,64]
+    W0a, W0b = W0[:, :128], W0[:, 128:]
+    M1 = W0a @ Wd6                                         # [128,64]   acts on d2
+    M2 = W0b @ Wout_h                                      # [128,128]  acts on the dense block's h
+    Pm = W0b @ Ae[128:]                                    # [128,3]
+    Qm = W0b @ Be[128:]
+    bm = W0a @ bd6 + W0b @ be[128:] + b0
+
+    P = torch.cat([Pd, Ae[:128], Pm])                      # [320,3]
+    Q = torch.cat([Qd, Be[:128], Qm])
+    bias = torch.cat([bd0, be[:128], bm, torch.zeros(320, dtype=torch.float64)])
+    w6 = torch.zeros(64, 32, dtype=torch.float64)
+    w6[:, :W6.shape[0]] = W6.t()
+    b6p = torch.zeros(32, dtype=torch.float64)
+    b6p[:b6.shape[0]] = b6
+    blob = torch.cat([
+        wdist,                                 # 0
+        Wd3.t().reshape(-1),                   # 64     [64][64]
+        bd3,                                   # 4160
+        e["wd"],                               # 4224   layers 1..7, [16 l][16]
+        W3.t().reshape(-1),                    # 11392  [128][64]
+        b3,                                    # 19584
+        w6.reshape(-1),                        # 19648  [64][32]
+        b6p,                                   # 21696
+        M1.t().reshape(-1),                    # 21728  [64][128]
+        M2.t().reshape(-1),                    # 29920  [128][128]
+    ])
+    assert blob.numel() == PF_INTERP_BLOB, blob.numel()
+    return dict(wpq=torch.cat([P.t(), Q.t()], dim=1).contiguous(), bpq=bias, blob=blob)
+
+
+def pack_flow_block(sd, i: int):
+    """FlowBlock i (interpflow.py:46-82) -> dict(wc[cond,192], flow[PF_FLOW_BLOB], cond[PF_COND_BLOB],
+    logdet_const) ; logdet_const = sum(logs) + log|det W| (per point)."""
+    p = f"flow_blocks.{i}"
+    tdim = 1 if i % 2 == 0 else 2                           # interpflow.py:55 (is_even = i % 2 == 0, :283)
+    logs = _f64(sd[p + ".actnorm.logs"]).reshape(3)
+    bias = _f64(sd[p + ".actnorm.bias"]).reshape(3)
+    W = _f64(sd[p + ".permutate1.permutater.W"])
+    direct = sd[p + ".permutate2.permutater.direct_idx"].tolist()
+    assert direct == [2, 1, 0], "kernels hard-code the 'reverse' permutation"
+    c1 = p + ".coupling1.bias_net.layers"
+    W1 = _f64(sd[c1 + ".0.weight"])                         # [64, tdim + cond]
+    assert W1.shape[0] == 64
+    w1h = torch.zeros(2, 64, dtype=torch.float64)
+    w1h[:tdim] = W1[:, :tdim].t()
+    w4 = torch.zeros(64, 2, dtype=torch.float64)
+    W4 = _f64(sd[c1 + ".4.weight"])                         # [3 - tdim, 64]
+    w4[:, :3 - tdim] = W4.t()
+    b4 = torch.zeros(2, dtype=torch.float64)
+    b4[:3 - tdim] = _f64(sd[c1 + ".4.bias"])
+    flow = torch.zeros(PF_FLOW_BLOB, dtype=torch.float64)
+    flow[0:3], flow[3:6], flow[6:9] = torch.exp(logs), bias, torch.exp(-logs)
+    flow[9:18], flow[18:27], flow[27] = W.reshape(-1), torch.linalg.inv(W).reshape(-1), float(tdim)
+    flow[32:160] = w1h.reshape(-1)
+    flow[160:224] = _f64(sd[c1 + ".2.bias"])
+    flow[224:352] = w4.reshape(-1)
+    flow[352:354] = b4
+    flow[384:4480] = _f64(sd[c1 + ".2.weight"]).t().reshape(-1)
+
+    s, b = p + ".coupling2.scale_net.layers", p + ".coupling2.bias_net.layers"
+    cond = torch.zeros(PF_COND_BLOB, dtype=torch.float64)
+    cond[0:4096] = _f64(sd[s + ".2.weight"]).t().reshape(-1)
+    cond[4096:8192] = _f64(sd[b + ".2.weight"]).t().reshape(-1)
+    cond[8192:8256] = _f64(sd[s + ".2.bias"])
+    cond[8256:8320] = _f64(sd[b + ".2.bias"])
+    ws4, wb4 = torch.zeros(64, 4, dtype=torch.float64), torch.zeros(64, 4, dtype=torch.float64)
+    ws4[:, :3], wb4[:, :3] = _f64(sd[s + ".4.weight"]).t(), _f64(sd[b + ".4.weight"]).t()
+    cond[8320:8576], cond[8576:8832] = ws4.reshape(-1), wb4.reshape(-1)
+    cond[8832:8835], cond[8836:8839] = _f64(sd[s + ".4.bias"]), _f64(sd[b + ".4.bias"])
+
+    wc = torch.cat([W1[:, tdim:].t(), _f64(sd[s + ".0.weight"]).t(), _f64(sd[b + ".0.weight"]).t()], dim=1)
+    logdet_const = float(logs.sum() + torch.linalg.slogdet(W)[1])
+    return dict(wc=wc.contiguous(), flow=flow, cond=cond, logdet_const=logdet_const)
+
+
+def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
+    """Whole model -> nested dict of contiguous fp32 tensors on `device`."""
+    out = {"feat": [], "merge": [], "wc": [], "logdet_const": 0.0}
+    flows, conds = [], []
+    for i, (C, g, Co) in enumerate(FEAT_CFG):
+        out["feat"].append(pack_edgeconv(sd, f"feat_convs.{i}", C, g, Co))
+        out["merge"].append(dict(
+            w1=_f64(sd[f"merge_convs.{i}.conv1.weight"]).t().contiguous(),
+            b1=_f64(sd[f"merge_convs.{i}.conv1.bias"]),
+            w2=_f64(sd[f"merge_convs.{i}.conv2.weight"]).t().contiguous()))
+        fb = pack_flow_block(sd, i)
+        out["wc"].append(fb["wc"])
+        flows.append(fb["flow"]), conds.append(fb["cond"])
+        out["logdet_const"] += fb["logdet_const"]
+    out["flow"] = torch.stack(flows)
+    out["cond"] = torch.stack(conds)
+    out["interp"] = pack_interp(sd)
+
+    def cast(o):
+        if isinstance(o, torch.Tensor):
+            return o.to(torch.float32).contiguous().to(device)
+        if isinstance(o, dict):
+            return {k: cast(v) for k, v in o.items()}
+        if isinstance(o, list):
+            return [cast(v) for v in o]
+        return o
+    return cast(out)

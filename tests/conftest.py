@@ -25,3 +25,15 @@ def golden():
 def state_dict():
     import torch
     return torch.load(os.path.join(GOLDEN, "puflow-x4-pu1k.pt"), map_location="cpu")
+
+
+def _ensure_native_built():
+    """The package refuses to import without its CUDA library; nvcc cross-compiles it here (no GPU
+    needed).  On the GPU box the prebuilt .so travels with the snapshot."""
+    so = os.path.join(ROOT, "puflow_b200", "_lib", "libpuflow_b200.so")
+    if not os.path.exists(so):
+        import __graft_entry__
+        __graft_entry__.build()
+
+
+_ensure_native_built()

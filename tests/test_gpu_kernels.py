@@ -1,0 +1,322 @@
+"""GPU parity tests: every C-ABI kernel against the CPU oracle (oracle/) / the golden fixtures of the
+unmodified reference (tests/golden), through puflow_b200.ops (ctypes -> C-ABI).
+
+Tolerances (tests/parity.py): indices bit-exact; fp32 tensors normwise per batch item, 1e-4 on final
+outputs and per-kernel outputs, 1e-3 on the ill-conditioned latent intermediates (z, zup)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import puflow_oracle as po
+from oracle import synth
+from tests import emulate, parity
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from puflow_b200 import ops as _ops
+    return _ops
+
+
+@pytest.fixture(scope="module")
+def packed(state_dict):
+    from puflow_b200 import packing
+    return packing.pack_state_dict(state_dict, "cpu")
+
+
+def _to(o, dev):
+    if isinstance(o, torch.Tensor):
+        return o.to(dev)
+    if isinstance(o, dict):
+        return {k: _to(v, dev) for k, v in o.items()}
+    if isinstance(o, list):
+        return [_to(v, dev) for v in o]
+    return o
+
+
+# ---- (1) kNN ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("B,N,K,shape", [(8, 256, 16, "surface"), (3, 256, 8, "uniform"), (2, 1024, 32, "uniform"),
+                                         (2, 2500, 16, "uniform"), (3, 250, 16, "uniform"), (2, 37, 4, "uniform"),
+                                         (1, 4096, 16, "uniform"), (5, 16, 16, "uniform")])
+def test_knn_bit_exact(ops, dev, B, N, K, shape):
+    if shape == "surface":
+        p = synth.make_patches(B, N, seed=B * N + K, shape="surface")
+    else:
+        p = np.random.default_rng(B * N + K).uniform(-1, 1, (B, N, 3)).astype(np.float32)
+    d_ref, i_ref = po.knn(p, p, K)
+    t = torch.from_numpy(p).to(dev)
+    d, i = ops.knn_topk(t, t, K)
+    assert np.array_equal(i.cpu().numpy().astype(np.int64), i_ref)
+    assert np.array_equal(d.cpu().numpy(), d_ref)
+
+
+def test_knn_lattice_ties(ops, dev):
+    p = np.stack([synth.make_cloud(343, s, "lattice") for s in (3, 4)])
+    _, i_ref = po.knn(p, p, 16)
+    t = torch.from_numpy(p).to(dev)
+    _, i = ops.knn_topk(t, t, 16)
+    assert np.array_equal(i.cpu().numpy().astype(np.int64), i_ref)
+
+
+def test_knn_query_set_differs_from_points(ops, dev):
+    rng = np.random.default_rng(0)
+    q = rng.uniform(-1, 1, (4, 77, 3)).astype(np.float32)
+    p = rng.uniform(-1, 1, (4, 1500, 3)).astype(np.float32)
+    d_ref, i_ref = po.knn(q, p, 8)
+    d, i = ops.knn_topk(torch.from_numpy(q).to(dev), torch.from_numpy(p).to(dev), 8)
+    assert np.array_equal(i.cpu().numpy().astype(np.int64), i_ref) and np.array_equal(d.cpu().numpy(), d_ref)
+
+
+def test_knn_golden_and_errors(ops, dev, golden):
+    g = golden("net_pu1k.npz")
+    t = torch.from_numpy(g["xyz"]).to(dev)
+    d, i = ops.knn_topk(t, t, 16)
+    assert np.array_equal(i.cpu().numpy(), g["knn_idx"]) and np.array_equal(d.cpu().numpy(), g["knn_d"])
+    from puflow_b200._native import PuflowError
+    with pytest.raises(PuflowError):
+        ops.knn_topk(t[:, :8].contiguous(), t[:, :8].contiguous(), 16)          # K > np
+    with pytest.raises(PuflowError):
+        ops.knn_topk(t.cpu(), t.cpu(), 16)                                       # no CPU fallback
+    e = torch.empty((0, 256, 3), device=dev)
+    assert ops.knn_topk(e, e, 16)[1].shape == (0, 256, 16)                       # empty batch
+
+
+# ---- (5) Chamfer -----------------------------------------------------------------------------------
+def test_chamfer_known_answer(ops, dev, golden):
+    """The reference's own unit test (metric/PyTorchCD/unit_test.py:14-35): MSE < 1e-8, indices identical."""
+    g = golden("chamfer_unit.npz")
+    d1, d2, i1, i2 = [t.cpu().numpy() for t in ops.chamfer_nn(torch.from_numpy(g["a"]).to(dev),
+                                                              torch.from_numpy(g["b"]).to(dev))]
+    assert np.mean((d1 - g["dist1"]) ** 2) + np.mean((d2 - g["dist2"]) ** 2) < 1e-8
+    assert np.array_equal(i1, g["idx1"]) and np.array_equal(i2, g["idx2"])
+
+
+@pytest.mark.parametrize("B,n,m", [(2, 8216, 2048), (3, 101, 57), (1, 5000, 20024), (4, 1, 3)])
+def test_chamfer_bit_exact(ops, dev, B, n, m):
+    rng = np.random.default_rng(n + m)
+    a = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    b = rng.uniform(-1, 1, (B, m, 3)).astype(np.float32)
+    if n > 100:
+        b[:, : min(m, 50)] = a[:, : min(m, 50)]            # exact zeros + duplicate candidates (ties)
+        b[:, 1] = b[:, 0]
+    ref = po.chamfer_nn(a, b)
+    out = ops.chamfer_nn(torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev))
+    for o, r in zip(out, ref):
+        assert np.array_equal(o.cpu().numpy(), r)
+
+
+# ---- linear ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("M,K,N,act", [(512, 3, 128, 0), (300, 32, 256, 0), (1000, 128, 512, 0), (256, 128, 64, 1),
+                                       (130, 64, 16, 1), (257, 160, 192, 2), (128, 3, 640, 0), (1, 16, 32, 0)])
+def test_linear(ops, dev, M, K, N, act):
+    gen = torch.Generator().manual_seed(M + K + N)
+    a = torch.randn(M, K, generator=gen)
+    w = torch.randn(K, N, generator=gen) / K ** 0.5
+    b = torch.randn(N, generator=gen)
+    ref = a.double() @ w.double() + b.double()
+    if act == 1:
+        ref = torch.relu(ref)
+    elif act == 2:
+        ref = torch.nn.functional.leaky_relu(ref, 0.05)
+    out = ops.linear(a.to(dev), w.to(dev), b.to(dev), act, 0.05).cpu()
+    assert (out.double() - ref).abs().max() <= 2e-6 * max(1.0, ref.abs().max())
+    # row-strided input view, no bias
+    big = torch.randn(M, K + 4 * 3, generator=gen)
+    out2 = ops.linear(big.to(dev)[:, 4:4 + K], w.to(dev)).cpu()
+    ref2 = big[:, 4:4 + K].double() @ w.double()
+    assert (out2.double() - ref2).abs().max() <= 2e-6 * max(1.0, ref2.abs().max())
+
+
+# ---- (2) EdgeConv ----------------------------------------------------------------------------------
+@pytest.mark.parametrize("blk,Bp,N", [(0, 3, 256), (1, 2, 256), (3, 3, 256), (5, 1, 250), (2, 300, 64)])
+def test_edgeconv_blocks_real_weights(ops, dev, packed, blk, Bp, N):
+    from puflow_b200.packing import FEAT_CFG
+    C, g, Co = FEAT_CFG[blk]
+    gen = torch.Generator().manual_seed(blk * 1000 + N)
+    x = torch.randn(Bp * N, C, generator=gen)
+    p = synth.make_patches(Bp, N, seed=blk, shape="uniform")
+    idx = torch.from_numpy(po.knn(p, p, 16)[1]).int()
+    f = packed["feat"][blk]
+    pq = emulate.linear(x, f["wpq"], f["bpq"])
+    ref = emulate.edgeconv(pq, idx, f["wd"], f["wo"], N, g, Co)
+    out = ops.edgeconv(pq.to(dev), idx.to(dev), f["wd"].to(dev), f["wo"].to(dev), Bp, N, g, Co).cpu()
+    ok, err = parity.close_norm(out.view(Bp, N, Co).numpy(), ref.view(Bp, N, Co).numpy(), 1e-5)
+    assert ok, err
+
+
+@pytest.mark.parametrize("K", [8, 32])
+def test_edgeconv_other_k(ops, dev, packed, K):
+    """config 4 of BASELINE.json sweeps k = 8/16/32 with block-3 weights."""
+    Bp, N, (C, g, Co) = 2, 512, (128, 32, 128)
+    gen = torch.Generator().manual_seed(K)
+    x = torch.randn(Bp * N, C, generator=gen)
+    p = synth.make_patches(Bp, N, seed=K, shape="uniform")
+    idx = torch.from_numpy(po.knn(p, p, K)[1]).int()
+    f = packed["feat"][3]
+    pq = emulate.linear(x, f["wpq"], f["bpq"])
+    ref = emulate.edgeconv(pq, idx, f["wd"], f["wo"], N, g, Co)
+    out = ops.edgeconv(pq.to(dev), idx.to(dev), f["wd"].to(dev), f["wo"].to(dev), Bp, N, g, Co).cpu()
+    ok, err = parity.close_norm(out.view(Bp, N, Co).numpy(), ref.view(Bp, N, Co).numpy(), 1e-5)
+    assert ok, err
+
+
+# ---- (3) flow --------------------------------------------------------------------------------------
+def _flow_inputs(packed, M, seed):
+    gen = torch.Generator().manual_seed(seed)
+    x = torch.randn(M, 3, generator=gen) * 0.5
+    raw = torch.stack([emulate.linear(torch.randn(M, packed["wc"][i].shape[0], generator=gen), packed["wc"][i])
+                       for i in range(6)])
+    return x, raw
+
+
+@pytest.mark.parametrize("M", [256, 1000, 77])
+def test_flow_cond_fwd_inv(ops, dev, packed, M):
+    x, raw = _flow_inputs(packed, M, M)
+    sb_ref = emulate.flow_cond(raw, packed["cond"])
+    sb = ops.flow_cond(raw.to(dev), packed["cond"].to(dev))
+    assert (sb.cpu() - sb_ref).abs().max() <= 1e-5 * max(1.0, sb_ref.abs().max())
+    z_ref, ss_ref = emulate.flow_fwd(x, raw, sb_ref, packed["flow"])
+    z, ss = ops.flow_fwd(x.to(dev), raw.to(dev), sb, packed["flow"].to(dev))
+    ok, err = parity.close_norm(z.cpu().numpy()[None], z_ref.numpy()[None], 1e-4)
+    assert ok, err
+    assert (ss.cpu() - ss_ref).abs().max() <= 1e-4 * max(1.0, ss_ref.abs().max())
+    R = 4
+    zin = torch.randn(M * R, 3, generator=torch.Generator().manual_seed(1)) * 0.5
+    xi_ref = emulate.flow_inv(zin, raw, sb_ref, packed["flow"], R)
+    xi = ops.flow_inv(zin.to(dev), raw.to(dev), sb, packed["flow"].to(dev), R)
+    ok, err = parity.close_norm(xi.cpu().numpy()[None], xi_ref.numpy()[None], 1e-4)
+    assert ok, err
+    # round trip: inverse(forward(x)) == x  (R = 1)
+    back = ops.flow_inv(z, raw.to(dev), sb, packed["flow"].to(dev), 1).cpu()
+    assert (back - x).abs().max() < 2e-5
+
+
+def test_flow_blocks_golden(ops, dev, packed, golden):
+    """Single FlowBlock forward / inverse against the unmodified reference (flows_pu1k.npz)."""
+    fl = golden("flows_pu1k.npz")
+    for bi in (0, 1):
+        x = torch.from_numpy(fl[f"b{bi}_x"]).reshape(-1, 3)
+        c = torch.from_numpy(fl[f"b{bi}_c"]).reshape(x.shape[0], -1)
+        raw = ops.linear(c.to(dev), packed["wc"][bi].to(dev))[None].contiguous()
+        cw, fw = packed["cond"][bi:bi + 1].to(dev), packed["flow"][bi:bi + 1].to(dev)
+        sb = ops.flow_cond(raw, cw)
+        y, _ = ops.flow_fwd(x.to(dev), raw, sb, fw)
+        ok, err = parity.close_norm(y.cpu().view(2, 64, 3).numpy(), fl[f"b{bi}_block_fwd"], 1e-4)
+        assert ok, (bi, err)
+        xi = ops.flow_inv(x.to(dev), raw, sb, fw, 1)
+        ok, err = parity.close_norm(xi.cpu().view(2, 64, 3).numpy(), fl[f"b{bi}_block_inv"], 1e-4)
+        assert ok, (bi, err)
+
+
+# ---- (4) interpolation -----------------------------------------------------------------------------
+@pytest.mark.parametrize("Bp,N,R", [(3, 256, 4), (2, 100, 2), (1, 256, 16)])
+def test_interp(ops, dev, packed, Bp, N, R):
+    p = synth.make_patches(Bp, N, seed=N + R, shape="surface")
+    xyz = torch.from_numpy(p)
+    z = torch.randn(Bp, N, 3, generator=torch.Generator().manual_seed(R)) * 0.6
+    idx = torch.from_numpy(po.knn(p, p, 16)[1]).int()
+    wi = packed["interp"]
+    pq = emulate.linear(xyz.reshape(-1, 3), wi["wpq"], wi["bpq"])
+    ref, _ = emulate.interp(xyz, z, idx, pq, wi["blob"], R)
+    out = ops.interp(xyz.to(dev), z.to(dev), idx.to(dev), pq.to(dev), wi["blob"].to(dev), R).cpu()
+    ok, err = parity.close_norm(out.numpy(), ref.numpy(), 1e-4)
+    assert ok, err
+
+
+# ---- whole path ------------------------------------------------------------------------------------
+def test_network_stages_match_reference(dev, state_dict, golden):
+    from puflow_b200.engine import PUFlowEngine
+    g = golden("net_pu1k.npz")
+    eng = PUFlowEngine(state_dict, dev)
+    r = eng.forward(torch.from_numpy(g["xyz"]).to(dev), 4, return_all=True)
+    assert np.array_equal(r["knn_idx"].cpu().numpy(), g["knn_idx"])
+    for i in range(6):
+        ok, err = parity.close_norm(r["feats"][i].cpu().numpy(), g[f"feat{i}"], 1e-4)
+        assert ok, ("feat", i, err)
+        ok, err = parity.close_norm(r["cs"][i].cpu().numpy(), g[f"cs{i}"], 1e-4)
+        assert ok, ("cs", i, err)
+    ok, err = parity.close_norm(r["z"].cpu().numpy(), g["z"], 1e-3)
+    assert ok, ("z", err)
+    fz = r["zup"].cpu().view(3, 256, 4, 3).permute(0, 1, 3, 2).numpy()
+    ok, err = parity.close_norm(fz, g["fz"], 1e-3)
+    assert ok, ("fz", err)
+    ok, err = parity.close_norm(r["x"].cpu().numpy(), g["x"], 1e-4)
+    assert ok, ("x", err)
+    assert abs(float(r["logp_x"]) - float(g["logp_x"][0])) <= 1e-4 * abs(float(g["logp_x"][0]))
+    for b in range(3):
+        assert parity.chamfer_distance(r["x"][b].cpu().numpy(), g["x"][b]) <= 1e-5
+
+
+def test_network_vs_oracle_one_cloud(dev, state_dict):
+    """32 real kNN-256 patches of one synthetic 2,048-pt cloud (config 1 of BASELINE.json)."""
+    from puflow_b200.engine import PUFlowEngine
+    pc = torch.from_numpy(synth.make_cloud(2048, 2021, "torus"))[None]
+    pcn, _, _ = po.normalize_pc(pc)
+    seeds = torch.from_numpy(po.fps(pcn.numpy(), 32)).long()
+    _, pidx = po.knn(pcn[0][seeds[0]][None].numpy(), pcn.numpy(), 256)
+    patches, _, _ = po.normalize_pc(pcn[0][torch.from_numpy(pidx[0])])
+    ref = po.PUFlowOracle(state_dict).forward(patches, 4, return_all=True)
+    eng = PUFlowEngine(state_dict, dev)
+    r = eng.forward(patches.to(dev), 4, return_all=True)
+    assert np.array_equal(r["knn_idx"].cpu().numpy().astype(np.int64), ref["knn_idx"].numpy())
+    ok, err = parity.close_norm(r["x"].cpu().numpy(), ref["x"].numpy(), 1e-4)
+    assert ok, err
+    assert abs(float(r["logp_x"]) - float(ref["logp_x"])) <= 1e-4 * abs(float(ref["logp_x"]))
+
+
+def test_full_size_properties(dev, state_dict):
+    """BASELINE.json config 2 size (4,096 patches): size-independent properties instead of the oracle."""
+    from puflow_b200.engine import PUFlowEngine
+    Bp = 4096
+    p = synth.make_patches(Bp, 256, seed=2021, shape="surface")
+    xyz = torch.from_numpy(p).to(dev)
+    eng = PUFlowEngine(state_dict, dev)
+    r = eng.forward(xyz, 4, return_all=True)
+    idx = r["knn_idx"]
+    assert (idx[:, :, 0] == torch.arange(256, device=dev)[None]).all()           # self is the nearest
+    assert int(idx.min()) >= 0 and int(idx.max()) < 256
+    assert torch.isfinite(r["x"]).all() and r["x"].shape == (Bp, 1024, 3)
+    # the batch is processed patch by patch: a slice of the batch gives bit-identical results
+    sub = eng.forward(xyz[1000:1003].contiguous(), 4)[0]
+    assert torch.equal(sub, r["x"][1000:1003])
+    # oracle on 2 of the 4,096 patches
+    ref = po.PUFlowOracle(state_dict).forward(torch.from_numpy(p[[7, 4000]]), 4)[0]
+    ok, err = parity.close_norm(r["x"][[7, 4000]].cpu().numpy(), ref.numpy(), 1e-4)
+    assert ok, err
+    # flow round trip at full size: g(f(x)) with R = 1 returns the input
+    cond = eng.conditioning(r["cs"])
+    back = eng.g(r["z"], cond, 1)
+    assert (back - xyz).abs().max() < 5e-5
+
+
+# ---- caller side -----------------------------------------------------------------------------------
+@pytest.mark.parametrize("B,n,npoint", [(3, 2048, 32), (2, 5000, 78), (2, 40960, 700), (1, 12345, 300), (4, 100, 100)])
+def test_fps_bit_exact(ops, dev, B, n, npoint):
+    rng = np.random.default_rng(n)
+    p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    ref = po.fps(p, npoint)
+    out = ops.fps(torch.from_numpy(p).to(dev), npoint).cpu().numpy()
+    assert np.array_equal(out, ref)
+
+
+def test_fps_lattice_ties(ops, dev):
+    p = np.stack([synth.make_cloud(1000, s, "lattice") for s in (1, 2)])
+    assert np.array_equal(ops.fps(torch.from_numpy(p).to(dev), 200).cpu().numpy(), po.fps(p, 200))
+
+
+@pytest.mark.parametrize("B,nq,np_,k", [(2, 32, 2048, 256), (1, 78, 5000, 256), (2, 5, 300, 256), (1, 3, 1000, 1000)])
+def test_knn_patch_bit_exact(ops, dev, B, nq, np_, k):
+    rng = np.random.default_rng(np_)
+    p = rng.uniform(-1, 1, (B, np_, 3)).astype(np.float32)
+    q = p[:, :nq].copy()
+    ref = po.knn(q, p, k)[1]
+    out = ops.knn_patch(torch.from_numpy(q).to(dev), torch.from_numpy(p).to(dev), k).cpu().numpy()
+    assert np.array_equal(out.astype(np.int64), ref)
