@@ -17,7 +17,7 @@
 //
 // Packed per-block weights (puflow_b200/packing.py), floats:
 //   flow blob (PF_FLOW_BLOB = 4480):  0 exp(logs)[3] | 3 bias[3] | 6 exp(-logs)[3] | 9 W[9] | 18 Winv[9]
-//       | 27 tdim | 32 w1h[2][64] | 160 b2[64] | 224 w4[64][2] | 352 b4[2] | 384 w2[64][64]
+//       | 27 tdim | 28 reverse (1: channel reverse after coupling1, 0: identity) | 32 w1h[2][64] | 160 b2[64] | 224 w4[64][2] | 352 b4[2] | 384 w2[64][64]
 //   cond blob (PF_COND_BLOB = 8840):  0 ws2[64][64] | 4096 wb2[64][64] | 8192 bs2[64] | 8256 bb2[64]
 //       | 8320 ws4[64][4] | 8576 wb4[64][4] | 8832 bs4[4] | 8836 bb4[4]
 #include "common.cuh"
@@ -198,6 +198,7 @@ __global__ void __launch_bounds__(NT, 1)
         const int blk = INVERSE ? nblocks - 1 - it : it;
         const float* fw = fws + (size_t)blk * PF_FLOW_BLOB;
         const int tdim = (int)fw[27];
+        const bool rev = fw[28] != 0.f;
         const float* rawrow = raw + ((size_t)blk * M + m) * 192;
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f;
         if (tid < TP) {
@@ -213,7 +214,7 @@ __global__ void __launch_bounds__(NT, 1)
             } else {
                 // coupling2.inverse: z * exp(s) + b ; permutate2.inverse: reverse
                 float a0 = fmaf(x0, expf(s0), b0), a1 = fmaf(x1, expf(s1), b1), a2 = fmaf(x2, expf(s2), b2);
-                x0 = a2, x1 = a1, x2 = a0;
+                x0 = rev ? a2 : a0, x1 = a1, x2 = rev ? a0 : a2;
             }
             xs[p] = x0;
             xs[TP + p] = (tdim == 2) ? x1 : 0.f;
@@ -226,7 +227,7 @@ __global__ void __launch_bounds__(NT, 1)
                 // coupling1.forward (additive): h2 -= bias_net ; reverse ; coupling2.forward
                 if (tdim == 1) x1 -= o0, x2 -= o1;
                 else x2 -= o0;
-                float a0 = x2, a1 = x1, a2 = x0;
+                float a0 = rev ? x2 : x0, a1 = x1, a2 = rev ? x0 : x2;
                 x0 = (a0 - b0) * expf(-s0);
                 x1 = (a1 - b1) * expf(-s1);
                 x2 = (a2 - b2) * expf(-s2);

@@ -43,8 +43,10 @@ def knn_topk(q: torch.Tensor, p: torch.Tensor, K: int, return_dist: bool = True)
     np_ = p.shape[1]
     idx = torch.empty((B, nq, K), dtype=torch.int32, device=q.device)
     dist = torch.empty((B, nq, K), dtype=torch.float32, device=q.device) if return_dist else None
+    if B == 0 or nq == 0:
+        return dist, idx
     with _dev(q):
-        for b0 in range(0, max(B, 1), 65535):
+        for b0 in range(0, B, 65535):
             b1 = min(B, b0 + 65535)
             N.check(lib.pf_knn_topk(q[b0:b1].data_ptr(), p[b0:b1].data_ptr(), b1 - b0, nq, np_, K,
                                     idx[b0:b1].data_ptr(), dist[b0:b1].data_ptr() if return_dist else None,

@@ -145,6 +145,7 @@ def pack_flow_block(sd, i: int):
     flow = torch.zeros(PF_FLOW_BLOB, dtype=torch.float64)
     flow[0:3], flow[3:6], flow[6:9] = torch.exp(logs), bias, torch.exp(-logs)
     flow[9:18], flow[18:27], flow[27] = W.reshape(-1), torch.linalg.inv(W).reshape(-1), float(tdim)
+    flow[28] = 1.0                                          # permutate2 = 'reverse' (interpflow.py:53)
     flow[32:160] = w1h.reshape(-1)
     flow[160:224] = _f64(sd[c1 + ".2.bias"])
     flow[224:352] = w4.reshape(-1)

@@ -80,7 +80,7 @@ def flow_fwd(x, raw, sb, flow):
         x = x @ fw[9:18].reshape(3, 3).t()
         o = _coupling(fw, x, raw[i], tdim)
         x = torch.cat([x[:, :tdim], x[:, tdim:] - o], 1)
-        x = x.flip(1)
+        x = x.flip(1) if fw[28] != 0 else x
         s, b = sb[i][:, 0:3], sb[i][:, 3:6]
         x = (x - b) * torch.exp(-s)
         ssum = ssum + s.sum(1)
@@ -95,7 +95,7 @@ def flow_inv(z, raw, sb, flow, R):
         s = sb[i][:, 0:3].repeat_interleave(R, 0)
         b = sb[i][:, 3:6].repeat_interleave(R, 0)
         z = z * torch.exp(s) + b
-        z = z.flip(1)
+        z = z.flip(1) if fw[28] != 0 else z
         o = _coupling(fw, z, raw[i].repeat_interleave(R, 0), tdim)
         z = torch.cat([z[:, :tdim], z[:, tdim:] + o], 1)
         z = z @ fw[18:27].reshape(3, 3).t()

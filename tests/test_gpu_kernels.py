@@ -196,7 +196,7 @@ def test_flow_cond_fwd_inv(ops, dev, packed, M):
     assert ok, err
     # round trip: inverse(forward(x)) == x  (R = 1)
     back = ops.flow_inv(z, raw.to(dev), sb, packed["flow"].to(dev), 1).cpu()
-    assert (back - x).abs().max() < 2e-5
+    assert (back - x).abs().max() < 1e-4      # random conditioning features: exp(s) is far larger than with real cs
 
 
 def test_flow_blocks_golden(ops, dev, packed, golden):
