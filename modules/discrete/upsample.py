@@ -1,0 +1,95 @@
+"""Discrete PU-Flow x4 upsampling entry point -- same `upsampling()` signature, CLI flags and file
+formats as the reference's modules/discrete/upsample.py:20-86 (whitespace .xyz in, '%.6f' .xyz out,
+same file name), running on the puflow_b200 kernels.
+
+Additions that keep the reference behaviour as the default:
+  --device cuda:N      (the reference hard-codes cuda:0, upsample.py:27)
+  torchrun / WORLD_SIZE > 1: the file list is sharded round-robin over ranks, one process per GPU,
+  no collective (every rank writes its own output files, exactly like the reference's per-file loop).
+"""
+import os
+import sys
+import torch
+import numpy as np
+
+from argparse import ArgumentParser
+from typing import List
+from pathlib import Path
+
+sys.path.append(os.getcwd())
+
+from modules.utils.patch import PatchHelper
+from modules.discrete.interpflow import PointInterpFlow
+
+
+# -----------------------------------------------------------------------------------------
+@torch.no_grad()
+def upsampling(data_paths: List[str], target_path: str, checkpoint_path: str, up_ratio: int, num_outlier: int,
+               num_patch: int, num_upsampling: int = None, seed=None, device=None):
+
+    if seed is not None:
+        np.random.seed(seed)
+        torch.random.manual_seed(seed)
+        torch.cuda.manual_seed(seed)
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    if device is None:
+        device = torch.device(f"cuda:{int(os.environ.get('LOCAL_RANK', 0))}")
+    device = torch.device(device)
+    torch.cuda.set_device(device)
+
+    pc_channel = 3
+    network = PointInterpFlow(pc_channel)
+
+    network.load_state_dict(torch.load(checkpoint_path, map_location="cpu"))
+    network.set_to_initialized_state()
+    network = network.to(device)
+    network.eval()
+    patch_helper = PatchHelper(num_patch, patch_expand_ratio=4)
+
+    for path in sorted(data_paths)[rank::world] if world > 1 else data_paths:
+        _, file_name = os.path.split(path)
+
+        pt_input = np.loadtxt(path, dtype=np.float32)
+        pt_input = torch.from_numpy(pt_input).unsqueeze(0).to(device)
+        pt_input = pt_input[:, torch.randperm(pt_input.shape[1])].contiguous()
+
+        if num_upsampling is None:  # the number of points after upsamling
+            NUM_UPSAMPLING_POINTS = pt_input.shape[1] * up_ratio + (num_outlier or 0)
+        else:
+            NUM_UPSAMPLING_POINTS = num_upsampling + (num_outlier or 0)
+
+        pred = patch_helper.upsample(network, pt_input, npoint=NUM_UPSAMPLING_POINTS, upratio=up_ratio, jitter=False)
+
+        if num_outlier is not None and num_outlier > 0:
+            pred = PatchHelper.remove_outliers(pred, pt_input, num_outlier)
+
+        pred = pred.squeeze().cpu().numpy()
+        np.savetxt(Path(target_path) / file_name, pred, fmt='%.6f')
+
+
+# -----------------------------------------------------------------------------------------
+if __name__ == "__main__":
+
+    # usage: python modules/discrete/upsample.py --source=path/to/input --target=path/to/output --checkpoint=path/to/checkpoint --up_ratio=4 --num_out=20000
+
+    parser = ArgumentParser()
+    parser.add_argument('--source', type=str, help='Path of input directory')
+    parser.add_argument('--target', type=str, help='Path of output directory')
+    parser.add_argument('--seed', type=int, default=2021)
+    parser.add_argument('--checkpoint', type=str, help='Path of checkpoint')
+    parser.add_argument('--up_ratio', type=int, help='upsampling ratio', default=4)
+    parser.add_argument('--num_patch', type=int, help='number of point in each patch', default=256)  # 192
+    parser.add_argument('--num_out', type=int, default=None, help='number of point of output point cloud')
+    parser.add_argument('--device', type=str, default=None, help='CUDA device (default cuda:LOCAL_RANK)')
+
+    args = parser.parse_args()
+
+    os.makedirs(args.target, exist_ok=True)
+
+    data_paths = []
+    for root, dirs, files in os.walk(args.source):
+        data_paths.extend([os.path.join(root, f) for f in files if '.xyz' in f])
+
+    upsampling(data_paths, args.target, args.checkpoint, up_ratio=args.up_ratio,
+        num_outlier=24, num_patch=args.num_patch, num_upsampling=args.num_out, seed=args.seed, device=args.device)

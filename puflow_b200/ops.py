@@ -12,6 +12,51 @@ from . import _native as N
 lib = N.lib
 
 
+class LaunchLog:
+    """Optional launch accounting for bench.py / profiling: counts the kernels this module launches and,
+    when `events` is on, brackets each C-ABI call with CUDA events on the launching stream."""
+
+    def __init__(self, events: bool = False):
+        self.events = events
+        self.count = 0
+        self.records = []          # (tag, start_event, end_event)
+
+    def times_ms(self):
+        out = {}
+        for tag, e0, e1 in self.records:
+            out.setdefault(tag, []).append(e0.elapsed_time(e1))
+        return out
+
+
+_log = None
+
+
+def set_launch_log(log):
+    """Install (or remove, with None) a LaunchLog; returns the previous one."""
+    global _log
+    prev, _log = _log, log
+    return prev
+
+
+class _launch:
+    def __init__(self, tag: str, n: int = 1):
+        self.tag, self.n = tag, n
+
+    def __enter__(self):
+        if _log is not None:
+            _log.count += self.n
+            if _log.events:
+                self.e0 = torch.cuda.Event(enable_timing=True)
+                self.e0.record()
+
+    def __exit__(self, *exc):
+        if _log is not None and _log.events and exc[0] is None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _log.records.append((self.tag, self.e0, e1))
+        return False
+
+
 def _stream():
     return torch.cuda.current_stream().cuda_stream
 
@@ -48,9 +93,10 @@ def knn_topk(q: torch.Tensor, p: torch.Tensor, K: int, return_dist: bool = True)
     with _dev(q):
         for b0 in range(0, B, 65535):
             b1 = min(B, b0 + 65535)
-            N.check(lib.pf_knn_topk(q[b0:b1].data_ptr(), p[b0:b1].data_ptr(), b1 - b0, nq, np_, K,
-                                    idx[b0:b1].data_ptr(), dist[b0:b1].data_ptr() if return_dist else None,
-                                    _stream()), "pf_knn_topk")
+            with _launch(f"knn_topk_k{K}"):
+                N.check(lib.pf_knn_topk(q[b0:b1].data_ptr(), p[b0:b1].data_ptr(), b1 - b0, nq, np_, K,
+                                        idx[b0:b1].data_ptr(), dist[b0:b1].data_ptr() if return_dist else None,
+                                        _stream()), "pf_knn_topk")
     return dist, idx
 
 
@@ -67,7 +113,7 @@ def chamfer_nn(a: torch.Tensor, b: torch.Tensor):
     d2 = torch.empty((B, m), dtype=torch.float32, device=a.device)
     i1 = torch.empty((B, n), dtype=torch.int32, device=a.device)
     i2 = torch.empty((B, m), dtype=torch.int32, device=a.device)
-    with _dev(a):
+    with _dev(a), _launch("chamfer_nn", 2):
         N.check(lib.pf_chamfer_nn(a.data_ptr(), n, b.data_ptr(), m, B, d1.data_ptr(), i1.data_ptr(), d2.data_ptr(),
                                   i2.data_ptr(), _stream()), "pf_chamfer_nn")
     return d1, d2, i1, i2
@@ -88,7 +134,7 @@ def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = N.ACT_NONE, s
     if out is None:
         out = torch.empty((M, Nn), dtype=torch.float32, device=a.device)
     lda = a.stride(0) if M > 1 else max(K, a.stride(0))
-    with _dev(a):
+    with _dev(a), _launch(f"linear_k{K}_n{Nn}"):
         N.check(lib.pf_linear(a.data_ptr(), lda, w.data_ptr(), bias.data_ptr() if bias is not None else None,
                               out.data_ptr(), out.stride(0), M, K, Nn, act, float(slope), _stream()), "pf_linear")
     return out
@@ -106,7 +152,7 @@ def edgeconv(pq: torch.Tensor, idx: torch.Tensor, wd: torch.Tensor, wo: torch.Te
     if wd.numel() != 6 * G * G or wo.numel() != 4 * G * C_out:
         raise ValueError("edgeconv: packed weight sizes do not match (G, C_out)")
     out = torch.empty((Bp * Npts, C_out), dtype=torch.float32, device=pq.device)
-    with _dev(pq):
+    with _dev(pq), _launch(f"edgeconv_g{G}_c{C_out}_k{K}"):
         N.check(lib.pf_edgeconv(pq.data_ptr(), idx.data_ptr(), wd.data_ptr(), wo.data_ptr(), out.data_ptr(), Bp, Npts,
                                 K, G, C_out, float(slope), _stream()), "pf_edgeconv")
     return out
@@ -120,7 +166,7 @@ def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
     if w != 192 or cond_w.shape != (nb, N.PF_COND_BLOB):
         raise ValueError("flow_cond: bad shapes")
     sb = torch.empty((nb, M, 8), dtype=torch.float32, device=raw.device)
-    with _dev(raw):
+    with _dev(raw), _launch("flow_cond"):
         N.check(lib.pf_flow_cond(raw.data_ptr(), cond_w.data_ptr(), sb.data_ptr(), M, nb, _stream()), "pf_flow_cond")
     return sb
 
@@ -133,7 +179,7 @@ def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch
         raise ValueError("flow_fwd: bad shapes")
     z = torch.empty_like(x)
     ssum = torch.empty((M,), dtype=torch.float32, device=x.device)
-    with _dev(x):
+    with _dev(x), _launch("flow_fwd"):
         N.check(lib.pf_flow_fwd(x.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
                                 ssum.data_ptr(), M, nb, _stream()), "pf_flow_fwd")
     return z, ssum
@@ -146,7 +192,7 @@ def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: tor
     if zin.shape != (M * R, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_BLOB):
         raise ValueError("flow_inv: bad shapes")
     x = torch.empty_like(zin)
-    with _dev(zin):
+    with _dev(zin), _launch("flow_inv"):
         N.check(lib.pf_flow_inv(zin.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(), M, R,
                                 nb, _stream()), "pf_flow_inv")
     return x
@@ -162,7 +208,7 @@ def interp(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, pq: torch.Tens
     if idx.shape[:2] != (Bp, Npts) or idx.shape[2] < 8:
         raise ValueError("interp: idx must be [Bp, N, >=8]")
     out = torch.empty((Bp, Npts * R, 3), dtype=torch.float32, device=xyz.device)
-    with _dev(xyz):
+    with _dev(xyz), _launch("interp"):
         N.check(lib.pf_interp(xyz.data_ptr(), z.data_ptr(), idx.data_ptr(), idx.shape[2], pq.data_ptr(), w.data_ptr(),
                               out.data_ptr(), Bp, Npts, R, _stream()), "pf_interp")
     return out
@@ -174,7 +220,7 @@ def fps(xyz: torch.Tensor, npoint: int):
     _chk(xyz, "xyz")
     B, n, _ = xyz.shape
     idx = torch.empty((B, npoint), dtype=torch.int32, device=xyz.device)
-    with _dev(xyz):
+    with _dev(xyz), _launch(f"fps_n{n}"):
         N.check(lib.pf_fps(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), None, _stream()), "pf_fps")
     return idx
 
@@ -184,7 +230,7 @@ def knn_patch(q: torch.Tensor, p: torch.Tensor, k: int):
     _chk(q, "q"), _chk(p, "p")
     B, nq, _ = q.shape
     idx = torch.empty((B, nq, k), dtype=torch.int32, device=q.device)
-    with _dev(q):
+    with _dev(q), _launch("knn_patch"):
         N.check(lib.pf_knn_patch(q.data_ptr(), p.data_ptr(), B, nq, p.shape[1], k, idx.data_ptr(), _stream()),
                 "pf_knn_patch")
     return idx

@@ -122,48 +122,90 @@ def pack_interp(sd):
     return dict(wpq=torch.cat([P.t(), Q.t()], dim=1).contiguous(), bpq=bias, blob=blob)
 
 
-def pack_flow_block(sd, i: int):
-    """FlowBlock i (interpflow.py:46-82) -> dict(wc[cond,192], flow[PF_FLOW_BLOB], cond[PF_COND_BLOB],
-    logdet_const) ; logdet_const = sum(logs) + log|det W| (per point)."""
-    p = f"flow_blocks.{i}"
-    tdim = 1 if i % 2 == 0 else 2                           # interpflow.py:55 (is_even = i % 2 == 0, :283)
-    logs = _f64(sd[p + ".actnorm.logs"]).reshape(3)
-    bias = _f64(sd[p + ".actnorm.bias"]).reshape(3)
-    W = _f64(sd[p + ".permutate1.permutater.W"])
-    direct = sd[p + ".permutate2.permutater.direct_idx"].tolist()
-    assert direct == [2, 1, 0], "kernels hard-code the 'reverse' permutation"
-    c1 = p + ".coupling1.bias_net.layers"
-    W1 = _f64(sd[c1 + ".0.weight"])                         # [64, tdim + cond]
-    assert W1.shape[0] == 64
+def identity_flow_blob():
+    """A flow-step blob whose every sub-layer is the identity (float64); the set_* helpers below fill in
+    the sub-layers a caller wants.  Lets the single modules/flows layer classes run on the fused kernel."""
+    flow = torch.zeros(PF_FLOW_BLOB, dtype=torch.float64)
+    flow[0:3], flow[6:9] = 1.0, 1.0
+    flow[9:18] = flow[18:27] = torch.eye(3, dtype=torch.float64).reshape(-1)
+    flow[27], flow[28] = 1.0, 0.0
+    return flow
+
+
+def set_actnorm(flow, logs, bias):
+    """ActNorm (modules/flows/normalize.py:30-43): z = x exp(logs) + bias."""
+    logs, bias = _f64(logs).reshape(3), _f64(bias).reshape(3)
+    flow[0:3], flow[3:6], flow[6:9] = torch.exp(logs), bias, torch.exp(-logs)
+
+
+def set_matrix(flow, W):
+    """InvertibleConv1x1_1D (modules/flows/permutate.py:117-126) or any 3x3 channel mix: z_i = sum_j W[i][j] x_j."""
+    W = _f64(W)
+    flow[9:18], flow[18:27] = W.reshape(-1), torch.linalg.inv(W).reshape(-1)
+
+
+def set_coupling1(flow, W1, W2, b2, W4, b4, tdim: int):
+    """Additive coupling with LinearA1D(tdim + cdim -> 64 -> 64 -> 3 - tdim) (interpflow.py:22-43,55-58).
+    Returns the conditioning part of the first layer, [cdim, 64] k-major."""
+    W1, W4 = _f64(W1), _f64(W4)
+    assert W1.shape[0] == 64 and W4.shape == (3 - tdim, 64), "kernels are built for hidden width 64, 3 channels"
     w1h = torch.zeros(2, 64, dtype=torch.float64)
     w1h[:tdim] = W1[:, :tdim].t()
     w4 = torch.zeros(64, 2, dtype=torch.float64)
-    W4 = _f64(sd[c1 + ".4.weight"])                         # [3 - tdim, 64]
     w4[:, :3 - tdim] = W4.t()
-    b4 = torch.zeros(2, dtype=torch.float64)
-    b4[:3 - tdim] = _f64(sd[c1 + ".4.bias"])
-    flow = torch.zeros(PF_FLOW_BLOB, dtype=torch.float64)
-    flow[0:3], flow[3:6], flow[6:9] = torch.exp(logs), bias, torch.exp(-logs)
-    flow[9:18], flow[18:27], flow[27] = W.reshape(-1), torch.linalg.inv(W).reshape(-1), float(tdim)
-    flow[28] = 1.0                                          # permutate2 = 'reverse' (interpflow.py:53)
+    b4p = torch.zeros(2, dtype=torch.float64)
+    b4p[:3 - tdim] = _f64(b4)
+    flow[27] = float(tdim)
     flow[32:160] = w1h.reshape(-1)
-    flow[160:224] = _f64(sd[c1 + ".2.bias"])
+    flow[160:224] = _f64(b2)
     flow[224:352] = w4.reshape(-1)
-    flow[352:354] = b4
-    flow[384:4480] = _f64(sd[c1 + ".2.weight"]).t().reshape(-1)
+    flow[352:354] = b4p
+    flow[384:4480] = _f64(W2).t().reshape(-1)
+    return W1[:, tdim:].t().contiguous()
 
-    s, b = p + ".coupling2.scale_net.layers", p + ".coupling2.bias_net.layers"
-    cond = torch.zeros(PF_COND_BLOB, dtype=torch.float64)
-    cond[0:4096] = _f64(sd[s + ".2.weight"]).t().reshape(-1)
-    cond[4096:8192] = _f64(sd[b + ".2.weight"]).t().reshape(-1)
-    cond[8192:8256] = _f64(sd[s + ".2.bias"])
-    cond[8256:8320] = _f64(sd[b + ".2.bias"])
+
+def zero_cond_blob():
+    return torch.zeros(PF_COND_BLOB, dtype=torch.float64)
+
+
+def set_injector(cond, scale_layers, bias_layers):
+    """Affine injector nets (coupling.py:127-151): two LinearA1D(cdim -> 64 -> 64 -> 3).  *_layers =
+    (W0, W2, b2, W4, b4).  Returns the two first-layer matrices [cdim, 64] k-major (scale, bias)."""
+    (Ws0, Ws2, bs2, Ws4, bs4), (Wb0, Wb2, bb2, Wb4, bb4) = scale_layers, bias_layers
+    cond[0:4096] = _f64(Ws2).t().reshape(-1)
+    cond[4096:8192] = _f64(Wb2).t().reshape(-1)
+    cond[8192:8256], cond[8256:8320] = _f64(bs2), _f64(bb2)
     ws4, wb4 = torch.zeros(64, 4, dtype=torch.float64), torch.zeros(64, 4, dtype=torch.float64)
-    ws4[:, :3], wb4[:, :3] = _f64(sd[s + ".4.weight"]).t(), _f64(sd[b + ".4.weight"]).t()
+    ws4[:, :3], wb4[:, :3] = _f64(Ws4).t(), _f64(Wb4).t()
     cond[8320:8576], cond[8576:8832] = ws4.reshape(-1), wb4.reshape(-1)
-    cond[8832:8835], cond[8836:8839] = _f64(sd[s + ".4.bias"]), _f64(sd[b + ".4.bias"])
+    cond[8832:8835], cond[8836:8839] = _f64(bs4), _f64(bb4)
+    return _f64(Ws0).t().contiguous(), _f64(Wb0).t().contiguous()
 
-    wc = torch.cat([W1[:, tdim:].t(), _f64(sd[s + ".0.weight"]).t(), _f64(sd[b + ".0.weight"]).t()], dim=1)
+
+def _a1d(sd, prefix):
+    return (sd[prefix + ".0.weight"], sd[prefix + ".2.weight"], sd[prefix + ".2.bias"], sd[prefix + ".4.weight"],
+            sd[prefix + ".4.bias"])
+
+
+def pack_flow_block(sd, i_or_prefix, tdim: int = None):
+    """FlowBlock (interpflow.py:46-82) -> dict(wc[cond,192], flow[PF_FLOW_BLOB], cond[PF_COND_BLOB],
+    logdet_const); logdet_const = sum(logs) + log|det W| (per point).  `i_or_prefix`: block index of a
+    PointInterpFlow state_dict, or the key prefix of a lone FlowBlock's state_dict ('' allowed)."""
+    if isinstance(i_or_prefix, int):
+        p = f"flow_blocks.{i_or_prefix}."
+        tdim = 1 if i_or_prefix % 2 == 0 else 2             # interpflow.py:55 (is_even = i % 2 == 0, :283)
+    else:
+        p = i_or_prefix
+    logs, W = _f64(sd[p + "actnorm.logs"]).reshape(3), _f64(sd[p + "permutate1.permutater.W"])
+    direct = sd[p + "permutate2.permutater.direct_idx"].tolist()
+    assert direct == [2, 1, 0], "the fused flow kernel implements the 'reverse' permutation (interpflow.py:53)"
+    flow, cond = identity_flow_blob(), zero_cond_blob()
+    set_actnorm(flow, logs, sd[p + "actnorm.bias"])
+    set_matrix(flow, W)
+    flow[28] = 1.0
+    w1c = set_coupling1(flow, *_a1d(sd, p + "coupling1.bias_net.layers"), tdim)
+    ws0, wb0 = set_injector(cond, _a1d(sd, p + "coupling2.scale_net.layers"), _a1d(sd, p + "coupling2.bias_net.layers"))
+    wc = torch.cat([w1c, ws0, wb0], dim=1)
     logdet_const = float(logs.sum() + torch.linalg.slogdet(W)[1])
     return dict(wc=wc.contiguous(), flow=flow, cond=cond, logdet_const=logdet_const)
 

@@ -1,0 +1,91 @@
+"""CPU: host-side logic of the drop-in modules (no kernel launches): state_dict layout, API surface,
+loud failure without CUDA, and that the C-ABI library exports every symbol include/puflow_b200.h declares."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "puflow_b200.h")).read()
+    declared = set(re.findall(r"PF_API\s+(?:const\s+char\s*\*|int)\s+(pf_\w+)\s*\(", hdr))
+    assert len(declared) >= 12, declared
+    lib = ctypes.CDLL(os.path.join(ROOT, "puflow_b200", "_lib", "libpuflow_b200.so"))
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+    from puflow_b200 import _native
+    assert set(_native.SIGNATURES) | {"pf_last_error"} == declared
+    assert lib.pf_abi_version() == _native.PF_ABI_VERSION
+
+
+def test_header_constants_match_binding():
+    hdr = open(os.path.join(ROOT, "include", "puflow_b200.h")).read()
+    from puflow_b200 import _native
+    for name in ("PF_COND_BLOB", "PF_FLOW_BLOB", "PF_INTERP_BLOB", "PF_ABI_VERSION"):
+        assert int(re.search(rf"#define {name} (\d+)", hdr).group(1)) == getattr(_native, name)
+
+
+def test_state_dict_layout_matches_checkpoint(state_dict):
+    from modules.discrete.interpflow import PointInterpFlow
+    net = PointInterpFlow(3)
+    own = net.state_dict()
+    assert len(own) == 408 and list(own.keys()) == list(state_dict.keys())
+    for k in own:
+        assert own[k].shape == state_dict[k].shape and own[k].dtype == state_dict[k].dtype, k
+    res = net.load_state_dict(state_dict)
+    assert not res.missing_keys and not res.unexpected_keys
+    net.set_to_initialized_state()
+    assert all(fb.actnorm.is_inited for fb in net.flow_blocks)
+    assert net.num_blocks == 6 and net.num_neighbors == 16 and net.interp.k == 8
+
+
+def test_no_cpu_fallback(state_dict):
+    from modules.discrete.interpflow import PointInterpFlow
+    from modules.flows.normalize import ActNorm
+    from modules.utils.patch import PatchHelper
+    from puflow_b200 import ops
+    from puflow_b200._native import PuflowError
+    net = PointInterpFlow(3)
+    net.load_state_dict(state_dict)
+    net.set_to_initialized_state()
+    x = torch.rand(2, 256, 3)
+    with pytest.raises(RuntimeError):
+        net(x)
+    with pytest.raises(RuntimeError):
+        ActNorm(3, dim=2)(x)
+    with pytest.raises(PuflowError):
+        ops.chamfer_nn(x, x)
+    with pytest.raises(PuflowError):
+        PatchHelper.remove_outliers(x, x, 4)
+
+
+def test_flow_layer_api_surface():
+    from modules.flows.coupling import AffineCouplingLayer, AffineInjectorLayer, AffineSpatialCouplingLayer
+    from modules.flows.normalize import ActNorm
+    from modules.flows.permutate import InvertibleConv1x1_1D, Permutation
+    from modules.discrete.interpflow import FlowBlock, LinearA1D
+    a = ActNorm(3, dim=2)
+    assert a.logs.shape == (1, 1, 3) and a.bias.shape == (1, 1, 3) and a.eps == 1e-6 and not a.is_inited
+    p = Permutation('reverse', 3, dim=2)
+    assert p.permutater.direct_idx.tolist() == [2, 1, 0] and p.permutater.inverse_idx.tolist() == [2, 1, 0]
+    assert Permutation('inv1x1', 3, dim=2).permutater.W.shape == (3, 3)
+    assert isinstance(Permutation('inv1x1', 3, dim=2).permutater, InvertibleConv1x1_1D)
+    fb = FlowBlock(idim=3, hdim=64, cdim=32, is_even=True)
+    keys = set(fb.state_dict().keys())
+    assert "coupling1.bias_net.layers.0.weight" in keys and "coupling2.scale_net.layers.4.bias" in keys
+    assert fb.coupling1.bias_net.layers[0].weight.shape == (64, 33)
+    assert isinstance(fb.coupling1, AffineSpatialCouplingLayer) and isinstance(fb.coupling2, AffineInjectorLayer)
+    assert issubclass(AffineSpatialCouplingLayer, AffineCouplingLayer)
+    assert LinearA1D(2, 64, 1, 128).layers[4].weight.abs().sum() == 0          # zero-initialised last layer
+
+
+def test_upsample_entry_point_signature():
+    import inspect
+    from modules.discrete import upsample
+    params = list(inspect.signature(upsample.upsampling).parameters)
+    assert params[:8] == ["data_paths", "target_path", "checkpoint_path", "up_ratio", "num_outlier", "num_patch",
+                          "num_upsampling", "seed"]
