@@ -51,21 +51,36 @@ def upsampling(data_paths: List[str], target_path: str, checkpoint_path: str, up
         _, file_name = os.path.split(path)
 
         pt_input = np.loadtxt(path, dtype=np.float32)
-        pt_input = torch.from_numpy(pt_input).unsqueeze(0).to(device)
-        pt_input = pt_input[:, torch.randperm(pt_input.shape[1])].contiguous()
+        pt_input = pt_input[torch.randperm(pt_input.shape[0]).numpy()]
+        pred = upsample_array(network, patch_helper, pt_input[None], up_ratio, num_outlier, num_upsampling, device)
+        np.savetxt(Path(target_path) / file_name, pred[0], fmt='%.6f')
 
-        if num_upsampling is None:  # the number of points after upsamling
-            NUM_UPSAMPLING_POINTS = pt_input.shape[1] * up_ratio + (num_outlier or 0)
-        else:
-            NUM_UPSAMPLING_POINTS = num_upsampling + (num_outlier or 0)
 
-        pred = patch_helper.upsample(network, pt_input, npoint=NUM_UPSAMPLING_POINTS, upratio=up_ratio, jitter=False)
+# -----------------------------------------------------------------------------------------
+@torch.no_grad()
+def upsample_array(network, patch_helper, clouds, up_ratio: int = 4, num_outlier: int = 24,
+                   num_upsampling: int = None, device=None, out: torch.Tensor = None):
+    """Host-buffer form of the per-file body of the reference's loop (upsample.py:42-56): clouds[B,N,3] fp32 in HOST
+    memory (numpy array or CPU tensor, pinned or not) -> upsampled clouds [B, N*up_ratio (or num_upsampling), 3] in
+    host memory (numpy; or written into the pinned CPU tensor `out`).  The host->device copy, the whole
+    PatchHelper.upsample + remove_outliers pipeline and the device->host copy run on the current stream; the call
+    returns after the result has landed in host memory."""
+    device = torch.device(device) if device is not None else next(network.parameters()).device
+    src = torch.from_numpy(clouds) if isinstance(clouds, np.ndarray) else clouds
+    if src.dim() != 3 or src.shape[2] != 3 or src.dtype != torch.float32:
+        raise ValueError(f"upsample_array: expected fp32 clouds[B,N,3], got {tuple(src.shape)} {src.dtype}")
+    pt_input = src.to(device, non_blocking=True).contiguous()
 
-        if num_outlier is not None and num_outlier > 0:
-            pred = PatchHelper.remove_outliers(pred, pt_input, num_outlier)
+    n_out = (pt_input.shape[1] * up_ratio if num_upsampling is None else num_upsampling) + (num_outlier or 0)
+    pred = patch_helper.upsample(network, pt_input, npoint=n_out, upratio=up_ratio, jitter=False)
+    if num_outlier is not None and num_outlier > 0:
+        pred = PatchHelper.remove_outliers(pred, pt_input, num_outlier)
 
-        pred = pred.squeeze().cpu().numpy()
-        np.savetxt(Path(target_path) / file_name, pred, fmt='%.6f')
+    if out is not None:
+        out.copy_(pred, non_blocking=True)
+        torch.cuda.current_stream(device).synchronize()
+        return out
+    return pred.cpu().numpy()
 
 
 # -----------------------------------------------------------------------------------------

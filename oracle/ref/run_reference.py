@@ -38,7 +38,7 @@ REPO = os.path.dirname(os.path.dirname(HERE))
 
 
 def _load_synth():
-    spec = importlib.util.spec_from_file_location("pf_synth", os.path.join(REPO, "oracle", "synth.py"))
+    spec = importlib.util.spec_from_file_location("pf_synth", os.path.join(REPO, "tools", "synth.py"))
     m = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(m)
     return m

@@ -2,7 +2,7 @@
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from oracle import synth
+from tools import synth
 from puflow_b200.engine import PUFlowEngine
 from puflow_b200 import ops
 
