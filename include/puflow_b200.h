@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 1
+#define PF_ABI_VERSION 2
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -87,6 +87,14 @@ PF_API int pf_linear(const float* A, int64_t lda, const float* W, const float* b
  * (G, C_out) in {(8,32), (16,64), (32,128)}; K in {8,16,32}; slope = LeakyReLU slope (0.05). */
 PF_API int pf_edgeconv(const float* pq, const int32_t* idx, const float* wd, const float* wo, float* out, int Bp, int N,
                 int K, int G, int C_out, float slope, void* stream);
+
+/* Tensor-core variant of pf_edgeconv for the compute-bound (G, C_out, K) = (32, 128, 16) blocks: the hidden-channel
+ * contractions run on tcgen05.mma (fp16 hi/lo split operands, 3 MMAs per product, fp32 accumulation in TMEM; results
+ * are fp32-class, tolerance in tests/test_gpu_kernels.py).  Same pq / idx / out as pf_edgeconv;  wtc: PF_EDGECONV_TC_BLOB
+ * bytes of pre-split fp16 weights in the tensor-core shared-memory layout (puflow_b200/packing.py pack_edgeconv_tc). */
+#define PF_EDGECONV_TC_BLOB 90112
+PF_API int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K, int G,
+                   int C_out, float slope, void* stream);
 
 /* ---- (3) flow stack ---------------------------------------------------------------------------------
  * FlowBlock.forward / inverse x6 (/root/reference/modules/discrete/interpflow.py:66-82,302-321):

@@ -27,6 +27,7 @@ SIGNATURES = {
     "pf_chamfer_nn": [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "pf_linear": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
     "pf_edgeconv": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
+    "pf_edgeconv_tc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
     "pf_flow_cond": [_vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
@@ -41,10 +42,11 @@ for _name, _args in SIGNATURES.items():
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 1
+PF_ABI_VERSION = 2
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
 PF_INTERP_BLOB = 46304
+PF_EDGECONV_TC_BLOB = 90112
 ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
 
 if lib.pf_abi_version() != PF_ABI_VERSION:

@@ -13,6 +13,7 @@ fixed sequence of puflow_b200 kernel launches on the current CUDA stream.
 (the drop-in PointInterpFlow) delegates to it.
 """
 import math
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -31,6 +32,9 @@ class PUFlowEngine:
         if self.device.type != "cuda":
             raise RuntimeError(f"PUFlowEngine needs a CUDA device, got {self.device} (no CPU fallback)")
         self.w = pack_state_dict(state_dict, self.device)
+        # tensor-core (tcgen05, split-fp16) EdgeConv for the compute-bound blocks; PUFLOW_EDGECONV=ffma selects the
+        # FP32 FFMA kernel everywhere (A/B comparison, tests)
+        self.use_tc = os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma"
 
     # ---- stages (each usable on its own; the drop-in module methods call these) -------------------
     def knn(self, xyz: torch.Tensor, K: int = K_MAIN):
@@ -41,6 +45,8 @@ class PUFlowEngine:
         f = self.w["feat"][i]
         _, g, Co = FEAT_CFG[i]
         pq = ops.linear(c, f["wpq"], f["bpq"])
+        if self.use_tc and "wtc" in f and idx.shape[-1] == K_MAIN:
+            return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05)
         return ops.edgeconv(pq, idx, f["wd"], f["wo"], Bp, N, g, Co, 0.05)
 
     def merge(self, i: int, c: torch.Tensor):

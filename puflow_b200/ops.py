@@ -158,6 +158,24 @@ def edgeconv(pq: torch.Tensor, idx: torch.Tensor, wd: torch.Tensor, wo: torch.Te
     return out
 
 
+def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int, Npts: int, G: int, C_out: int,
+                slope: float = 0.05):
+    """Tensor-core (tcgen05, split-fp16) variant of `edgeconv` for (G, C_out, K) = (32, 128, 16);
+    wtc: uint8[PF_EDGECONV_TC_BLOB] from packing.pack_edgeconv_tc."""
+    _chk(pq, "pq"), _chk(idx, "idx", torch.int32), _chk(wtc, "wtc", torch.uint8)
+    K = idx.shape[-1]
+    R = 4 * G + C_out
+    if pq.shape != (Bp * Npts, 2 * R) or idx.numel() != Bp * Npts * K:
+        raise ValueError(f"edgeconv_tc: pq {tuple(pq.shape)} / idx {tuple(idx.shape)} do not match Bp={Bp} N={Npts} R={R}")
+    if wtc.numel() != N.PF_EDGECONV_TC_BLOB:
+        raise ValueError("edgeconv_tc: packed weight blob has the wrong size")
+    out = torch.empty((Bp * Npts, C_out), dtype=torch.float32, device=pq.device)
+    with _dev(pq), _launch(f"edgeconv_tc_g{G}_c{C_out}_k{K}"):
+        N.check(lib.pf_edgeconv_tc(pq.data_ptr(), idx.data_ptr(), wtc.data_ptr(), out.data_ptr(), Bp, Npts, K, G, C_out,
+                                   float(slope), _stream()), "pf_edgeconv_tc")
+    return out
+
+
 # ---- (3) flow ------------------------------------------------------------------------------------
 def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
     """raw[nb, M, 192] -> sb[nb, M, 8] = (s0,s1,s2,b0,b1,b2,0,0): coupling2 scale/bias per input point."""

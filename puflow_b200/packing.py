@@ -74,6 +74,33 @@ def pack_edgeconv(sd, prefix: str, C: int, g: int, C_out: int, layers: int = 4):
     )
 
 
+def umma_kmajor_fp16(mat):
+    """[rows, Kt] float64 -> (hi, lo) uint8 byte strings in the K-major no-swizzle tensor-core operand layout of
+    csrc/tc.cuh: half index (r//8)*(Kt*8) + (k//8)*64 + (r%8)*8 + (k%8).  hi = fp16(fp32(w)), lo = fp16(fp32(w) - hi)."""
+    rows, Kt = mat.shape
+    assert rows % 8 == 0 and Kt % 16 == 0, (rows, Kt)
+    w32 = mat.to(torch.float32)
+    hi = w32.to(torch.float16)
+    lo = (w32 - hi.to(torch.float32)).to(torch.float16)
+
+    def lay(x):
+        return x.reshape(rows // 8, 8, Kt // 8, 8).permute(0, 2, 1, 3).contiguous().view(torch.uint8).reshape(-1)
+    return lay(hi), lay(lo)
+
+
+def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
+    """(wd, wo) of pack_edgeconv -> uint8[PF_EDGECONV_TC_BLOB] for pf_edgeconv_tc:
+    [W1 hi | W1 lo | W2 hi | W2 lo | W3 hi | W3 lo | Wo hi | Wo lo], W_l as [g out][g*l in], Wo as [C_out][layers*g]."""
+    parts, off = [], 0
+    for l in range(1, layers):
+        Wl = wd[off:off + g * l * g].reshape(g * l, g).t()           # [g out, g*l in]
+        off += g * l * g
+        parts.extend(umma_kmajor_fp16(Wl.double()))
+    parts.extend(umma_kmajor_fp16(wo.t().double()))                  # [C_out, layers*g]
+    blob = torch.cat(parts)
+    return blob
+
+
 def pack_interp(sd):
     """InterpolationModule (interpflow.py:85-186) -> dict(wpq[3,640], bpq[640], blob[PF_INTERP_BLOB])."""
     p = "interp.knn_context.distance_encoder.mlp"
@@ -216,6 +243,8 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
     flows, conds = [], []
     for i, (C, g, Co) in enumerate(FEAT_CFG):
         out["feat"].append(pack_edgeconv(sd, f"feat_convs.{i}", C, g, Co))
+        if (g, Co) == (32, 128):
+            out["feat"][-1]["wtc"] = pack_edgeconv_tc(out["feat"][-1]["wd"], out["feat"][-1]["wo"])
         out["merge"].append(dict(
             w1=_f64(sd[f"merge_convs.{i}.conv1.weight"]).t().contiguous(),
             b1=_f64(sd[f"merge_convs.{i}.conv1.bias"]),
@@ -230,6 +259,8 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
 
     def cast(o):
         if isinstance(o, torch.Tensor):
+            if o.dtype == torch.uint8:
+                return o.contiguous().to(device)
             return o.to(torch.float32).contiguous().to(device)
         if isinstance(o, dict):
             return {k: cast(v) for k, v in o.items()}
