@@ -17,8 +17,12 @@
 //   conv_out     D^T[128 ch x 128 edges] = Wo[128 x 128] . H^T  (M=128, N=128, K=128): transposed so that a
 //                thread owns one output channel and the max over the 16 neighbours is a register max; the Q_j
 //                gather and the output store are then coalesced across the warp.
-// Weights are pre-split and pre-laid-out by puflow_b200/packing.py (pack_edgeconv_tc) and arrive with one TMA
-// bulk copy per CTA.
+//                Wo (hi/lo) lives in TMEM as the A operand (tcgen05.mma with A from tensor memory), which frees
+//                64 KB of shared memory for the gather staging below.
+// Gathers never stall the math: the Q_j rows of layer l+1 (and P_i / Q_j / neighbour indices of the NEXT tile) are
+// fetched with cp.async into XOR-swizzled staging buffers while layer l computes.
+// Weights are pre-split and pre-laid-out by puflow_b200/packing.py (pack_edgeconv_tc): the dense-layer weights
+// arrive with one TMA bulk copy per CTA, Wo is written to TMEM once per CTA with tcgen05.st.
 #include "common.cuh"
 #include "puflow_b200.h"
 #include "tc.cuh"
@@ -36,48 +40,33 @@ constexpr int NT = 256;
 // W_l (l = 1..3): 32 rows x 32l halfs per part; hi part at wd_off(l), lo part at wd_off(l) + wd_part(l)
 __host__ __device__ constexpr uint32_t wd_part(int l) { return 2048u * l; }
 __host__ __device__ constexpr uint32_t wd_off(int l) { return 4096u * (l * (l - 1) / 2); }
-constexpr uint32_t WO_OFF = 24576, WO_PART = 32768;
-constexpr uint32_t W_BYTES = WO_OFF + 2 * WO_PART;                       // 90,112
-constexpr uint32_t A_OFF = W_BYTES, A_PART = 32768;                      // A[wg][hi|lo]
-constexpr uint32_t STQ_OFF = A_OFF + 4 * A_PART;                         // 221,184
-constexpr uint32_t STQ_PITCH = 36, STQ_WARP = 8 * STQ_PITCH * 4;         // 8 rows x 36 floats per warp
-constexpr uint32_t JROW_OFF = STQ_OFF + 8 * STQ_WARP;                    // 230,400
-constexpr uint32_t BAR_OFF = JROW_OFF + 2 * TM * 4;                      // 231,424
-constexpr uint32_t SMEM_BYTES = BAR_OFF + 64;                            // 231,488 <= 232,448
+constexpr uint32_t WD_BYTES = 24576;
+constexpr uint32_t WO_GLOBAL_OFF = WD_BYTES, WO_PART = 32768;            // blob: [Wd | Wo hi [128][64 words] | Wo lo]
+constexpr uint32_t A_OFF = WD_BYTES, A_PART = 32768;                     // A[wg][hi|lo]
+constexpr uint32_t QS_OFF = A_OFF + 4 * A_PART, QS_BUF = 16384;          // qs[wg][2]: 128 rows x 128 B, XOR-swizzled
+constexpr uint32_t PS_OFF = QS_OFF + 4 * QS_BUF, PS_BUF = 4096;          // ps[wg]: 8 points x 128 floats (dense P)
+constexpr uint32_t JB_OFF = PS_OFF + 2 * PS_BUF, JB_BUF = 256;           // jbuf[wg][2][128] uint16 (patch-local j)
+constexpr uint32_t BAR_OFF = JB_OFF + 4 * JB_BUF;
+constexpr uint32_t SMEM_BYTES = BAR_OFF + 64;                            // 230,464 <= 232,448
 constexpr uint32_t A_SBO = 128 * 16;                                     // Kt = 128 halfs
 
+// ---- tensor memory map (columns) ----
 constexpr uint32_t TM_COLS = 512;
 constexpr uint32_t TM_WG = 160, TM_OUT = 32;                             // per WG: dense D at +0 (32 cols), out D at +32 (128)
-
-__device__ __forceinline__ void issue_gemm(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t a_sbo,
-                                           uint32_t b_hi, uint32_t b_lo, uint32_t b_sbo, int ksteps, uint32_t idesc) {
-    // D = A_hi.B_hi + A_lo.B_hi + A_hi.B_lo
-    uint32_t acc = 0;
-#pragma unroll 1
-    for (int part = 0; part < 3; part++) {
-        const uint32_t a = (part == 1) ? a_lo : a_hi, b = (part == 2) ? b_lo : b_hi;
-#pragma unroll 1
-        for (int s = 0; s < ksteps; s++) {
-            tc::mma_f16(d_tmem, tc::smem_desc(a + 256u * s, a_sbo), tc::smem_desc(b + 256u * s, b_sbo), idesc, acc);
-            acc = 1;
-        }
-    }
-}
+constexpr uint32_t TM_WO_HI = 320, TM_WO_LO = 384;                       // Wo as A operand: 128 lanes x 64 cols each
 
 __global__ void __launch_bounds__(NT, 1)
     edgeconv_tc_kernel(const float* __restrict__ pq, const int32_t* __restrict__ idx, const uint8_t* __restrict__ wblob,
                        float* __restrict__ out, int N, int tiles_per_patch, long long total_tiles, float slope) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
-    float* stq_all = reinterpret_cast<float*>(smem + STQ_OFF);
-    int* jrow_all = reinterpret_cast<int*>(smem + JROW_OFF);
     uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
     uint64_t* mbar = wbar + 1;                                            // [2], one per WG
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_OFF + 32);
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5;
     const int wg = warp >> 2, wq = warp & 3;                              // warpgroup, TMEM lane quadrant
-    const int e = tid & 127;                                              // row of the tile this thread owns
+    const int e = tid & 127;                                              // tile row (edge) / output channel of this thread
 
     if (tid == 0) {
         mbar_init(wbar, 1);
@@ -90,48 +79,82 @@ __global__ void __launch_bounds__(NT, 1)
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t lane_sel = (uint32_t)(wq * 32) << 16;
     if (tid == 0) {
-        mbar_expect_tx(wbar, W_BYTES);
-        bulk_g2s_chunked(smem, wblob, W_BYTES, wbar);
+        mbar_expect_tx(wbar, WD_BYTES);
+        bulk_g2s_chunked(smem, wblob, WD_BYTES, wbar);
     }
+    if (wg == 0) {   // Wo -> TMEM: thread = lane = output channel, two fp16 per column
+#pragma unroll 1
+        for (int part = 0; part < 2; part++)
+#pragma unroll 1
+            for (int half = 0; half < 2; half++) {
+                const uint4* src = reinterpret_cast<const uint4*>(wblob + WO_GLOBAL_OFF + (size_t)part * WO_PART +
+                                                                  (size_t)e * 256 + half * 128);
+                uint32_t r[32];
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const uint4 v = __ldg(src + i);
+                    r[4 * i] = v.x, r[4 * i + 1] = v.y, r[4 * i + 2] = v.z, r[4 * i + 3] = v.w;
+                }
+                tc::st32(tmem_base + lane_sel + (part ? TM_WO_LO : TM_WO_HI) + 32 * half, r);
+            }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
 
     const uint32_t a_hi = sbase + A_OFF + (uint32_t)wg * 2 * A_PART, a_lo = a_hi + A_PART;
     uint8_t* a_hi_p = smem + A_OFF + (size_t)wg * 2 * A_PART;
     uint8_t* a_lo_p = a_hi_p + A_PART;
     const uint32_t a_row = (uint32_t)(e >> 3) * A_SBO + (uint32_t)(e & 7) * 16;   // byte offset of row e, chunk 0
-    float* stq = stq_all + (size_t)warp * (STQ_WARP / 4);
-    int* jrow = jrow_all + wg * TM;
+    const uint32_t qs_addr = sbase + QS_OFF + (uint32_t)wg * 2 * QS_BUF;
+    const uint8_t* qs_p = smem + QS_OFF + (size_t)wg * 2 * QS_BUF;
+    const uint32_t ps_addr = sbase + PS_OFF + (uint32_t)wg * PS_BUF;
+    const uint8_t* ps_p = smem + PS_OFF + (size_t)wg * PS_BUF;
+    uint16_t* jb = reinterpret_cast<uint16_t*>(smem + JB_OFF) + wg * 2 * TM;
     const uint32_t d_dense = tmem_base + (uint32_t)wg * TM_WG;
     const uint32_t d_out = d_dense + TM_OUT;
-    const uint32_t lane_sel = (uint32_t)(wq * 32) << 16;
-    uint32_t phase = 0;
-    bool weights_ready = false;
+    const uint32_t idesc_d = tc::idesc_f16(128, G), idesc_o = tc::idesc_f16(128, 128);
     const int bar_id = 1 + wg;
+    uint32_t phase = 0;
 
-    // Q_l[j_e][32 floats] for the 32 rows of this warp: coalesced 128-byte row reads staged through shared memory
-    auto gather_q = [&](int col, float (&q)[32]) {
+    // ---- staging helpers (cp.async; every thread of the WG issues its share) ----
+    // Q columns [col, col+32) of the 128 neighbour rows -> qs[buf]; row r chunk c at r*128 + ((c ^ (r & 7)) * 16)
+    auto stage_q = [&](const float* patch_pq, const uint16_t* jl, int col, int buf) {
+        const int c = e & 7;
 #pragma unroll
-        for (int pass = 0; pass < 4; pass++) {
-            __syncwarp();
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int rr = (lane >> 3) + 4 * h;                                   // row 0..7 of this pass
-                const int jr = jrow[wq * 32 + pass * 8 + rr];
-                const float4 v = __ldg(reinterpret_cast<const float4*>(pq + (size_t)jr * R2 + R + col) + (lane & 7));
-                *reinterpret_cast<float4*>(stq + rr * STQ_PITCH + (lane & 7) * 4) = v;
-            }
-            __syncwarp();
-            if ((lane >> 3) == pass) {
-                const float* src = stq + (lane & 7) * STQ_PITCH;
-#pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const float4 v = *reinterpret_cast<const float4*>(src + 4 * c);
-                    q[4 * c] = v.x, q[4 * c + 1] = v.y, q[4 * c + 2] = v.z, q[4 * c + 3] = v.w;
-                }
-            }
+        for (int it = 0; it < 8; it++) {
+            const int r = it * 16 + (e >> 3);
+            tc::cp_async16(qs_addr + buf * QS_BUF + r * 128 + ((c ^ (r & 7)) << 4),
+                           patch_pq + (size_t)jl[r] * R2 + R + col + c * 4);
         }
     };
-    // h[32] (fp32) -> fp16 hi/lo into K-slice l of this thread's row of the A operand
+    // dense P columns [0, 128) of the tile's 8 points -> ps (8 x 512 B)
+    auto stage_p = [&](const float* patch_pq, int p0) {
+#pragma unroll
+        for (int it = 0; it < 2; it++) {
+            const int i = it * 128 + e, pt = i >> 5, c16 = i & 31;
+            tc::cp_async16(ps_addr + pt * 512 + c16 * 16, patch_pq + (size_t)min(p0 + pt, N - 1) * R2 + c16 * 4);
+        }
+    };
+    auto read_q = [&](int buf, float (&q)[32]) {
+        const uint8_t* row = qs_p + buf * QS_BUF + e * 128;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const float4 v = *reinterpret_cast<const float4*>(row + ((c ^ (e & 7)) << 4));
+            q[4 * c] = v.x, q[4 * c + 1] = v.y, q[4 * c + 2] = v.z, q[4 * c + 3] = v.w;
+        }
+    };
+    auto add_p = [&](int l, float (&q)[32]) {
+        const uint8_t* row = ps_p + (e >> 4) * 512 + l * 128;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const float4 v = *reinterpret_cast<const float4*>(row + c * 16);
+            q[4 * c] += v.x, q[4 * c + 1] += v.y, q[4 * c + 2] += v.z, q[4 * c + 3] += v.w;
+        }
+    };
+    // h[32] (fp32) -> fp16 hi/lo into K-slice l of this thread's row of the activation operand
     auto store_slice = [&](int l, const float (&h)[32]) {
 #pragma unroll
         for (int c = 0; c < 4; c++) {
@@ -143,33 +166,84 @@ __global__ void __launch_bounds__(NT, 1)
             *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
     };
-
-    for (long long t = (long long)blockIdx.x * 2 + wg; t < total_tiles; t += (long long)gridDim.x * 2) {
-        const int patch = (int)(t / tiles_per_patch);
-        const int p0 = (int)(t % tiles_per_patch) * PT;
+    auto tile_coords = [&](long long t, int& patch, int& p0) {
+        patch = (int)(t / tiles_per_patch);
+        p0 = (int)(t % tiles_per_patch) * PT;
+    };
+    auto load_j = [&](int patch, int p0) {
         const int pi = min(p0 + (e >> 4), N - 1);
-        const int row_i = patch * N + pi;
-        {
-            int j = __ldg(idx + (size_t)row_i * KN + (e & 15));
-            j = min(max(j, 0), N - 1);
-            jrow[e] = patch * N + j;
-        }
-        tc::named_bar(bar_id, 128);
-
-        // ---- layer 0: pure gather ----
-        {
-            float q[32], p[32];
-            gather_q(0, q);
-            ldg_vec<32>(pq + (size_t)row_i * R2, p);
+        const int j = __ldg(idx + ((size_t)patch * N + pi) * KN + (e & 15));
+        return (uint16_t)min(max(j, 0), N - 1);
+    };
+    const uint64_t da_hi = tc::smem_desc(a_hi, A_SBO), da_lo = tc::smem_desc(a_lo, A_SBO);
+    // D[128 edges x 32] = H[:, 0:32l] . W_l^T   (3 split products; K-step s is 256 B = 16 descriptor units further)
+    auto issue_dense = [&](int l) {
+        const uint32_t wl = sbase + wd_off(l);
+        const uint64_t db_hi = tc::smem_desc(wl, 512u * l), db_lo = tc::smem_desc(wl + wd_part(l), 512u * l);
+        const int ks = 2 * l;
+        uint32_t acc = 0;
+#pragma unroll 1
+        for (int s = 0; s < ks; s++, acc = 1) tc::mma_f16(d_dense, da_hi + 16u * s, db_hi + 16u * s, idesc_d, acc);
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_lo + 16u * s, db_hi + 16u * s, idesc_d, 1);
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_lo + 16u * s, idesc_d, 1);
+    };
+    // D^T[128 ch x 128 edges] = Wo . H^T, Wo from TMEM (8 columns per K-step)
+    auto issue_out = [&]() {
+        const uint32_t wo_hi = tmem_base + TM_WO_HI, wo_lo = tmem_base + TM_WO_LO;
 #pragma unroll
-            for (int c = 0; c < 32; c++) q[c] = lrelu(p[c] + q[c], slope);
+        for (int s = 0; s < 8; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_hi + 16u * s, idesc_o, s > 0);
+#pragma unroll
+        for (int s = 0; s < 8; s++) tc::mma_f16_ts(d_out, wo_lo + 8u * s, da_hi + 16u * s, idesc_o, 1);
+#pragma unroll
+        for (int s = 0; s < 8; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_lo + 16u * s, idesc_o, 1);
+    };
+
+    const long long stride = (long long)gridDim.x * 2;
+    long long t = (long long)blockIdx.x * 2 + wg;
+    int tb = 0;
+    if (t < total_tiles) {   // prologue: indices, P and Q0 of the first tile
+        int patch, p0;
+        tile_coords(t, patch, p0);
+        jb[e] = load_j(patch, p0);
+        tc::named_bar(bar_id, 128);
+        const float* ppq = pq + (size_t)patch * N * R2;
+        stage_p(ppq, p0);
+        stage_q(ppq, jb, 0, 0);
+        tc::cp_async_commit();
+        tc::cp_async_wait<0>();
+        tc::named_bar(bar_id, 128);
+    }
+    tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
+
+    for (; t < total_tiles; t += stride, tb ^= 1) {
+        int patch, p0;
+        tile_coords(t, patch, p0);
+        const float* ppq = pq + (size_t)patch * N * R2;
+        const uint16_t* jl = jb + tb * TM;
+        const bool has_next = t + stride < total_tiles;
+        int patch_n = 0, p0_n = 0;
+        uint16_t j_next = 0;
+        if (has_next) {
+            tile_coords(t + stride, patch_n, p0_n);
+            j_next = load_j(patch_n, p0_n);
+        }
+        const float* ppq_n = pq + (size_t)patch_n * N * R2;
+
+        // ---- layer 0: h0 = lrelu(P0_i + Q0_j) ----
+        stage_q(ppq, jl, G, 1);
+        tc::cp_async_commit();
+        {
+            float q[32];
+            read_q(0, q);
+            add_p(0, q);
+#pragma unroll
+            for (int c = 0; c < 32; c++) q[c] = lrelu(q[c], slope);
             store_slice(0, q);
         }
+        tc::cp_async_wait<0>();
         tc::fence_async_smem();
-        if (!weights_ready) {
-            tc::mbar_wait_bounded(wbar, 0);
-            weights_ready = true;
-        }
         tc::fence_before_sync();
         tc::named_bar(bar_id, 128);
 
@@ -178,15 +252,18 @@ __global__ void __launch_bounds__(NT, 1)
         for (int l = 1; l < 4; l++) {
             if (e == 0) {
                 tc::fence_after_sync();
-                issue_gemm(d_dense, a_hi, a_lo, A_SBO, sbase + wd_off(l), sbase + wd_off(l) + wd_part(l),
-                           (uint32_t)(32 * l) * 16, 2 * l, tc::idesc_f16(128, G));
+                issue_dense(l);
                 tc::commit(mbar + wg);
             }
-            float q[32], p[32];
-            gather_q(l * G, q);
-            ldg_vec<32>(pq + (size_t)row_i * R2 + l * G, p);
-#pragma unroll
-            for (int c = 0; c < 32; c++) q[c] += p[c];
+            if (l < 3)
+                stage_q(ppq, jl, (l + 1) * G, (l + 1) & 1);
+            else if (has_next)
+                stage_q(ppq_n, jb + (tb ^ 1) * TM, 0, 0);                 // next tile's Q0
+            tc::cp_async_commit();
+            if (l == 1 && has_next) jb[(tb ^ 1) * TM + e] = j_next;       // published by this layer's closing barrier
+            float q[32];
+            read_q(l & 1, q);
+            add_p(l, q);
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
@@ -195,6 +272,7 @@ __global__ void __launch_bounds__(NT, 1)
 #pragma unroll
             for (int c = 0; c < 32; c++) acc[c] = lrelu(acc[c] + q[c], slope);
             store_slice(l, acc);
+            tc::cp_async_wait<0>();
             tc::fence_async_smem();
             tc::fence_before_sync();
             tc::named_bar(bar_id, 128);
@@ -203,43 +281,53 @@ __global__ void __launch_bounds__(NT, 1)
         // ---- conv_out (transposed) + max over the 16 neighbours ----
         if (e == 0) {
             tc::fence_after_sync();
-            issue_gemm(d_out, sbase + WO_OFF, sbase + WO_OFF + WO_PART, A_SBO, a_hi, a_lo, A_SBO, 8,
-                       tc::idesc_f16(128, 128));
+            issue_out();
             tc::commit(mbar + wg);
         }
+        if (has_next) stage_p(ppq_n, p0_n);
+        tc::cp_async_commit();
         {
             const int ch = e;                                             // output channel of this thread
-            const float* qcol = pq + R + 4 * G + ch;
+            const float* qcol = ppq + R + 4 * G + ch;
+            float qv[32];
+            auto load_qchunk = [&](int c) {
+#pragma unroll
+                for (int v8 = 0; v8 < 4; v8++) {
+                    const uint4 jj = *reinterpret_cast<const uint4*>(jl + 32 * c + 8 * v8);
+                    const uint32_t w[4] = {jj.x, jj.y, jj.z, jj.w};
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        qv[8 * v8 + 2 * u] = __ldg(qcol + (size_t)(w[u] & 0xffffu) * R2);
+                        qv[8 * v8 + 2 * u + 1] = __ldg(qcol + (size_t)(w[u] >> 16) * R2);
+                    }
+                }
+            };
+            load_qchunk(0);
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
-#pragma unroll 1
+#pragma unroll
             for (int c = 0; c < 4; c++) {                                 // 32 edges = 2 points per chunk
                 float acc[32];
                 tc::ld32(d_out + lane_sel + 32 * c, acc);
-                float qv[32];
-#pragma unroll
-                for (int u = 0; u < 32; u++) qv[u] = __ldg(qcol + (size_t)jrow[32 * c + u] * R2);
 #pragma unroll
                 for (int u = 0; u < 32; u++) acc[u] += qv[u];
+                if (c < 3) load_qchunk(c + 1);
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     float m = acc[16 * h];
 #pragma unroll
                     for (int u = 1; u < 16; u++) m = fmaxf(m, acc[16 * h + u]);
                     const int pp = p0 + 2 * c + h;
-                    if (pp < N) {
-                        const size_t row = (size_t)patch * N + pp;
-                        out[row * CO + ch] = m + __ldg(pq + row * R2 + 4 * G + ch);
-                    }
+                    if (pp < N) out[((size_t)patch * N + pp) * CO + ch] = m + __ldg(ppq + (size_t)pp * R2 + 4 * G + ch);
                 }
             }
         }
+        tc::cp_async_wait<0>();
         tc::fence_before_sync();
-        tc::named_bar(bar_id, 128);          // D, A and jrow of this WG are free for the next tile
+        tc::named_bar(bar_id, 128);          // D, H and jbuf[tb] are free; ps / qs[0] / jbuf[tb^1] hold the next tile
     }
 
-    if (!weights_ready) tc::mbar_wait_bounded(wbar, 0);   // never exit with the bulk copy in flight
     tc::fence_before_sync();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc(tmem_base, TM_COLS);
@@ -252,6 +340,7 @@ extern "C" int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* w
     PF_CHECK_ARG(pq && idx && wtc && out, "pf_edgeconv_tc: null pointer");
     PF_CHECK_ARG(Bp >= 0 && N > 0, "pf_edgeconv_tc: bad sizes Bp=%d N=%d", Bp, N);
     PF_CHECK_ARG((long long)Bp * N < 0x7fffffffLL, "pf_edgeconv_tc: Bp*N overflows int32");
+    PF_CHECK_ARG(N <= 65536, "pf_edgeconv_tc: N=%d > 65536 points per patch", N);
     PF_CHECK_ARG(K == KN && G_ == G && C_out == CO, "pf_edgeconv_tc: only (G, C_out, K) = (32, 128, 16), got (%d, %d, %d)",
                  G_, C_out, K);
     PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(pq) | reinterpret_cast<uintptr_t>(wtc) | reinterpret_cast<uintptr_t>(out)) &

@@ -90,13 +90,17 @@ def umma_kmajor_fp16(mat):
 
 def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
     """(wd, wo) of pack_edgeconv -> uint8[PF_EDGECONV_TC_BLOB] for pf_edgeconv_tc:
-    [W1 hi | W1 lo | W2 hi | W2 lo | W3 hi | W3 lo | Wo hi | Wo lo], W_l as [g out][g*l in], Wo as [C_out][layers*g]."""
+    [W1 hi | W1 lo | W2 hi | W2 lo | W3 hi | W3 lo | Wo hi | Wo lo]; W_l as [g out][g*l in] in the shared-memory
+    operand layout, Wo as plain row-major fp16 [C_out][layers*g] (it is copied to tensor memory, one row per lane)."""
     parts, off = [], 0
     for l in range(1, layers):
         Wl = wd[off:off + g * l * g].reshape(g * l, g).t()           # [g out, g*l in]
         off += g * l * g
         parts.extend(umma_kmajor_fp16(Wl.double()))
-    parts.extend(umma_kmajor_fp16(wo.t().double()))                  # [C_out, layers*g]
+    wo32 = wo.t().contiguous().to(torch.float32)                      # [C_out, layers*g]
+    wo_hi = wo32.to(torch.float16)
+    wo_lo = (wo32 - wo_hi.to(torch.float32)).to(torch.float16)
+    parts.extend([wo_hi.contiguous().view(torch.uint8).reshape(-1), wo_lo.contiguous().view(torch.uint8).reshape(-1)])
     blob = torch.cat(parts)
     return blob
 
