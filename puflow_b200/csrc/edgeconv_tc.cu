@@ -34,7 +34,7 @@ using namespace pf;
 constexpr int G = 32, CO = 128, KN = 16;
 constexpr int R = 4 * G + CO, R2 = 2 * R;      // 256, 512
 constexpr int TM = 128, PT = TM / KN;          // edges / points per tile
-constexpr int NT = 256;
+constexpr int NT = 320;                        // 2 epilogue warpgroups + one MMA-issuing warp per warpgroup
 
 // ---- shared memory map (bytes) ----
 // W_l (l = 1..3): 32 rows x 32l halfs per part; hi part at wd_off(l), lo part at wd_off(l) + wd_part(l)
@@ -55,23 +55,41 @@ constexpr uint32_t TM_COLS = 512;
 constexpr uint32_t TM_WG = 160, TM_OUT = 32;                             // per WG: dense D at +0 (32 cols), out D at +32 (128)
 constexpr uint32_t TM_WO_HI = 320, TM_WO_LO = 384;                       // Wo as A operand: 128 lanes x 64 cols each
 
+#ifdef PF_TC_TIMING
+__device__ long long g_tc_timing[64];
+#define TSTAMP(k)                                                          \
+    do {                                                                   \
+        if (blockIdx.x == 0 && tid == 0) {                                 \
+            long long now_ = clock64();                                    \
+            g_tc_timing[k] += now_ - tprev_;                               \
+            tprev_ = now_;                                                 \
+        }                                                                  \
+    } while (0)
+#else
+#define TSTAMP(k)
+#endif
+
 __global__ void __launch_bounds__(NT, 1)
     edgeconv_tc_kernel(const float* __restrict__ pq, const int32_t* __restrict__ idx, const uint8_t* __restrict__ wblob,
                        float* __restrict__ out, int N, int tiles_per_patch, long long total_tiles, float slope) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
-    uint64_t* mbar = wbar + 1;                                            // [2], one per WG
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_OFF + 32);
+    uint64_t* mbar = wbar + 1;                                            // [2] MMA done, one per WG
+    uint64_t* ready = wbar + 3;                                           // [2] operands ready, one per WG
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_OFF + 40);
 
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int wg = warp >> 2, wq = warp & 3;                              // warpgroup, TMEM lane quadrant
+    const bool is_mma_warp = warp >= 8;
+    const int wg = is_mma_warp ? warp - 8 : warp >> 2, wq = warp & 3;    // warpgroup, TMEM lane quadrant
     const int e = tid & 127;                                              // tile row (edge) / output channel of this thread
 
     if (tid == 0) {
         mbar_init(wbar, 1);
         mbar_init(mbar, 1);
         mbar_init(mbar + 1, 1);
+        mbar_init(ready, 1);
+        mbar_init(ready + 1, 1);
         mbar_fence_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, TM_COLS);
@@ -84,7 +102,7 @@ __global__ void __launch_bounds__(NT, 1)
         mbar_expect_tx(wbar, WD_BYTES);
         bulk_g2s_chunked(smem, wblob, WD_BYTES, wbar);
     }
-    if (wg == 0) {   // Wo -> TMEM: thread = lane = output channel, two fp16 per column
+    if (warp < 4) {   // Wo -> TMEM: thread = lane = output channel, two fp16 per column
 #pragma unroll 1
         for (int part = 0; part < 2; part++)
 #pragma unroll 1
@@ -167,8 +185,9 @@ __global__ void __launch_bounds__(NT, 1)
         }
     };
     auto tile_coords = [&](long long t, int& patch, int& p0) {
-        patch = (int)(t / tiles_per_patch);
-        p0 = (int)(t % tiles_per_patch) * PT;
+        const uint32_t tt = (uint32_t)t, tpp = (uint32_t)tiles_per_patch;
+        patch = (int)(tt / tpp);
+        p0 = (int)(tt - (uint32_t)patch * tpp) * PT;
     };
     auto load_j = [&](int patch, int p0) {
         const int pi = min(p0 + (e >> 4), N - 1);
@@ -202,6 +221,28 @@ __global__ void __launch_bounds__(NT, 1)
 
     const long long stride = (long long)gridDim.x * 2;
     long long t = (long long)blockIdx.x * 2 + wg;
+    if (is_mma_warp) {
+        // ---- MMA-issuing warp of warpgroup wg: one thread; waits for "operands ready", issues, commits ----
+        if ((tid & 31) == 0) {
+            tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
+            uint32_t rphase = 0;
+            for (; t < total_tiles; t += stride) {
+#pragma unroll 1
+                for (int l = 1; l < 4; l++) {
+                    tc::mbar_wait_bounded(ready + wg, rphase);
+                    rphase ^= 1;
+                    tc::fence_after_sync();
+                    issue_dense(l);
+                    tc::commit(mbar + wg);
+                }
+                tc::mbar_wait_bounded(ready + wg, rphase);
+                rphase ^= 1;
+                tc::fence_after_sync();
+                issue_out();
+                tc::commit(mbar + wg);
+            }
+        }
+    } else {
     int tb = 0;
     if (t < total_tiles) {   // prologue: indices, P and Q0 of the first tile
         int patch, p0;
@@ -217,9 +258,13 @@ __global__ void __launch_bounds__(NT, 1)
     }
     tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
 
+#ifdef PF_TC_TIMING
+    long long tprev_ = clock64();
+#endif
     for (; t < total_tiles; t += stride, tb ^= 1) {
         int patch, p0;
         tile_coords(t, patch, p0);
+        TSTAMP(0);
         const float* ppq = pq + (size_t)patch * N * R2;
         const uint16_t* jl = jb + tb * TM;
         const bool has_next = t + stride < total_tiles;
@@ -242,19 +287,18 @@ __global__ void __launch_bounds__(NT, 1)
             for (int c = 0; c < 32; c++) q[c] = lrelu(q[c], slope);
             store_slice(0, q);
         }
+        TSTAMP(1);
         tc::cp_async_wait<0>();
         tc::fence_async_smem();
         tc::fence_before_sync();
         tc::named_bar(bar_id, 128);
+        if (e == 0) mbar_arrive(ready + wg);
+        TSTAMP(2);
 
         // ---- layers 1..3 ----
 #pragma unroll 1
         for (int l = 1; l < 4; l++) {
-            if (e == 0) {
-                tc::fence_after_sync();
-                issue_dense(l);
-                tc::commit(mbar + wg);
-            }
+            TSTAMP(3);
             if (l < 3)
                 stage_q(ppq, jl, (l + 1) * G, (l + 1) & 1);
             else if (has_next)
@@ -264,33 +308,36 @@ __global__ void __launch_bounds__(NT, 1)
             float q[32];
             read_q(l & 1, q);
             add_p(l, q);
+            TSTAMP(4);
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
+            TSTAMP(5);
             float acc[32];
             tc::ld32(d_dense + lane_sel, acc);
+            TSTAMP(6);
 #pragma unroll
             for (int c = 0; c < 32; c++) acc[c] = lrelu(acc[c] + q[c], slope);
             store_slice(l, acc);
+            TSTAMP(7);
             tc::cp_async_wait<0>();
+            TSTAMP(8);
             tc::fence_async_smem();
             tc::fence_before_sync();
             tc::named_bar(bar_id, 128);
+            if (e == 0) mbar_arrive(ready + wg);
+            TSTAMP(9);
         }
 
         // ---- conv_out (transposed) + max over the 16 neighbours ----
-        if (e == 0) {
-            tc::fence_after_sync();
-            issue_out();
-            tc::commit(mbar + wg);
-        }
+        TSTAMP(10);
         if (has_next) stage_p(ppq_n, p0_n);
         tc::cp_async_commit();
         {
             const int ch = e;                                             // output channel of this thread
             const float* qcol = ppq + R + 4 * G + ch;
-            float qv[32];
-            auto load_qchunk = [&](int c) {
+            float qva[32], qvb[32];
+            auto load_qchunk = [&](int c, float (&qv)[32]) {
 #pragma unroll
                 for (int v8 = 0; v8 < 4; v8++) {
                     const uint4 jj = *reinterpret_cast<const uint4*>(jl + 32 * c + 8 * v8);
@@ -302,17 +349,22 @@ __global__ void __launch_bounds__(NT, 1)
                     }
                 }
             };
-            load_qchunk(0);
+            load_qchunk(0, qva);
+            load_qchunk(1, qvb);
+            TSTAMP(11);
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
+            TSTAMP(12);
 #pragma unroll
             for (int c = 0; c < 4; c++) {                                 // 32 edges = 2 points per chunk
                 float acc[32];
                 tc::ld32(d_out + lane_sel + 32 * c, acc);
 #pragma unroll
-                for (int u = 0; u < 32; u++) acc[u] += qv[u];
-                if (c < 3) load_qchunk(c + 1);
+                for (int u = 0; u < 32; u++) acc[u] += (c & 1) ? qvb[u] : qva[u];
+                if (c < 2) {
+                    if (c & 1) load_qchunk(c + 2, qvb); else load_qchunk(c + 2, qva);
+                }
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     float m = acc[16 * h];
@@ -323,10 +375,12 @@ __global__ void __launch_bounds__(NT, 1)
                 }
             }
         }
+        TSTAMP(13);
         tc::cp_async_wait<0>();
         tc::fence_before_sync();
         tc::named_bar(bar_id, 128);          // D, H and jbuf[tb] are free; ps / qs[0] / jbuf[tb^1] hold the next tile
     }
+    }   // epilogue warpgroups
 
     tc::fence_before_sync();
     __syncthreads();
@@ -334,6 +388,16 @@ __global__ void __launch_bounds__(NT, 1)
 }
 
 }  // namespace
+
+#ifdef PF_TC_TIMING
+extern "C" __attribute__((visibility("default"))) int pf_tc_timing(long long* host64) {
+    cudaDeviceSynchronize();
+    cudaError_t e = cudaMemcpyFromSymbol(host64, g_tc_timing, sizeof(long long) * 64);
+    long long z[64] = {0};
+    cudaMemcpyToSymbol(g_tc_timing, z, sizeof(z));
+    return (int)e;
+}
+#endif
 
 extern "C" int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K,
                               int G_, int C_out, float slope, void* stream) {

@@ -38,3 +38,18 @@ if Bp >= 1024:
         for _ in range(5): fn()
         e1.record(); torch.cuda.synchronize()
         print(f"{name}: {e0.elapsed_time(e1)/5:.3f} ms")
+import ctypes
+from puflow_b200 import _native
+if hasattr(_native.lib, "pf_tc_timing"):
+    buf = (ctypes.c_longlong * 64)()
+    _native.lib.pf_tc_timing(buf)           # reset
+    f = eng.w["feat"][3]; pq = ops.linear(c, f["wpq"], f["bpq"])
+    ops.edgeconv_tc(pq, idx, f["wtc"], Bp, 256, 32, 128, 0.05)
+    _native.lib.pf_tc_timing(buf)
+    ntile = Bp * 32 / (148 * 2)
+    names = ["tile top", "L0 epilogue", "L0 wait+bar", "Ll issue", "Ll readq/addp", "Ll mbar wait", "Ll tmem ld", "Ll epilogue",
+             "Ll cpasync wait", "Ll fence+bar", "out issue", "out qprefetch", "out mbar wait", "out epilogue"]
+    tot = sum(buf[:14])
+    for k, nm in enumerate(names):
+        print(f"  {nm:18s} {buf[k]/ntile:9.0f} cyc/tile  {100*buf[k]/tot:5.1f}%")
+    print(f"  total {tot/ntile:.0f} cyc/tile")
