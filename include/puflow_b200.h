@@ -137,10 +137,16 @@ PF_API int pf_interp(const float* xyz, const float* z, const int32_t* idx, int l
  * pf_fps replaces pointnet2_ops.furthest_point_sample (/root/reference/modules/utils/patch.py:102,156)
  * with the semantics of the reference's own modules/utils/fps.py:40-73: start at index 0, running
  * min squared distance initialised to 1e10, arg-max with the first index winning ties.
- *   xyz[B][n][3] -> idx[B][npoint] int32;  work: >= B*n floats of scratch.
+ *   xyz[B][n][3] -> idx[B][npoint] int32;  work: NULL (brute force) or pf_fps_work_floats(B, n) floats of scratch.
  * pf_knn_patch replaces knn_cuda.KNN(k)(ref, query) (patch.py:33,107): for each of the nq queries the
  * k nearest of the np points, ascending by (distance, index); idx[B][nq][k] int32.  k <= 1024. */
 PF_API int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
+/* Same result as pf_fps, bit for bit, by exact spatial pruning (grid-sorted buckets with bounding boxes; a round only
+ * touches buckets the new sample can change): one CTA per cloud, built for the merge FPS of a batch (8,216 of 40,960
+ * candidates per cloud, patch.py:156).  work: pf_fps_work_floats(B, n) floats of scratch (sorted copy of the clouds).
+ * pf_fps dispatches here when work != NULL and n >= 4096. */
+PF_API long long pf_fps_work_floats(int B, int n);
+PF_API int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
 
 #ifdef __cplusplus

@@ -15,6 +15,7 @@ WeightEstimationUnit exist for their parameters: their arithmetic is fused insid
 """
 from typing import List
 
+import os
 import torch
 import torch.nn as nn
 import torch.nn.functional as F  # noqa: F401  (kept for API familiarity)
@@ -261,7 +262,11 @@ class FeatureExtractUnit(nn.Module):
 
         def build():
             sd = {"u." + k: v.detach() for k, v in self.state_dict().items()}
-            return {k: to_dev(v, device) for k, v in packing.pack_edgeconv(sd, "u", C, g, Co, self.num_conv).items()}
+            w = packing.pack_edgeconv(sd, "u", C, g, Co, self.num_conv)
+            out = {k: to_dev(v, device) for k, v in w.items()}
+            if (g, Co, self.num_conv) == (32, 128, 4):
+                out["wtc"] = packing.pack_edgeconv_tc(w["wd"], w["wo"]).to(device)
+            return out
         return self._cache.get(tensors, device, build)
 
     def forward(self, x: Tensor, knn_idx: Tensor or None, is_pooling=True):
@@ -279,7 +284,10 @@ class FeatureExtractUnit(nn.Module):
             knn_idx = ops.knn_topk(x.contiguous().float(), x.contiguous().float(), self.k, return_dist=False)[1]
         w = self._packed(x.device)
         pq = ops.linear(x.reshape(B * N, C).contiguous().float(), w["wpq"], w["bpq"])
-        return ops.edgeconv(pq, _idx32(knn_idx), w["wd"], w["wo"], B, N, g, Co, 0.05).view(B, N, Co)
+        idx32 = _idx32(knn_idx)
+        if "wtc" in w and idx32.shape[-1] == 16 and os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma":
+            return ops.edgeconv_tc(pq, idx32, w["wtc"], B, N, g, Co, 0.05).view(B, N, Co)     # tcgen05 path
+        return ops.edgeconv(pq, idx32, w["wd"], w["wo"], B, N, g, Co, 0.05).view(B, N, Co)
 
 
 # -----------------------------------------------------------------------------------------

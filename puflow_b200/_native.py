@@ -33,12 +33,15 @@ SIGNATURES = {
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
     "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
+    "pf_fps_bucketed": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_knn_patch": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
 }
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)
     _fn.argtypes = _args
     _fn.restype = ctypes.c_int
+lib.pf_fps_work_floats.argtypes = [_i, _i]
+lib.pf_fps_work_floats.restype = ctypes.c_longlong
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 

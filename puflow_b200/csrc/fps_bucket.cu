@@ -1,0 +1,292 @@
+// Farthest point sampling with exact spatial pruning: one CTA per cloud, all clouds of a batch in one wave.
+//
+// Same semantics as pf_fps / the reference's own farthest_point_sampling
+// (/root/reference/modules/utils/fps.py:40-73; replaces pointnet2_ops.furthest_point_sample at
+// /root/reference/modules/utils/patch.py:102,156): start at index 0, running min squared distance initialised to
+// 1e10, arg-max with the lowest index winning ties.  Results are bit-identical to the brute-force kernel.
+//
+// The merge FPS of the x4 path draws 8,216 of 40,960 candidates: 8,216 dependent rounds that each touch every
+// point when done by brute force.  But a round only changes the running minimum of points closer to the new
+// sample than their current minimum, which after the first few rounds is a small neighbourhood.  So:
+//   setup   counting-sort the cloud into a 16^3 grid (Morton order), cut the sorted sequence into buckets of 32
+//           points, keep per bucket a bounding box and the maximum running-min distance (shared memory);
+//   round   every warp tests the boxes of the buckets it owns against the new sample and only updates buckets
+//           whose box is closer than their current maximum (exact: a skipped bucket cannot change);
+//           arg-max = max over bucket maxima, then a look inside the bucket(s) holding the maximum.
+// Running minima live in shared memory (164 KB for 40,960 points), sorted coordinates in an L2-resident scratch.
+// Two __syncthreads per round; no clusters, no cross-CTA traffic.
+#include "common.cuh"
+#include "puflow_b200.h"
+
+namespace {
+
+constexpr int FT = 1024, NW = FT / 32;
+constexpr int CELLS = 4096;                  // 16^3 grid
+constexpr float INIT_D = 1e10f;              // fps.py:53
+constexpr float SAFE = 0.9999f;              // box lower bound is scaled down: never above any computed distance
+
+__device__ __forceinline__ unsigned morton4(unsigned x, unsigned y, unsigned z) {
+    auto spread = [](unsigned v) { return (v & 1u) | ((v & 2u) << 2) | ((v & 4u) << 4) | ((v & 8u) << 6); };
+    return spread(x) | (spread(y) << 1) | (spread(z) << 2);
+}
+__device__ __forceinline__ float sqdist(float px, float py, float pz, float cx, float cy, float cz) {
+    const float dx = __fsub_rn(px, cx), dy = __fsub_rn(py, cy), dz = __fsub_rn(pz, cz);
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+struct Slot {
+    unsigned oidx;
+    float x, y, z;
+};
+
+// work (per cloud, npad = 32 * nb entries each): sx | sy | sz | oidx | md (md only used when !MD_SMEM)
+template <bool MD_SMEM>
+__global__ void __launch_bounds__(FT, 1)
+    fps_bucket_kernel(const float* __restrict__ xyz, int n, int npoint, int32_t* __restrict__ out, float* work, int nb,
+                      int KB) {
+    extern __shared__ __align__(16) float sm[];
+    const int npad = nb * 32;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int cloud = blockIdx.x;
+    const float* pb = xyz + (size_t)cloud * n * 3;
+    float* sx = work + (size_t)cloud * npad * 5;
+    float* sy = sx + npad;
+    float* sz = sy + npad;
+    unsigned* so = reinterpret_cast<unsigned*>(sz + npad);
+    float* mdg = sz + 2 * (size_t)npad;
+
+    // ---- shared memory carve-up ----
+    const int mdwords = MD_SMEM ? npad : CELLS;            // region 0: md (rounds) aliased by the histogram (setup)
+    float* md_s = sm;
+    int* hist = reinterpret_cast<int*>(sm);
+    float* bb = sm + (mdwords > CELLS ? mdwords : CELLS);  // [6][NW*KB]
+    const int nslot = NW * KB;
+    float* bmax = bb + 6 * nslot;
+    float* red = bmax + nslot;                             // [6*NW] setup reductions, then wmax[NW]
+    Slot* slots = reinterpret_cast<Slot*>(red + 6 * NW);   // [NW]
+    int* scan_tmp = reinterpret_cast<int*>(slots + NW);    // [NW]
+
+    // ---- setup 1: bounding box of the cloud ----
+    float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (int i = tid; i < n; i += FT)
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const float v = pb[(size_t)i * 3 + a];
+            lo[a] = fminf(lo[a], v), hi[a] = fmaxf(hi[a], v);
+        }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        lo[a] = warp_min(lo[a]), hi[a] = warp_max(hi[a]);
+        if (lane == 0) red[a * NW + w] = lo[a], red[(3 + a) * NW + w] = hi[a];
+    }
+    for (int i = tid; i < CELLS; i += FT) hist[i] = 0;
+    __syncthreads();
+    float inv[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        lo[a] = warp_min(red[a * NW + lane]);
+        hi[a] = warp_max(red[(3 + a) * NW + lane]);
+        const float ext = hi[a] - lo[a];
+        inv[a] = ext > 0.f ? 15.999f / ext : 0.f;
+    }
+    auto cell_of = [&](float x, float y, float z) {
+        const unsigned cx = min(15u, (unsigned)((x - lo[0]) * inv[0])), cy = min(15u, (unsigned)((y - lo[1]) * inv[1])),
+                       cz = min(15u, (unsigned)((z - lo[2]) * inv[2]));
+        return morton4(cx, cy, cz);
+    };
+    // ---- setup 2: histogram, exclusive scan, scatter (counting sort by cell) ----
+    for (int i = tid; i < n; i += FT) atomicAdd(&hist[cell_of(pb[(size_t)i * 3], pb[(size_t)i * 3 + 1], pb[(size_t)i * 3 + 2])], 1);
+    __syncthreads();
+    {
+        int v[4], s = 0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) v[u] = hist[4 * tid + u], s += v[u];
+        int incl = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) scan_tmp[w] = incl;
+        __syncthreads();
+        int wsum = scan_tmp[lane];
+        int wincl = wsum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, wincl, o);
+            if (lane >= o) wincl += t;
+        }
+        const int wbase = __shfl_sync(0xffffffffu, wincl - wsum, w);
+        int run = wbase + incl - s;
+#pragma unroll
+        for (int u = 0; u < 4; u++) hist[4 * tid + u] = run, run += v[u];
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += FT) {
+        const float x = pb[(size_t)i * 3], y = pb[(size_t)i * 3 + 1], z = pb[(size_t)i * 3 + 2];
+        const int pos = atomicAdd(&hist[cell_of(x, y, z)], 1);
+        sx[pos] = x, sy[pos] = y, sz[pos] = z, so[pos] = (unsigned)i;
+    }
+    for (int i = n + tid; i < npad; i += FT) sx[i] = pb[0], sy[i] = pb[1], sz[i] = pb[2], so[i] = 0x7fffffffu;
+    __syncthreads();
+    // ---- setup 3: bucket boxes, running minima ----
+    for (int k = 0; k < KB; k++) {
+        const int b = w + NW * k, slot = w * KB + k;
+        if (b < nb) {
+            const float x = sx[32 * b + lane], y = sy[32 * b + lane], z = sz[32 * b + lane];
+            const float v[6] = {warp_min(x), warp_min(y), warp_min(z), warp_max(x), warp_max(y), warp_max(z)};
+            if (lane == 0) {
+#pragma unroll
+                for (int a = 0; a < 6; a++) bb[a * nslot + slot] = v[a];
+                bmax[slot] = INIT_D;
+            }
+            const float m0 = (32 * b + lane < n) ? INIT_D : 0.f;
+            if (MD_SMEM) md_s[32 * b + lane] = m0; else mdg[32 * b + lane] = m0;
+        } else if (lane == 0) {
+#pragma unroll
+            for (int a = 0; a < 6; a++) bb[a * nslot + slot] = 0.f;
+            bmax[slot] = 0.f;
+        }
+    }
+    float cx = pb[0], cy = pb[1], cz = pb[2];
+    if (tid == 0) out[(size_t)cloud * npoint] = 0;
+    __syncthreads();
+
+    // ---- rounds ----
+    float* wmax = red;
+    for (int s = 0; s + 1 < npoint; s++) {
+        // (1) update the buckets whose box is closer to the new sample than their current maximum
+        float lane_max = 0.f;
+        for (int kbase = 0; kbase < KB; kbase += 32) {
+            const int k = kbase + lane, slot = w * KB + k;
+            bool act = false;
+            float bm = 0.f;
+            if (k < KB) {
+                bm = bmax[slot];
+                const float ex = fmaxf(fmaxf(bb[slot] - cx, cx - bb[3 * nslot + slot]), 0.f);
+                const float ey = fmaxf(fmaxf(bb[nslot + slot] - cy, cy - bb[4 * nslot + slot]), 0.f);
+                const float ez = fmaxf(fmaxf(bb[2 * nslot + slot] - cz, cz - bb[5 * nslot + slot]), 0.f);
+                act = (ex * ex + ey * ey + ez * ez) * SAFE < bm;
+            }
+            unsigned mask = __ballot_sync(0xffffffffu, act);
+            while (mask) {
+                int kk[4];
+                float px[4], py[4], pz[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    kk[u] = -1;
+                    if (mask) {
+                        kk[u] = __ffs(mask) - 1;
+                        mask &= mask - 1;
+                        const int p = 32 * (w + NW * (kbase + kk[u])) + lane;
+                        px[u] = sx[p], py[u] = sy[p], pz[u] = sz[p];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (kk[u] >= 0) {
+                        const int p = 32 * (w + NW * (kbase + kk[u])) + lane;
+                        const float d = sqdist(px[u], py[u], pz[u], cx, cy, cz);
+                        float m = MD_SMEM ? md_s[p] : mdg[p];
+                        if (d < m) {
+                            m = d;
+                            if (MD_SMEM) md_s[p] = d; else mdg[p] = d;
+                        }
+                        const float nm = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(m)));
+                        if (lane == kk[u]) bm = nm;
+                    }
+                }
+            }
+            if (k < KB) {
+                if (act) bmax[slot] = bm;
+                lane_max = fmaxf(lane_max, bm);
+            }
+        }
+        const float Mw = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(lane_max)));
+        if (lane == 0) wmax[w] = Mw;
+        __syncthreads();
+        // (2) global maximum; the warp(s) owning a bucket that attains it look inside
+        const float M = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(wmax[lane])));
+        unsigned best = 0xffffffffu;
+        float bx = 0.f, by = 0.f, bz = 0.f;
+        if (Mw == M) {
+            for (int kbase = 0; kbase < KB; kbase += 32) {
+                const int k = kbase + lane;
+                const bool hit = k < KB && (w + NW * k) < nb && bmax[w * KB + k] == M;
+                unsigned mask = __ballot_sync(0xffffffffu, hit);
+                while (mask) {
+                    const int kk = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const int p = 32 * (w + NW * (kbase + kk)) + lane;
+                    const float m = MD_SMEM ? md_s[p] : mdg[p];
+                    unsigned o = 0xffffffffu;
+                    float x = 0.f, y = 0.f, z = 0.f;
+                    if (m == M) o = so[p], x = sx[p], y = sy[p], z = sz[p];
+                    const unsigned omin = __reduce_min_sync(0xffffffffu, o);
+                    if (omin < best) {
+                        const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
+                        best = omin;
+                        bx = __shfl_sync(0xffffffffu, x, src), by = __shfl_sync(0xffffffffu, y, src),
+                        bz = __shfl_sync(0xffffffffu, z, src);
+                    }
+                }
+            }
+        }
+        if (lane == 0) slots[w].oidx = best, slots[w].x = bx, slots[w].y = by, slots[w].z = bz;
+        __syncthreads();
+        // (3) the lowest original index among the candidates wins (fps.py: torch.max returns the first maximum)
+        {
+            const unsigned o = slots[lane].oidx;
+            const unsigned omin = __reduce_min_sync(0xffffffffu, o);
+            const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
+            cx = slots[src].x, cy = slots[src].y, cz = slots[src].z;
+            if (tid == 0) out[(size_t)cloud * npoint + s + 1] = (int32_t)omin;
+        }
+    }
+}
+
+}  // namespace
+
+static int fps_bucket_geometry(int n, int* nb, int* KB, size_t* smem_md, size_t* smem_nomd) {
+    *nb = (n + 31) / 32;
+    *KB = (*nb + NW - 1) / NW;
+    const size_t meta = (size_t)(7 * NW * *KB + 6 * NW) * 4 + NW * sizeof(Slot) + NW * 4;
+    const size_t npad = (size_t)*nb * 32;
+    *smem_md = ((npad > (size_t)CELLS ? npad : (size_t)CELLS) * 4) + meta;
+    *smem_nomd = (size_t)CELLS * 4 + meta;
+    return 0;
+}
+
+extern "C" long long pf_fps_work_floats(int B, int n) {
+    if (B <= 0 || n <= 0) return 0;
+    return (long long)B * (((long long)n + 31) / 32 * 32) * 5;
+}
+
+extern "C" int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream) {
+    PF_CHECK_ARG(xyz && idx && work, "pf_fps_bucketed: null pointer (work must hold pf_fps_work_floats(B, n) floats)");
+    PF_CHECK_ARG(B >= 0 && n > 0 && npoint > 0, "pf_fps_bucketed: bad sizes B=%d n=%d npoint=%d", B, n, npoint);
+    if (B == 0) return 0;
+    int nb, KB;
+    size_t s_md, s_nomd;
+    fps_bucket_geometry(n, &nb, &KB, &s_md, &s_nomd);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (s_md <= 227 * 1024) {
+        if (int rc = pf_smem_optin(fps_bucket_kernel<true>, s_md)) return rc;
+        fps_bucket_kernel<true><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB);
+    } else {
+        PF_CHECK_ARG(s_nomd <= 227 * 1024, "pf_fps_bucketed: n=%d too large (bucket metadata exceeds shared memory)", n);
+        if (int rc = pf_smem_optin(fps_bucket_kernel<false>, s_nomd)) return rc;
+        fps_bucket_kernel<false><<<B, FT, s_nomd, st>>>(xyz, n, npoint, idx, work, nb, KB);
+    }
+    return pf_launch_status("fps_bucket_kernel");
+}

@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(ST) knn_patch_kernel(const float* __restrict__
 }  // namespace
 
 extern "C" int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream) {
-    (void)work;
+    if (work != nullptr && n >= 4096) return pf_fps_bucketed(xyz, B, n, npoint, idx, work, stream);
     PF_CHECK_ARG(xyz && idx, "pf_fps: null pointer");
     PF_CHECK_ARG(B >= 0 && n > 0 && npoint > 0, "pf_fps: bad sizes B=%d n=%d npoint=%d", B, n, npoint);
     PF_CHECK_ARG((long long)B * CS < 0x7fffffffLL, "pf_fps: B too large");

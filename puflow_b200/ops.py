@@ -233,13 +233,23 @@ def interp(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, pq: torch.Tens
 
 
 # ---- caller side ---------------------------------------------------------------------------------
-def fps(xyz: torch.Tensor, npoint: int):
-    """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0)."""
+def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
+    """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0).
+    mode: "brute" = cluster brute-force kernel, "bucket" = exact spatially pruned kernel (one CTA per cloud),
+    "auto" = bucket for n >= 4096.  Both give identical indices."""
     _chk(xyz, "xyz")
     B, n, _ = xyz.shape
     idx = torch.empty((B, npoint), dtype=torch.int32, device=xyz.device)
+    if B == 0:
+        return idx
+    use_bucket = mode == "bucket" or (mode == "auto" and n >= 4096)
     with _dev(xyz), _launch(f"fps_n{n}"):
-        N.check(lib.pf_fps(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), None, _stream()), "pf_fps")
+        if use_bucket:
+            work = torch.empty((lib.pf_fps_work_floats(B, n),), dtype=torch.float32, device=xyz.device)
+            N.check(lib.pf_fps_bucketed(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), work.data_ptr(), _stream()),
+                    "pf_fps_bucketed")
+        else:
+            N.check(lib.pf_fps(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), None, _stream()), "pf_fps")
     return idx
 
 

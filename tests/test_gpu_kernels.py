@@ -168,6 +168,43 @@ def test_edgeconv_other_k(ops, dev, packed, K):
     assert ok, err
 
 
+@pytest.mark.parametrize("blk,Bp,N", [(2, 3, 256), (3, 2, 256), (5, 1, 250), (4, 37, 64), (3, 600, 256)])
+def test_edgeconv_tensor_core(ops, dev, packed, blk, Bp, N):
+    """pf_edgeconv_tc (tcgen05, fp16 hi/lo split operands, 3 MMAs per product, fp32 accumulate).
+    STATED TOLERANCE: 2e-5 normwise per patch against the float64-accumulated emulation (the split drops the
+    lo*lo term, 2^-22 relative per product; measured 2e-7..1e-6), i.e. the same class as the FP32 FFMA kernel,
+    which is checked at 1e-5 above.  Also: bit-identical to itself on a sub-batch (tile scheduling independent)."""
+    from puflow_b200.packing import FEAT_CFG
+    C, g, Co = FEAT_CFG[blk]
+    gen = torch.Generator().manual_seed(blk * 1000 + N)
+    scale = [1.0, 1.0, 2.0, 5.0, 20.0, 90.0][blk]                       # input magnitudes seen with pu1k weights
+    x = torch.randn(Bp * N, C, generator=gen) * scale
+    p = synth.make_patches(Bp, N, seed=blk, shape="uniform")
+    idx = torch.from_numpy(po.knn(p, p, 16)[1]).int()
+    f = packed["feat"][blk]
+    pq = emulate.linear(x, f["wpq"], f["bpq"])
+    out = ops.edgeconv_tc(pq.to(dev), idx.to(dev), f["wtc"].to(dev), Bp, N, g, Co).cpu()
+    nref = min(Bp, 3)
+    ref = emulate.edgeconv(pq[:nref * N], idx[:nref], f["wd"], f["wo"], N, g, Co)
+    ok, err = parity.close_norm(out[:nref * N].view(nref, N, Co).numpy(), ref.view(nref, N, Co).numpy(), 2e-5)
+    assert ok, err
+    ffma = ops.edgeconv(pq.to(dev), idx.to(dev), f["wd"].to(dev), f["wo"].to(dev), Bp, N, g, Co).cpu()
+    ok, err = parity.close_norm(out.view(Bp, N, Co).numpy(), ffma.view(Bp, N, Co).numpy(), 2e-5)
+    assert ok, err
+    if Bp > 2:
+        sub = ops.edgeconv_tc(pq[N:3 * N].contiguous().to(dev), idx[1:3].contiguous().to(dev), f["wtc"].to(dev), 2, N, g,
+                              Co).cpu()
+        assert torch.equal(sub, out[N:3 * N])
+
+
+def test_edgeconv_tensor_core_rejects_other_shapes(ops, dev, packed):
+    f = packed["feat"][3]
+    pq = torch.zeros(256, 512, device=dev)
+    idx8 = torch.zeros(1, 256, 8, dtype=torch.int32, device=dev)
+    with pytest.raises(Exception):
+        ops.edgeconv_tc(pq, idx8, f["wtc"].to(dev), 1, 256, 32, 128)
+
+
 # ---- (3) flow --------------------------------------------------------------------------------------
 def _flow_inputs(packed, M, seed):
     gen = torch.Generator().manual_seed(seed)
@@ -255,6 +292,23 @@ def test_network_stages_match_reference(dev, state_dict, golden):
         assert parity.chamfer_distance(r["x"][b].cpu().numpy(), g["x"][b]) <= 1e-5
 
 
+def test_network_ffma_and_tensor_core_paths_agree(dev, state_dict, golden, monkeypatch):
+    """The FP32-FFMA EdgeConv path (PUFLOW_EDGECONV=ffma) and the default tensor-core path both meet the reference."""
+    from puflow_b200.engine import PUFlowEngine
+    g = golden("net_pu1k.npz")
+    xyz = torch.from_numpy(g["xyz"]).to(dev)
+    x_tc = PUFlowEngine(state_dict, dev).forward(xyz, 4)[0]
+    monkeypatch.setenv("PUFLOW_EDGECONV", "ffma")
+    eng = PUFlowEngine(state_dict, dev)
+    assert not eng.use_tc
+    x_ff = eng.forward(xyz, 4)[0]
+    for x in (x_tc, x_ff):
+        ok, err = parity.close_norm(x.cpu().numpy(), g["x"], 1e-4)
+        assert ok, err
+    ok, err = parity.close_norm(x_tc.cpu().numpy(), x_ff.cpu().numpy(), 1e-4)
+    assert ok, err
+
+
 def test_network_vs_oracle_one_cloud(dev, state_dict):
     """32 real kNN-256 patches of one synthetic 2,048-pt cloud (config 1 of BASELINE.json)."""
     from puflow_b200.engine import PUFlowEngine
@@ -310,6 +364,33 @@ def test_fps_bit_exact(ops, dev, B, n, npoint):
 def test_fps_lattice_ties(ops, dev):
     p = np.stack([synth.make_cloud(1000, s, "lattice") for s in (1, 2)])
     assert np.array_equal(ops.fps(torch.from_numpy(p).to(dev), 200).cpu().numpy(), po.fps(p, 200))
+
+
+@pytest.mark.parametrize("B,n,npoint,kind", [(3, 2048, 32, "uniform"), (2, 5000, 600, "surface"), (2, 40960, 1500, "surface"),
+                                             (1, 12345, 700, "uniform"), (4, 100, 100, "uniform"), (2, 1000, 400, "lattice"),
+                                             (1, 99840, 400, "surface"), (2, 3000, 3000, "dup")])
+def test_fps_bucketed_bit_exact(ops, dev, B, n, npoint, kind):
+    """The spatially pruned FPS (pf_fps_bucketed) returns exactly the indices of the brute-force definition
+    (oracle C restatement of modules/utils/fps.py:40-73), including exact ties (lattice, duplicated points) and
+    npoint == n, and agrees with the brute-force CUDA kernel."""
+    rng = np.random.default_rng(n + npoint)
+    if kind == "uniform":
+        p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    elif kind == "surface":
+        p = np.stack([synth.make_cloud(n, 11 + b, synth.SHAPES[b % 3]) for b in range(B)])
+    elif kind == "lattice":
+        p = np.stack([synth.make_cloud(n, 5 + b, "lattice") for b in range(B)])
+    else:   # every point appears three times
+        base = rng.uniform(-1, 1, (B, n // 3, 3)).astype(np.float32)
+        p = np.concatenate([base, base, base], 1)[:, rng.permutation(n // 3 * 3)]
+        n = p.shape[1]
+        npoint = min(npoint, n)
+    ref = po.fps(p, npoint)
+    x = torch.from_numpy(np.ascontiguousarray(p)).to(dev)
+    out = ops.fps(x, npoint, mode="bucket").cpu().numpy()
+    assert np.array_equal(out, ref)
+    if n <= 102400:
+        assert np.array_equal(ops.fps(x, npoint, mode="brute").cpu().numpy(), ref)
 
 
 @pytest.mark.parametrize("B,nq,np_,k", [(2, 32, 2048, 256), (1, 78, 5000, 256), (2, 5, 300, 256), (1, 3, 1000, 1000)])
