@@ -75,6 +75,12 @@ PF_API int pf_chamfer_nn(const float* a, int n, const float* b, int m, int B, fl
 PF_API int pf_linear(const float* A, int64_t lda, const float* W, const float* bias, float* out, int64_t ldo, int64_t M,
               int K, int N, int act, float slope, void* stream);
 
+/* Tensor-core variant of pf_linear for K in {16, 32, 64, 128}, N % 16 == 0 (tcgen05.mma on fp16 hi/lo split operands,
+ * fp32 accumulation: fp32-class result, tolerance in tests/test_gpu_kernels.py).  wtc: weights pre-split and laid out
+ * per 128-column chunk by puflow_b200/packing.py pack_linear_tc: ceil(N/128) chunks of 128*K*4 bytes. */
+PF_API int pf_linear_tc(const float* A, int64_t lda, const void* wtc, const float* bias, float* out, int64_t ldo, int64_t M,
+                 int K, int N, int act, float slope, void* stream);
+
 /* ---- (2) fused EdgeConv block -----------------------------------------------------------------
  * Replaces FeatureExtractUnit.forward (/root/reference/modules/discrete/interpflow.py:223-248):
  * neighbour gather + 4-layer dense block (1x1 conv + eval-BN + LeakyReLU + concat) + conv_out + max

@@ -26,6 +26,7 @@ SIGNATURES = {
     "pf_knn_topk": [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
     "pf_chamfer_nn": [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "pf_linear": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
+    "pf_linear_tc": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
     "pf_edgeconv": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
     "pf_edgeconv_tc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
     "pf_flow_cond": [_vp, _vp, _vp, _i64, _i, _vp],

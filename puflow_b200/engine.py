@@ -36,6 +36,12 @@ class PUFlowEngine:
         # FP32 FFMA kernel everywhere (A/B comparison, tests)
         self.use_tc = os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma"
 
+    def _linear(self, a, wd, name, bias=None, act=ACT_NONE):
+        """Per-point linear layer: tensor-core kernel when a packed blob exists (K in {16..128}), FFMA otherwise."""
+        if self.use_tc and (name + "_tc") in wd:
+            return ops.linear_tc(a, wd[name + "_tc"], wd[name].shape[1], bias, act)
+        return ops.linear(a, wd[name], bias, act)
+
     # ---- stages (each usable on its own; the drop-in module methods call these) -------------------
     def knn(self, xyz: torch.Tensor, K: int = K_MAIN):
         return ops.knn_topk(xyz, xyz, K, return_dist=False)[1]
@@ -44,7 +50,7 @@ class PUFlowEngine:
         """FeatureExtractUnit i on c[Bp*N, C_in] -> [Bp*N, C_out]."""
         f = self.w["feat"][i]
         _, g, Co = FEAT_CFG[i]
-        pq = ops.linear(c, f["wpq"], f["bpq"])
+        pq = self._linear(c, f, "wpq", f["bpq"])
         if self.use_tc and "wtc" in f and idx.shape[-1] == K_MAIN:
             return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05)
         return ops.edgeconv(pq, idx, f["wd"], f["wo"], Bp, N, g, Co, 0.05)
@@ -52,8 +58,8 @@ class PUFlowEngine:
     def merge(self, i: int, c: torch.Tensor):
         """FeatMergeUnit i (interpflow.py:251-258)."""
         m = self.w["merge"][i]
-        h = ops.linear(c, m["w1"], m["b1"], ACT_RELU)
-        return ops.linear(h, m["w2"])
+        h = self._linear(c, m, "w1", m["b1"], ACT_RELU)
+        return self._linear(h, m, "w2")
 
     def feat_extract(self, xyz: torch.Tensor, idx: torch.Tensor, return_feats: bool = False):
         """PointInterpFlow.feat_extract (interpflow.py:292-300) -> list of cs[i] [Bp, N, cond_i]."""
@@ -71,7 +77,10 @@ class PUFlowEngine:
         M = cs[0].shape[0] * cs[0].shape[1]
         raw = torch.empty((NUM_BLOCKS, M, 192), dtype=torch.float32, device=self.device)
         for i in range(NUM_BLOCKS):
-            ops.linear(cs[i].reshape(M, -1), self.w["wc"][i], None, ACT_NONE, out=raw[i])
+            if self.use_tc and self.w["wc_tc"][i] is not None:
+                ops.linear_tc(cs[i].reshape(M, -1), self.w["wc_tc"][i], 192, None, ACT_NONE, out=raw[i])
+            else:
+                ops.linear(cs[i].reshape(M, -1), self.w["wc"][i], None, ACT_NONE, out=raw[i])
         sb = ops.flow_cond(raw, self.w["cond"])
         return raw, sb
 

@@ -140,6 +140,28 @@ def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = N.ACT_NONE, s
     return out
 
 
+def linear_tc(a: torch.Tensor, wtc: torch.Tensor, N_out: int, bias=None, act: int = N.ACT_NONE, slope: float = 0.0,
+              out=None):
+    """Tensor-core (tcgen05, split-fp16) variant of `linear`: a[M,K] fp32, wtc = packing.pack_linear_tc(W[K,N]).
+    K in {16,32,64,128}, N % 16 == 0."""
+    if a.dim() != 2 or a.stride(1) != 1 or not a.is_cuda or a.dtype != torch.float32:
+        raise ValueError("linear_tc: a must be a 2-D fp32 CUDA tensor with unit inner stride")
+    _chk(wtc, "wtc", torch.uint8)
+    M, K = a.shape
+    if wtc.numel() != ((N_out + 127) // 128) * 128 * K * 4:
+        raise ValueError(f"linear_tc: packed weight blob does not match K={K}, N={N_out}")
+    if bias is not None:
+        _chk(bias, "bias")
+    if out is None:
+        out = torch.empty((M, N_out), dtype=torch.float32, device=a.device)
+    lda = a.stride(0) if M > 1 else max(K, a.stride(0))
+    with _dev(a), _launch(f"linear_tc_k{K}_n{N_out}"):
+        N.check(lib.pf_linear_tc(a.data_ptr(), lda, wtc.data_ptr(), bias.data_ptr() if bias is not None else None,
+                                 out.data_ptr(), out.stride(0), M, K, N_out, act, float(slope), _stream()),
+                "pf_linear_tc")
+    return out
+
+
 # ---- (2) EdgeConv --------------------------------------------------------------------------------
 def edgeconv(pq: torch.Tensor, idx: torch.Tensor, wd: torch.Tensor, wo: torch.Tensor, Bp: int, Npts: int, G: int,
              C_out: int, slope: float = 0.05):

@@ -105,6 +105,24 @@ def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
     return blob
 
 
+def linear_tc_ok(K: int, N: int) -> bool:
+    return K in (16, 32, 64, 128) and N % 16 == 0
+
+
+def pack_linear_tc(W):
+    """W[K, N] (k-major, float64/float32) -> uint8 blob for pf_linear_tc: per 128-column chunk
+    [hi (nc*K halfs) | lo (nc*K halfs) | pad to 128*K*4 bytes], each part in the csrc/tc.cuh operand layout."""
+    K, Nn = W.shape
+    assert linear_tc_ok(K, Nn), (K, Nn)
+    chunks = []
+    for n0 in range(0, Nn, 128):
+        nc = min(128, Nn - n0)
+        hi, lo = umma_kmajor_fp16(W[:, n0:n0 + nc].t().contiguous().double())
+        pad = torch.zeros(128 * K * 4 - hi.numel() - lo.numel(), dtype=torch.uint8)
+        chunks.extend([hi, lo, pad])
+    return torch.cat(chunks)
+
+
 def pack_interp(sd):
     """InterpolationModule (interpflow.py:85-186) -> dict(wpq[3,640], bpq[640], blob[PF_INTERP_BLOB])."""
     p = "interp.knn_context.distance_encoder.mlp"
@@ -243,18 +261,24 @@ def pack_flow_block(sd, i_or_prefix, tdim: int = None):
 
 def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
     """Whole model -> nested dict of contiguous fp32 tensors on `device`."""
-    out = {"feat": [], "merge": [], "wc": [], "logdet_const": 0.0}
+    out = {"feat": [], "merge": [], "wc": [], "wc_tc": [], "logdet_const": 0.0}
     flows, conds = [], []
     for i, (C, g, Co) in enumerate(FEAT_CFG):
         out["feat"].append(pack_edgeconv(sd, f"feat_convs.{i}", C, g, Co))
         if (g, Co) == (32, 128):
             out["feat"][-1]["wtc"] = pack_edgeconv_tc(out["feat"][-1]["wd"], out["feat"][-1]["wo"])
+        if linear_tc_ok(*out["feat"][-1]["wpq"].shape):
+            out["feat"][-1]["wpq_tc"] = pack_linear_tc(out["feat"][-1]["wpq"])
         out["merge"].append(dict(
             w1=_f64(sd[f"merge_convs.{i}.conv1.weight"]).t().contiguous(),
             b1=_f64(sd[f"merge_convs.{i}.conv1.bias"]),
             w2=_f64(sd[f"merge_convs.{i}.conv2.weight"]).t().contiguous()))
+        for nm in ("w1", "w2"):
+            if linear_tc_ok(*out["merge"][-1][nm].shape):
+                out["merge"][-1][nm + "_tc"] = pack_linear_tc(out["merge"][-1][nm])
         fb = pack_flow_block(sd, i)
         out["wc"].append(fb["wc"])
+        out["wc_tc"].append(pack_linear_tc(fb["wc"]) if linear_tc_ok(*fb["wc"].shape) else None)
         flows.append(fb["flow"]), conds.append(fb["cond"])
         out["logdet_const"] += fb["logdet_const"]
     out["flow"] = torch.stack(flows)

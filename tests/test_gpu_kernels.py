@@ -135,6 +135,33 @@ def test_linear(ops, dev, M, K, N, act):
     assert (out2.double() - ref2).abs().max() <= 2e-6 * max(1.0, ref2.abs().max())
 
 
+@pytest.mark.parametrize("M,K,N,act", [(1000, 128, 512, 0), (300, 64, 192, 2), (129, 32, 16, 1), (128, 16, 32, 0),
+                                       (5000, 128, 64, 1), (70000, 64, 128, 0)])
+def test_linear_tensor_core(ops, dev, M, K, N, act):
+    """pf_linear_tc (tcgen05, fp16 hi/lo split, 3 MMAs per product).  STATED TOLERANCE: 4e-6 * max|ref| against a
+    float64 reference (the FFMA pf_linear is checked at 2e-6 above): fp32-class."""
+    from puflow_b200.packing import pack_linear_tc
+    gen = torch.Generator().manual_seed(M + K + N)
+    a = torch.randn(M, K, generator=gen) * 3.0
+    w = torch.randn(K, N, generator=gen) / K ** 0.5
+    b = torch.randn(N, generator=gen)
+    wtc = pack_linear_tc(w).to(dev)
+    ref = a.double() @ w.double() + b.double()
+    if act == 1:
+        ref = torch.relu(ref)
+    elif act == 2:
+        ref = torch.nn.functional.leaky_relu(ref, 0.05)
+    out = ops.linear_tc(a.to(dev), wtc, N, b.to(dev), act, 0.05).cpu()
+    assert (out.double() - ref).abs().max() <= 4e-6 * max(1.0, ref.abs().max())
+    # row-strided input view, no bias, output into a row-strided slice
+    big = torch.randn(M, K + 8, generator=gen)
+    dst = torch.zeros(M, N + 16, device=dev)
+    ops.linear_tc(big.to(dev)[:, 4:4 + K], wtc, N, out=dst[:, 16:])
+    ref2 = big[:, 4:4 + K].double() @ w.double()
+    assert (dst[:, 16:].cpu().double() - ref2).abs().max() <= 4e-6 * max(1.0, ref2.abs().max())
+    assert float(dst[:, :16].abs().max()) == 0.0
+
+
 # ---- (2) EdgeConv ----------------------------------------------------------------------------------
 @pytest.mark.parametrize("blk,Bp,N", [(0, 3, 256), (1, 2, 256), (3, 3, 256), (5, 1, 250), (2, 300, 64)])
 def test_edgeconv_blocks_real_weights(ops, dev, packed, blk, Bp, N):

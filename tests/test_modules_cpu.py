@@ -12,13 +12,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "puflow_b200.h")).read()
-    declared = set(re.findall(r"PF_API\s+(?:const\s+char\s*\*|int)\s+(pf_\w+)\s*\(", hdr))
+    declared = set(re.findall(r"PF_API\s+(?:const\s+char\s*\*|int|long\s+long)\s+(pf_\w+)\s*\(", hdr))
     assert len(declared) >= 12, declared
     lib = ctypes.CDLL(os.path.join(ROOT, "puflow_b200", "_lib", "libpuflow_b200.so"))
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
     from puflow_b200 import _native
-    assert set(_native.SIGNATURES) | {"pf_last_error"} == declared
+    assert set(_native.SIGNATURES) | {"pf_last_error", "pf_fps_work_floats"} == declared
     assert lib.pf_abi_version() == _native.PF_ABI_VERSION
 
 
