@@ -139,6 +139,13 @@ PF_API int pf_flow_inv(const float* zin, const float* raw, const float* sb, cons
 PF_API int pf_interp(const float* xyz, const float* z, const int32_t* idx, int ldidx, const float* pq, const float* w,
               float* out, int Bp, int N, int R, void* stream);
 
+/* Tensor-core variant of pf_interp (tcgen05.mma on fp16 hi/lo split operands, fp32 accumulation; tolerance in
+ * tests/test_gpu_kernels.py).  Needs no pre-projected pq: coordinates enter the MMAs through a "geo" K-slice.
+ * wtc: PF_INTERP_TC_BLOB bytes from puflow_b200/packing.py pack_interp_tc. */
+#define PF_INTERP_TC_BLOB 205440
+PF_API int pf_interp_tc(const float* xyz, const float* z, const int32_t* idx, int ldidx, const void* wtc, float* out,
+                 int Bp, int N, int R, void* stream);
+
 /* ---- caller side ("next" rows of SURVEY.md section 8f) ---------------------------------------------------
  * pf_fps replaces pointnet2_ops.furthest_point_sample (/root/reference/modules/utils/patch.py:102,156)
  * with the semantics of the reference's own modules/utils/fps.py:40-73: start at index 0, running

@@ -33,6 +33,7 @@ SIGNATURES = {
     "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
     "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_bucketed": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_knn_patch": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
@@ -51,6 +52,7 @@ PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
 PF_INTERP_BLOB = 46304
 PF_EDGECONV_TC_BLOB = 90112
+PF_INTERP_TC_BLOB = 205440
 ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
 
 if lib.pf_abi_version() != PF_ABI_VERSION:

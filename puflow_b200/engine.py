@@ -105,6 +105,8 @@ class PUFlowEngine:
         if idx is None:
             idx = self.knn(xyz, K_INTERP)
         wi = self.w["interp"]
+        if self.use_tc:
+            return ops.interp_tc(xyz, z, idx, wi["tc"], upratio)
         pq = ops.linear(xyz.reshape(Bp * N, 3), wi["wpq"], wi["bpq"])
         return ops.interp(xyz, z, idx, pq, wi["blob"], upratio)
 

@@ -254,6 +254,22 @@ def interp(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, pq: torch.Tens
     return out
 
 
+def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, R: int):
+    """Tensor-core (tcgen05, split-fp16) variant of `interp`; needs no pq.  wtc: uint8[PF_INTERP_TC_BLOB] from
+    packing.pack_interp_tc."""
+    _chk(xyz, "xyz"), _chk(z, "z"), _chk(idx, "idx", torch.int32), _chk(wtc, "wtc", torch.uint8)
+    Bp, Npts, _ = xyz.shape
+    if z.shape != xyz.shape or wtc.numel() != N.PF_INTERP_TC_BLOB:
+        raise ValueError("interp_tc: bad shapes")
+    if idx.shape[:2] != (Bp, Npts) or idx.shape[2] < 8:
+        raise ValueError("interp_tc: idx must be [Bp, N, >=8]")
+    out = torch.empty((Bp, Npts * R, 3), dtype=torch.float32, device=xyz.device)
+    with _dev(xyz), _launch("interp_tc"):
+        N.check(lib.pf_interp_tc(xyz.data_ptr(), z.data_ptr(), idx.data_ptr(), idx.shape[2], wtc.data_ptr(),
+                                 out.data_ptr(), Bp, Npts, R, _stream()), "pf_interp_tc")
+    return out
+
+
 # ---- caller side ---------------------------------------------------------------------------------
 def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
     """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0).

@@ -171,6 +171,72 @@ def pack_interp(sd):
     return dict(wpq=torch.cat([P.t(), Q.t()], dim=1).contiguous(), bpq=bias, blob=blob)
 
 
+INTERP_TC_SMEM = 98944        # bytes of the pf_interp_tc blob that live in shared memory
+INTERP_TC_BLOB = INTERP_TC_SMEM + 2 * 128 * 104 * 4
+
+
+def pack_interp_tc(sd):
+    """InterpolationModule (interpflow.py:85-186) -> uint8[INTERP_TC_BLOB] for pf_interp_tc.
+
+    Every conv that reads raw coordinates takes them from a 16-wide "geo" K-slice of the activation operand,
+        geo = [x_i (3) | x_j (3) | x_j - x_i (3) | |x_i - x_j| | 1 | 0 x 5],
+    with the reference's UNFOLDED weights (no (W1-W3) x_i + (W2+W3) x_j cancellation) and the bias on the constant 1.
+    Shared-memory part (B operands, [N][K] K-major, fp16 hi then lo each):
+        Wd1g[64][16] | Wd2[64][64] | Wh_l[16][16+16l] (l = 0..7, K = geo | h_<l) | W3[64][128] | W6[32][64]
+        | fp32 bd3[64] | b3[64] | b6[32]
+    Tensor-memory part (A operand of the transposed composed layer, plain row-major fp16 [128][208], hi then lo):
+        M12g = [geo part | M2 (h, 128) | M1 (d2, 64)]."""
+    p = "interp.knn_context.distance_encoder.mlp"
+    Wd0, bd0 = _conv_bn(sd, p + ".0", p + ".1")            # [64,10] on [x_i, x_j, x_i-x_j, dist]
+    Wd3, bd3 = _conv_bn(sd, p + ".3", p + ".4")            # [64,64]
+    Wd6, bd6 = _conv_bn(sd, p + ".6")                      # [128,64]
+
+    def geo(Wxi, Wxj, Wdiff, wdist, bias):
+        g = torch.zeros(Wxi.shape[0], 16, dtype=torch.float64)
+        g[:, 0:3], g[:, 3:6], g[:, 6:9] = Wxi, Wxj, Wdiff
+        if wdist is not None:
+            g[:, 9] = wdist
+        g[:, 10] = bias
+        return g
+
+    parts = []
+
+    def add(mat):
+        parts.extend(umma_kmajor_fp16(mat))
+
+    add(geo(Wd0[:, 0:3], Wd0[:, 3:6], -Wd0[:, 6:9], Wd0[:, 9], bd0))          # d1 = lrelu(Wd1g . geo)
+    add(Wd3)                                                                     # d2 = lrelu(Wd3 . d1 + bd3)
+    fc = "interp.knn_context.feat_conv"
+    for l in range(8):
+        W, b = _conv_bn(sd, f"{fc}.convs.{l}.0", f"{fc}.convs.{l}.1")           # [16, 9 + 16 l]
+        add(torch.cat([geo(W[:, 0:3], W[:, 3:6], W[:, 6:9], None, b), W[:, 9:]], dim=1))
+    Wco, bco = _conv_bn(sd, f"{fc}.conv_out")                                   # [128, 9 + 128]
+    q = "interp.weight_unit.mlp"
+    W0, b0 = _conv_bn(sd, q + ".0", q + ".1")              # [128,256] on [dist feats 128 | context feats 128]
+    W3, b3 = _conv_bn(sd, q + ".3", q + ".4")              # [64,128]
+    W6, b6 = _conv_bn(sd, q + ".6")                        # [32,64]
+    add(W3)
+    w6 = torch.zeros(32, 64, dtype=torch.float64)
+    w6[:W6.shape[0]] = W6
+    add(w6)
+    b6p = torch.zeros(32, dtype=torch.float64)
+    b6p[:b6.shape[0]] = b6
+    parts.append(torch.cat([bd3, b3, b6p]).to(torch.float32).contiguous().view(torch.uint8).reshape(-1))
+    smem = torch.cat(parts)
+    assert smem.numel() == INTERP_TC_SMEM, smem.numel()
+
+    W0a, W0b = W0[:, :128], W0[:, 128:]
+    G = W0b @ Wco[:, 0:9]                                  # composed geo part [128, 9]
+    bm = W0a @ bd6 + W0b @ bco + b0
+    M12g = torch.cat([geo(G[:, 0:3], G[:, 3:6], G[:, 6:9], None, bm), W0b @ Wco[:, 9:], W0a @ Wd6], dim=1)   # [128, 208]
+    m32 = M12g.to(torch.float32)
+    hi = m32.to(torch.float16)
+    lo = (m32 - hi.to(torch.float32)).to(torch.float16)
+    blob = torch.cat([smem, hi.contiguous().view(torch.uint8).reshape(-1), lo.contiguous().view(torch.uint8).reshape(-1)])
+    assert blob.numel() == INTERP_TC_BLOB, blob.numel()
+    return blob
+
+
 def identity_flow_blob():
     """A flow-step blob whose every sub-layer is the identity (float64); the set_* helpers below fill in
     the sub-layers a caller wants.  Lets the single modules/flows layer classes run on the fused kernel."""
@@ -284,6 +350,7 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
     out["flow"] = torch.stack(flows)
     out["cond"] = torch.stack(conds)
     out["interp"] = pack_interp(sd)
+    out["interp"]["tc"] = pack_interp_tc(sd)
 
     def cast(o):
         if isinstance(o, torch.Tensor):

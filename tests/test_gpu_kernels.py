@@ -295,6 +295,28 @@ def test_interp(ops, dev, packed, Bp, N, R):
     assert ok, err
 
 
+@pytest.mark.parametrize("Bp,N,R", [(3, 256, 4), (2, 100, 2), (1, 256, 16), (40, 256, 4), (1, 64, 32)])
+def test_interp_tensor_core(ops, dev, packed, Bp, N, R):
+    """pf_interp_tc (tcgen05, fp16 hi/lo split, unfolded geo weights).  STATED TOLERANCE: 1e-4 normwise per patch
+    against the float64-accumulated emulation of the FFMA formulation (same bound as pf_interp above)."""
+    p = synth.make_patches(Bp, N, seed=N + R, shape="surface")
+    xyz = torch.from_numpy(p)
+    z = torch.randn(Bp, N, 3, generator=torch.Generator().manual_seed(R)) * 0.6
+    idx = torch.from_numpy(po.knn(p, p, 16)[1]).int()
+    wi = packed["interp"]
+    nref = min(Bp, 3)
+    pq = emulate.linear(xyz[:nref].reshape(-1, 3), wi["wpq"], wi["bpq"])
+    ref, _ = emulate.interp(xyz[:nref], z[:nref], idx[:nref], pq, wi["blob"], R)
+    out = ops.interp_tc(xyz.to(dev), z.to(dev), idx.to(dev), wi["tc"].to(dev), R).cpu()
+    ok, err = parity.close_norm(out[:nref].numpy(), ref.numpy(), 1e-4)
+    assert ok, err
+    assert torch.isfinite(out).all()
+    if Bp > 2:
+        sub = ops.interp_tc(xyz[1:3].contiguous().to(dev), z[1:3].contiguous().to(dev), idx[1:3].contiguous().to(dev),
+                            wi["tc"].to(dev), R).cpu()
+        assert torch.equal(sub, out[1:3])
+
+
 # ---- whole path ------------------------------------------------------------------------------------
 def test_network_stages_match_reference(dev, state_dict, golden):
     from puflow_b200.engine import PUFlowEngine
