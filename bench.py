@@ -180,8 +180,8 @@ def algorithmic_work(tag, Bc, npts):
     if tag.startswith("knn_topk_k"):
         K = int(tag.split("_k")[-1])
         return "hbm", M * (12 + 4 * K), "B"
-    if tag.startswith("edgeconv_g"):
-        g, c, k = (int(x[1:]) for x in tag.split("_")[1:4])
+    if tag.startswith("edgeconv_g") or tag.startswith("edgeconv_tc_g"):
+        g, c, k = (int(x[1:]) for x in tag.replace("edgeconv_tc_", "edgeconv_").split("_")[1:4])
         R = 4 * g + c
         return "tensor", 2.0 * (6 * g * g + 4 * g * c) * M * k, "FLOP"          # hidden-channel MACs of the dense block
     if tag.startswith("linear_k"):
@@ -193,7 +193,7 @@ def algorithmic_work(tag, Bc, npts):
         return "hbm", M * (24 + 4.0 * 6 * (64 + 8)), "B"
     if tag == "flow_inv":
         return "hbm", M * (UP * 24 + 4.0 * 6 * (64 + 8)), "B"
-    if tag == "interp":
+    if tag in ("interp", "interp_tc"):
         return "tensor", 2.0 * 81792 * 8 * M, "FLOP"
     if tag.startswith("fps_n"):
         n = int(tag[5:])

@@ -8,6 +8,7 @@ import torch.nn as nn
 from torch import Tensor
 
 from puflow_b200 import ops
+from puflow_b200.sharding import patch_sharded
 
 
 class KNN(object):
@@ -71,12 +72,18 @@ class PatchHelper(object):
 
     @staticmethod
     def _upsampling_patches(upsampler: nn.Module, patches: Tensor, upratio=None, **kwargs):
-        """reference patch.py:82-93 (name-mangled __upsampling_patches there)."""
+        """reference patch.py:82-93 (name-mangled __upsampling_patches there).
+        Addition: shard_patches=True under an initialised torch.distributed group splits the B * n_patch patches over
+        the ranks (every rank must hold the same `patches`) and all_gathers the generated points -- the config-3
+        single-large-cloud mode, puflow_b200/sharding.py; default False = the reference behaviour."""
         B, n_patch, k1, C = patches.shape
         patches = patches.reshape(B * n_patch, k1, C)
         patches, centroids, furthest_distance = PatchHelper.normalize_pc(patches)
 
-        predict_patches = upsampler.sample(patches, upratio=(upratio or 4), **kwargs)  # [B * n_patch, k2, C]
+        if kwargs.pop("shard_patches", False):
+            predict_patches = patch_sharded(lambda p: upsampler.sample(p, upratio=(upratio or 4), **kwargs), patches)
+        else:
+            predict_patches = upsampler.sample(patches, upratio=(upratio or 4), **kwargs)  # [B * n_patch, k2, C]
         predict_patches = torch.cat([predict_patches, patches], dim=1)
         predict_patches = predict_patches * furthest_distance + centroids
         return predict_patches.reshape(B, n_patch, -1, C)
