@@ -125,6 +125,19 @@ PF_API int pf_flow_fwd(const float* x, const float* raw, const float* sb, const 
 PF_API int pf_flow_inv(const float* zin, const float* raw, const float* sb, const float* flow_w, float* x, int64_t M,
                 int R, int nblocks, void* stream);
 
+/* Tensor-core variants (tcgen05.mma on fp16 hi/lo split operands for the 64x64 hidden layers of LinearA1D, fp32
+ * accumulation; everything else fp32 as above; tolerance in tests/test_gpu_kernels.py).  Same arguments, except the
+ * weights: cond_tc[nblocks][PF_COND_TC_BLOCK bytes], flow_tc[nblocks][PF_FLOW_TC_BLOCK bytes] from
+ * puflow_b200/packing.py (pack_cond_tc / pack_flow_tc).  nblocks <= 6 for pf_flow_fwd_tc / pf_flow_inv_tc.
+ * raw, sb and the blobs must be 32-byte aligned. */
+#define PF_COND_TC_BLOCK 35360
+#define PF_FLOW_TC_BLOCK 17920
+PF_API int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, void* stream);
+PF_API int pf_flow_fwd_tc(const float* x, const float* raw, const float* sb, const void* flow_tc, float* z, float* ssum,
+                   int64_t M, int nblocks, void* stream);
+PF_API int pf_flow_inv_tc(const float* zin, const float* raw, const float* sb, const void* flow_tc, float* x, int64_t M,
+                   int R, int nblocks, void* stream);
+
 /* ---- (4) latent interpolation -------------------------------------------------------------------------
  * Replaces InterpolationModule.forward (/root/reference/modules/discrete/interpflow.py:162-186) with
  * KnnContextEncoder (:123-134), DistanceEncoder (:85-120) and WeightEstimationUnit (:137-159) fused:

@@ -32,6 +32,9 @@ SIGNATURES = {
     "pf_flow_cond": [_vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
+    "pf_flow_cond_tc": [_vp, _vp, _vp, _i64, _i, _vp],
+    "pf_flow_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
+    "pf_flow_inv_tc": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
     "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
     "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
@@ -50,6 +53,8 @@ lib.pf_last_error.restype = ctypes.c_char_p
 PF_ABI_VERSION = 2
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
+PF_COND_TC_BLOCK = 35360
+PF_FLOW_TC_BLOCK = 17920
 PF_INTERP_BLOB = 46304
 PF_EDGECONV_TC_BLOB = 90112
 PF_INTERP_TC_BLOB = 205440

@@ -1,0 +1,364 @@
+// Glow-style flow stack on the 5th-gen tensor cores: same contract as flow.cu (pf_flow_fwd / pf_flow_inv /
+// pf_flow_cond; replaces FlowBlock.forward / inverse and PointInterpFlow.f / g,
+// /root/reference/modules/discrete/interpflow.py:66-82,302-321; LinearA1D :22-43; coupling.py:55-58,82-85,108-151).
+//
+// ncu on the FFMA kernels (profiles/r01_ncu_v3_tc.md): FP32 FMA pipe 40-42 % busy, DRAM 3-11 %: they are bound by the
+// 64x64 hidden layer of LinearA1D (4,096 of the ~4,500 FMAs per point per block).  Here that layer runs as
+// tcgen05.mma.kind::f16 on fp16 hi/lo split operands (3 MMAs per product, fp32 accumulation in TMEM: fp32-class
+// result, tolerance stated in tests/test_gpu_kernels.py), everything else stays per-thread fp32 with the same
+// operation order as flow.cu.
+//
+// A warpgroup (128 threads) owns a 128-point tile: thread = point = TMEM lane, the point's 3 coordinates stay in
+// registers through all blocks.  Per block: layer 0 (conditioning part from `raw`, one 256-bit load per 8 channels,
+// + W1h . h1) -> LeakyReLU -> fp16 hi/lo -> this thread's row of the A operand in shared memory; one thread issues
+// 12 MMAs (M=128, N=64, K=64, x3 split terms); tcgen05.ld of the thread's 64 accumulators -> +b2, LeakyReLU, the
+// 64 -> (3 - tdim) output layer as per-thread FMAs.  NWG warpgroups per CTA work on independent tiles, so one
+// group's MMA / TMEM latency is covered by the others' CUDA-core work.  W2 (hi/lo) of all blocks + the small fp32
+// parameters arrive with one TMA bulk copy per (persistent) CTA.
+#include "common.cuh"
+#include "puflow_b200.h"
+#include "tc.cuh"
+
+namespace {
+
+using namespace pf;
+
+constexpr int H = 64, TP = 128;
+constexpr float SLOPE = 0.01f;                 // nn.LeakyReLU() default (interpflow.py:34,36)
+constexpr int MAXB = 8;
+constexpr uint32_t W_PART = H * H * 2;         // one 64x64 fp16 operand
+constexpr uint32_t A_PART = TP * H * 2, A_WG = 2 * A_PART;     // A[hi|lo] of one warpgroup: 128 rows x 64 halfs each
+constexpr uint32_t A_SBO = H * 16;             // 8-row groups are K*16 bytes apart (tc.cuh layout)
+
+__device__ __forceinline__ void ldg256(const float* p, float (&v)[8]) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+}
+
+// Per-warpgroup state of the "64 -> 64 hidden layer on a 128-row tile" building block.
+struct Wg {
+    uint8_t* a_row_hi;      // this thread's row of the hi operand (chunk 0); lo is A_PART further; chunk c at + c * 128
+    uint32_t a_hi;          // shared-memory address of the hi operand
+    uint32_t d_tmem;        // accumulator columns of this warpgroup
+    uint32_t lane_sel;      // TMEM lane quadrant of this warp
+    uint64_t* mbar;         // MMA-done barrier of this warpgroup
+    uint32_t phase;
+    int bar_id, e;
+};
+
+// 8 activations (already through LeakyReLU) -> chunk c (K = 8c .. 8c+7) of this thread's operand row
+__device__ __forceinline__ void store_chunk(const Wg& g, int c, const float (&h)[8]) {
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
+    *reinterpret_cast<uint4*>(g.a_row_hi + c * 128) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(g.a_row_hi + A_PART + c * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+// acc[64] = A[row of this thread] . W^T, W (hi at w_addr, lo W_PART further) in the tc.cuh operand layout.
+// All 128 threads of the warpgroup call this after their store_chunk()s.
+__device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[64]) {
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    tc::named_bar(g.bar_id, 128);        // operand rows written; previous accumulators read by everyone
+    if (g.e == 0) {
+        tc::fence_after_sync();
+        const uint32_t idesc = tc::idesc_f16(128, H);
+        const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
+        const uint64_t db_hi = tc::smem_desc(w_addr, H * 16), db_lo = tc::smem_desc(w_addr + W_PART, H * 16);
+#pragma unroll
+        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, s > 0);
+#pragma unroll
+        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, 1);
+#pragma unroll
+        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+        tc::commit(g.mbar);
+    }
+    tc::mbar_wait_bounded(g.mbar, g.phase);
+    g.phase ^= 1;
+    tc::fence_after_sync();
+    float lo32[32], hi32[32];
+    tc::ld32(g.d_tmem + g.lane_sel, lo32);
+    tc::ld32(g.d_tmem + g.lane_sel + 32, hi32);
+#pragma unroll
+    for (int i = 0; i < 32; i++) acc[i] = lo32[i], acc[32 + i] = hi32[i];
+}
+
+__device__ __forceinline__ void wg_init(Wg& g, uint8_t* smem, uint32_t a_off, uint64_t* mbars, uint32_t tmem_base,
+                                        int tid) {
+    const int warp = tid >> 5, wg = warp >> 2;
+    g.e = tid & 127;
+    uint8_t* a = smem + a_off + (size_t)wg * A_WG;
+    g.a_hi = smem_u32(a);
+    g.a_row_hi = a + (uint32_t)(g.e >> 3) * A_SBO + (uint32_t)(g.e & 7) * 16;
+    g.d_tmem = tmem_base + (uint32_t)wg * H;
+    g.lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    g.mbar = mbars + wg;
+    g.phase = 0;
+    g.bar_id = 1 + wg;
+}
+
+// ---- flow forward / inverse --------------------------------------------------------------------------------
+// tc blob per block (PF_FLOW_TC_BLOCK bytes): W2 hi [64 out][64 in] | W2 lo | the first 384 floats of the fp32 flow
+// blob (flow.cu header: actnorm, W, Winv, tdim, reverse, w1h, b2, w4, b4)
+constexpr int NWG = 3, NT = NWG * 128;
+constexpr uint32_t FBLK = PF_FLOW_TC_BLOCK;
+
+template <bool INVERSE>
+__global__ void __launch_bounds__(NT, 1)
+    flow_tc_kernel(const float* __restrict__ xin, const float* __restrict__ raw, const float* __restrict__ sb,
+                   const uint8_t* __restrict__ wtc, float* __restrict__ xout, float* __restrict__ ssum, int64_t M,
+                   int R, int nblocks) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t w_bytes = (uint32_t)nblocks * FBLK;
+    const uint32_t a_off = (w_bytes + 127u) & ~127u;
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off + NWG * A_WG);
+    uint64_t* mbars = wbar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbars + NWG);
+
+    const int tid = threadIdx.x, warp = tid >> 5, wg = warp >> 2;
+    if (tid == 0) {
+        mbar_init(wbar, 1);
+        for (int i = 0; i < NWG; i++) mbar_init(mbars + i, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    if (tid == 0) {
+        mbar_expect_tx(wbar, w_bytes);
+        bulk_g2s_chunked(smem, wtc, w_bytes, wbar);
+    }
+    Wg g;
+    wg_init(g, smem, a_off, mbars, *tmem_slot, tid);
+    const uint32_t sbase = smem_u32(smem);
+    const int64_t rows = INVERSE ? M * R : M;
+    const int64_t ntiles = (rows + TP - 1) / TP;
+    tc::mbar_wait_bounded(wbar, 0);
+
+    for (int64_t t = (int64_t)blockIdx.x * NWG + wg; t < ntiles; t += (int64_t)gridDim.x * NWG) {
+        const int64_t r = t * TP + g.e;
+        const int64_t row = min(r, rows - 1);
+        const int64_t m = INVERSE ? row / R : row;             // input point that conditions this row
+        float x0, x1, x2, ss = 0.f;
+        {
+            const float* s = xin + (size_t)row * 3;
+            x0 = s[0], x1 = s[1], x2 = s[2];
+        }
+#pragma unroll 1
+        for (int it = 0; it < nblocks; it++) {
+            const int blk = INVERSE ? nblocks - 1 - it : it;
+            const float* fw = reinterpret_cast<const float*>(smem + (size_t)blk * FBLK + 2 * W_PART);
+            const int tdim = (int)fw[27];
+            const bool rev = fw[28] != 0.f;
+            const float* rawrow = raw + ((size_t)blk * M + m) * 192;
+            const float4 v0 = __ldg(reinterpret_cast<const float4*>(sb + ((size_t)blk * M + m) * 8));
+            const float4 v1 = __ldg(reinterpret_cast<const float4*>(sb + ((size_t)blk * M + m) * 8) + 1);
+            const float s0 = v0.x, s1 = v0.y, s2 = v0.z, b0 = v0.w, b1 = v1.x, b2 = v1.y;
+            if (!INVERSE) {
+                // ActNorm.forward: x * exp(logs) + bias ; inv1x1.forward: z_i = sum_j W[i][j] x_j
+                const float a0 = fmaf(x0, fw[0], fw[3]), a1 = fmaf(x1, fw[1], fw[4]), a2 = fmaf(x2, fw[2], fw[5]);
+                x0 = fw[9] * a0 + fw[10] * a1 + fw[11] * a2;
+                x1 = fw[12] * a0 + fw[13] * a1 + fw[14] * a2;
+                x2 = fw[15] * a0 + fw[16] * a1 + fw[17] * a2;
+            } else {
+                // coupling2.inverse: z * exp(s) + b ; permutate2.inverse: reverse
+                const float a0 = fmaf(x0, expf(s0), b0), a1 = fmaf(x1, expf(s1), b1), a2 = fmaf(x2, expf(s2), b2);
+                x0 = rev ? a2 : a0, x1 = a1, x2 = rev ? a0 : a2;
+            }
+            // layer 0: a1 = lrelu(u1 + W1h . h1)   (W1h rows beyond tdim are zero)
+            const float h1b = (tdim == 2) ? x1 : 0.f;
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                float u[8], h[8];
+                ldg256(rawrow + 8 * c, u);
+                const float4 wa0 = *reinterpret_cast<const float4*>(fw + 32 + 8 * c);
+                const float4 wa1 = *reinterpret_cast<const float4*>(fw + 32 + 8 * c + 4);
+                const float4 wb0 = *reinterpret_cast<const float4*>(fw + 96 + 8 * c);
+                const float4 wb1 = *reinterpret_cast<const float4*>(fw + 96 + 8 * c + 4);
+                const float wa[8] = {wa0.x, wa0.y, wa0.z, wa0.w, wa1.x, wa1.y, wa1.z, wa1.w};
+                const float wb[8] = {wb0.x, wb0.y, wb0.z, wb0.w, wb1.x, wb1.y, wb1.z, wb1.w};
+#pragma unroll
+                for (int k = 0; k < 8; k++) h[k] = lrelu(fmaf(wb[k], h1b, fmaf(wa[k], x0, u[k])), SLOPE);
+                store_chunk(g, c, h);
+            }
+            // layer 2 on the tensor cores, layer 4 per thread
+            float acc[64];
+            hidden_mma(g, sbase + (uint32_t)blk * FBLK, acc);
+            float o0 = fw[352], o1 = fw[353];
+#pragma unroll
+            for (int k = 0; k < H; k++) {
+                const float a = lrelu(acc[k] + fw[160 + k], SLOPE);
+                const float2 w = *reinterpret_cast<const float2*>(fw + 224 + 2 * k);
+                o0 = fmaf(a, w.x, o0), o1 = fmaf(a, w.y, o1);
+            }
+            if (!INVERSE) {
+                // coupling1.forward (additive): h2 -= bias_net ; reverse ; coupling2.forward
+                if (tdim == 1) x1 -= o0, x2 -= o1;
+                else x2 -= o0;
+                const float a0 = rev ? x2 : x0, a1 = x1, a2 = rev ? x0 : x2;
+                x0 = (a0 - b0) * expf(-s0);
+                x1 = (a1 - b1) * expf(-s1);
+                x2 = (a2 - b2) * expf(-s2);
+                ss += (s0 + s1) + s2;
+            } else {
+                // coupling1.inverse: h2 += bias_net ; inv1x1.inverse ; ActNorm.inverse
+                if (tdim == 1) x1 += o0, x2 += o1;
+                else x2 += o0;
+                const float a0 = fw[18] * x0 + fw[19] * x1 + fw[20] * x2;
+                const float a1 = fw[21] * x0 + fw[22] * x1 + fw[23] * x2;
+                const float a2 = fw[24] * x0 + fw[25] * x1 + fw[26] * x2;
+                x0 = (a0 - fw[3]) * fw[6];
+                x1 = (a1 - fw[4]) * fw[7];
+                x2 = (a2 - fw[5]) * fw[8];
+            }
+        }
+        if (r < rows) {
+            float* d = xout + (size_t)r * 3;
+            d[0] = x0, d[1] = x1, d[2] = x2;
+            if (!INVERSE && ssum) ssum[r] = ss;
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+}
+
+// ---- conditioning: coupling2.scale_net / bias_net hidden + output layers per input point ------------------------
+// tc blob per block (PF_COND_TC_BLOCK bytes): Ws2 hi | Ws2 lo | Wb2 hi | Wb2 lo | floats 8192.. of the fp32 cond blob
+// (bs2[64] | bb2[64] | ws4[64][4] | wb4[64][4] | bs4[4] | bb4[4])
+constexpr int NWG_C = 4, NT_C = NWG_C * 128;
+constexpr uint32_t CBLK = PF_COND_TC_BLOCK;
+
+__global__ void __launch_bounds__(NT_C, 1)
+    flow_cond_tc_kernel(const float* __restrict__ raw, const uint8_t* __restrict__ wtc, float* __restrict__ sb,
+                        int64_t M) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr uint32_t a_off = (CBLK + 127u) & ~127u;
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off + NWG_C * A_WG);
+    uint64_t* mbars = wbar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbars + NWG_C);
+
+    const int tid = threadIdx.x, warp = tid >> 5, wg = warp >> 2;
+    const int blk = blockIdx.y;
+    if (tid == 0) {
+        mbar_init(wbar, 1);
+        for (int i = 0; i < NWG_C; i++) mbar_init(mbars + i, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    if (tid == 0) {
+        mbar_expect_tx(wbar, CBLK);
+        bulk_g2s_chunked(smem, wtc + (size_t)blk * CBLK, CBLK, wbar);
+    }
+    Wg g;
+    wg_init(g, smem, a_off, mbars, *tmem_slot, tid);
+    const uint32_t sbase = smem_u32(smem);
+    const float* cw = reinterpret_cast<const float*>(smem + 4 * W_PART);
+    const int64_t ntiles = (M + TP - 1) / TP;
+    tc::mbar_wait_bounded(wbar, 0);
+
+    for (int64_t t = (int64_t)blockIdx.x * NWG_C + wg; t < ntiles; t += (int64_t)gridDim.x * NWG_C) {
+        const int64_t r = t * TP + g.e;
+        const int64_t m = min(r, M - 1);
+        const float* rawrow = raw + ((size_t)blk * M + m) * 192 + 64;
+        float o[2][3];
+#pragma unroll
+        for (int net = 0; net < 2; net++) {
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                float u[8];
+                ldg256(rawrow + net * 64 + 8 * c, u);
+#pragma unroll
+                for (int k = 0; k < 8; k++) u[k] = lrelu(u[k], SLOPE);
+                store_chunk(g, c, u);
+            }
+            float acc[64];
+            hidden_mma(g, sbase + (uint32_t)net * 2 * W_PART, acc);
+            const float* b2 = cw + net * 64;
+            const float* w4 = cw + 128 + net * 256;
+            const float* b4 = cw + 640 + net * 4;
+            float o0 = b4[0], o1 = b4[1], o2 = b4[2];
+#pragma unroll
+            for (int k = 0; k < H; k++) {
+                const float a = lrelu(acc[k] + b2[k], SLOPE);
+                const float4 w = *reinterpret_cast<const float4*>(w4 + 4 * k);
+                o0 = fmaf(a, w.x, o0), o1 = fmaf(a, w.y, o1), o2 = fmaf(a, w.z, o2);
+            }
+            o[net][0] = o0, o[net][1] = o1, o[net][2] = o2;
+        }
+        if (r < M) {
+            float4* dst = reinterpret_cast<float4*>(sb + ((size_t)blk * M + r) * 8);
+            dst[0] = make_float4(o[0][0], o[0][1], o[0][2], o[1][0]);
+            dst[1] = make_float4(o[1][1], o[1][2], 0.f, 0.f);
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+}
+
+int sm_count() {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+}
+
+}  // namespace
+
+extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, void* stream) {
+    PF_CHECK_ARG(raw && cond_tc && sb, "pf_flow_cond_tc: null pointer");
+    PF_CHECK_ARG(M >= 0 && nblocks >= 1 && nblocks <= MAXB, "pf_flow_cond_tc: bad sizes M=%lld nblocks=%d", (long long)M,
+                 nblocks);
+    PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(cond_tc) |
+                   reinterpret_cast<uintptr_t>(sb)) & 31) == 0, "pf_flow_cond_tc: pointers must be 32-byte aligned");
+    if (M == 0) return 0;
+    constexpr size_t smem = ((CBLK + 127u) & ~127u) + NWG_C * A_WG + 64;
+    if (int rc = pf_smem_optin(flow_cond_tc_kernel, smem)) return rc;
+    const int64_t ntiles = (M + TP - 1) / TP;
+    int workers = sm_count() / nblocks;
+    if (workers < 1) workers = 1;
+    if ((int64_t)workers * NWG_C > ntiles) workers = (int)((ntiles + NWG_C - 1) / NWG_C);
+    dim3 grid((unsigned)workers, (unsigned)nblocks);
+    flow_cond_tc_kernel<<<grid, NT_C, smem, (cudaStream_t)stream>>>(raw, static_cast<const uint8_t*>(cond_tc), sb, M);
+    return pf_launch_status("flow_cond_tc_kernel");
+}
+
+static int flow_tc_launch(bool inverse, const float* xin, const float* raw, const float* sb, const void* flow_tc,
+                          float* xout, float* ssum, int64_t M, int R, int nblocks, void* stream) {
+    PF_CHECK_ARG(xin && raw && sb && flow_tc && xout, "pf_flow_tc: null pointer");
+    PF_CHECK_ARG(M >= 0 && R >= 1 && nblocks >= 1 && nblocks <= 6, "pf_flow_tc: bad sizes M=%lld R=%d nblocks=%d (<= 6)",
+                 (long long)M, R, nblocks);
+    PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(flow_tc) |
+                   reinterpret_cast<uintptr_t>(sb)) & 31) == 0, "pf_flow_tc: pointers must be 32-byte aligned");
+    if (M == 0) return 0;
+    const size_t smem = (((size_t)nblocks * FBLK + 127u) & ~(size_t)127u) + NWG * A_WG + 64;
+    const int64_t rows = inverse ? M * R : M;
+    const int64_t ntiles = (rows + TP - 1) / TP;
+    int grid = sm_count();
+    if ((int64_t)grid * NWG > ntiles) grid = (int)((ntiles + NWG - 1) / NWG);
+    const uint8_t* w = static_cast<const uint8_t*>(flow_tc);
+    if (inverse) {
+        if (int rc = pf_smem_optin(flow_tc_kernel<true>, smem)) return rc;
+        flow_tc_kernel<true><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, nullptr, M, R, nblocks);
+    } else {
+        if (int rc = pf_smem_optin(flow_tc_kernel<false>, smem)) return rc;
+        flow_tc_kernel<false><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, ssum, M, 1, nblocks);
+    }
+    return pf_launch_status("flow_tc_kernel");
+}
+
+extern "C" int pf_flow_fwd_tc(const float* x, const float* raw, const float* sb, const void* flow_tc, float* z,
+                              float* ssum, int64_t M, int nblocks, void* stream) {
+    return flow_tc_launch(false, x, raw, sb, flow_tc, z, ssum, M, 1, nblocks, stream);
+}
+
+extern "C" int pf_flow_inv_tc(const float* zin, const float* raw, const float* sb, const void* flow_tc, float* x,
+                              int64_t M, int R, int nblocks, void* stream) {
+    return flow_tc_launch(true, zin, raw, sb, flow_tc, x, nullptr, M, R, nblocks, stream);
+}

@@ -35,6 +35,8 @@ class PUFlowEngine:
         # tensor-core (tcgen05, split-fp16) EdgeConv for the compute-bound blocks; PUFLOW_EDGECONV=ffma selects the
         # FP32 FFMA kernel everywhere (A/B comparison, tests)
         self.use_tc = os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma"
+        # same switch for the flow stack (PUFLOW_FLOW=ffma keeps flow.cu's FP32 kernels)
+        self.flow_tc = self.use_tc and os.environ.get("PUFLOW_FLOW", "tc") != "ffma"
 
     def _linear(self, a, wd, name, bias=None, act=ACT_NONE):
         """Per-point linear layer: tensor-core kernel when a packed blob exists (K in {16..128}), FFMA otherwise."""
@@ -81,14 +83,14 @@ class PUFlowEngine:
                 ops.linear_tc(cs[i].reshape(M, -1), self.w["wc_tc"][i], 192, None, ACT_NONE, out=raw[i])
             else:
                 ops.linear(cs[i].reshape(M, -1), self.w["wc"][i], None, ACT_NONE, out=raw[i])
-        sb = ops.flow_cond(raw, self.w["cond"])
+        sb = ops.flow_cond(raw, self.w["cond_tc"] if self.flow_tc else self.w["cond"])
         return raw, sb
 
     def f(self, xyz: torch.Tensor, cond):
         """PointInterpFlow.f (interpflow.py:302-313) -> (z[Bp,N,3], log_det_J[Bp])."""
         Bp, N, _ = xyz.shape
         raw, sb = cond
-        z, ssum = ops.flow_fwd(xyz.reshape(Bp * N, 3), raw, sb, self.w["flow"])
+        z, ssum = ops.flow_fwd(xyz.reshape(Bp * N, 3), raw, sb, self.w["flow_tc"] if self.flow_tc else self.w["flow"])
         logdet = self.w["logdet_const"] * N - ssum.view(Bp, N).sum(1)
         return z.view(Bp, N, 3), logdet
 
@@ -114,7 +116,7 @@ class PUFlowEngine:
         """PointInterpFlow.g (interpflow.py:315-321) on zup[Bp, N*R, 3] (row n*R + r)."""
         raw, sb = cond
         Bp = zup.shape[0]
-        x = ops.flow_inv(zup.reshape(-1, 3), raw, sb, self.w["flow"], upratio)
+        x = ops.flow_inv(zup.reshape(-1, 3), raw, sb, self.w["flow_tc"] if self.flow_tc else self.w["flow"], upratio)
         return x.view(Bp, -1, 3)
 
     # ---- whole path ----------------------------------------------------------------------------------

@@ -201,11 +201,20 @@ def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int,
 # ---- (3) flow ------------------------------------------------------------------------------------
 def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
     """raw[nb, M, 192] -> sb[nb, M, 8] = (s0,s1,s2,b0,b1,b2,0,0): coupling2 scale/bias per input point."""
-    _chk(raw, "raw"), _chk(cond_w, "cond_w")
+    _chk(raw, "raw")
     nb, M, w = raw.shape
+    sb = torch.empty((nb, M, 8), dtype=torch.float32, device=raw.device)
+    if cond_w.dtype == torch.uint8:          # tensor-core variant: blob from packing.pack_cond_tc
+        _chk(cond_w, "cond_w", torch.uint8)
+        if w != 192 or cond_w.shape != (nb, N.PF_COND_TC_BLOCK):
+            raise ValueError("flow_cond: bad shapes")
+        with _dev(raw), _launch("flow_cond_tc"):
+            N.check(lib.pf_flow_cond_tc(raw.data_ptr(), cond_w.data_ptr(), sb.data_ptr(), M, nb, _stream()),
+                    "pf_flow_cond_tc")
+        return sb
+    _chk(cond_w, "cond_w")
     if w != 192 or cond_w.shape != (nb, N.PF_COND_BLOB):
         raise ValueError("flow_cond: bad shapes")
-    sb = torch.empty((nb, M, 8), dtype=torch.float32, device=raw.device)
     with _dev(raw), _launch("flow_cond"):
         N.check(lib.pf_flow_cond(raw.data_ptr(), cond_w.data_ptr(), sb.data_ptr(), M, nb, _stream()), "pf_flow_cond")
     return sb
@@ -213,12 +222,18 @@ def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
 
 def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor):
     """x[M,3] -> (z[M,3], ssum[M]); FlowBlock.forward x nb (interpflow.py:66-74,302-313)."""
-    _chk(x, "x"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w")
+    tc = flow_w.dtype == torch.uint8         # tensor-core variant: blob from packing.pack_flow_tc
+    _chk(x, "x"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w", torch.uint8 if tc else torch.float32)
     nb, M, _ = raw.shape
-    if x.shape != (M, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_BLOB):
+    if x.shape != (M, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_TC_BLOCK if tc else N.PF_FLOW_BLOB):
         raise ValueError("flow_fwd: bad shapes")
     z = torch.empty_like(x)
     ssum = torch.empty((M,), dtype=torch.float32, device=x.device)
+    if tc:
+        with _dev(x), _launch("flow_fwd_tc"):
+            N.check(lib.pf_flow_fwd_tc(x.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
+                                       ssum.data_ptr(), M, nb, _stream()), "pf_flow_fwd_tc")
+        return z, ssum
     with _dev(x), _launch("flow_fwd"):
         N.check(lib.pf_flow_fwd(x.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
                                 ssum.data_ptr(), M, nb, _stream()), "pf_flow_fwd")
@@ -227,11 +242,18 @@ def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch
 
 def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor, R: int):
     """zin[M*R,3] (row n*R+r conditioned by input point n) -> x[M*R,3]; FlowBlock.inverse x nb."""
-    _chk(zin, "zin"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w")
+    tc = flow_w.dtype == torch.uint8
+    _chk(zin, "zin"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w", torch.uint8 if tc else torch.float32)
     nb, M, _ = raw.shape
-    if zin.shape != (M * R, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_BLOB):
+    if zin.shape != (M * R, 3) or sb.shape != (nb, M, 8) or \
+            flow_w.shape != (nb, N.PF_FLOW_TC_BLOCK if tc else N.PF_FLOW_BLOB):
         raise ValueError("flow_inv: bad shapes")
     x = torch.empty_like(zin)
+    if tc:
+        with _dev(zin), _launch("flow_inv_tc"):
+            N.check(lib.pf_flow_inv_tc(zin.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(),
+                                       M, R, nb, _stream()), "pf_flow_inv_tc")
+        return x
     with _dev(zin), _launch("flow_inv"):
         N.check(lib.pf_flow_inv(zin.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(), M, R,
                                 nb, _stream()), "pf_flow_inv")

@@ -20,7 +20,7 @@ from typing import Dict
 
 import torch
 
-from ._native import PF_COND_BLOB, PF_FLOW_BLOB, PF_INTERP_BLOB
+from ._native import PF_COND_BLOB, PF_COND_TC_BLOCK, PF_FLOW_BLOB, PF_FLOW_TC_BLOCK, PF_INTERP_BLOB
 
 BN_EPS = 1e-5
 NUM_BLOCKS = 6
@@ -297,6 +297,35 @@ def set_injector(cond, scale_layers, bias_layers):
     return _f64(Ws0).t().contiguous(), _f64(Wb0).t().contiguous()
 
 
+def pack_flow_tc(flow):
+    """flow[nb, PF_FLOW_BLOB] (float64/32) -> uint8[nb, PF_FLOW_TC_BLOCK] for pf_flow_fwd_tc / pf_flow_inv_tc:
+    per block W2 hi | W2 lo ([64 out][64 in], csrc/tc.cuh operand layout) | the first 384 floats as fp32."""
+    out = []
+    for f in flow:
+        W2 = f[384:4480].reshape(64, 64).t().contiguous().double()        # [out, in]
+        hi, lo = umma_kmajor_fp16(W2)
+        out.append(torch.cat([hi, lo, f[:384].to(torch.float32).contiguous().view(torch.uint8)]))
+    blob = torch.stack(out)
+    assert blob.shape[1] == PF_FLOW_TC_BLOCK, blob.shape
+    return blob
+
+
+def pack_cond_tc(cond):
+    """cond[nb, PF_COND_BLOB] -> uint8[nb, PF_COND_TC_BLOCK] for pf_flow_cond_tc:
+    per block Ws2 hi | Ws2 lo | Wb2 hi | Wb2 lo | floats 8192.. (biases and output layers) as fp32."""
+    out = []
+    for c in cond:
+        parts = []
+        for net in range(2):
+            W = c[4096 * net:4096 * (net + 1)].reshape(64, 64).t().contiguous().double()
+            parts.extend(umma_kmajor_fp16(W))
+        parts.append(c[8192:].to(torch.float32).contiguous().view(torch.uint8))
+        out.append(torch.cat(parts))
+    blob = torch.stack(out)
+    assert blob.shape[1] == PF_COND_TC_BLOCK, blob.shape
+    return blob
+
+
 def _a1d(sd, prefix):
     return (sd[prefix + ".0.weight"], sd[prefix + ".2.weight"], sd[prefix + ".2.bias"], sd[prefix + ".4.weight"],
             sd[prefix + ".4.bias"])
@@ -349,6 +378,8 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
         out["logdet_const"] += fb["logdet_const"]
     out["flow"] = torch.stack(flows)
     out["cond"] = torch.stack(conds)
+    out["flow_tc"] = pack_flow_tc(out["flow"])
+    out["cond_tc"] = pack_cond_tc(out["cond"])
     out["interp"] = pack_interp(sd)
     out["interp"]["tc"] = pack_interp_tc(sd)
 

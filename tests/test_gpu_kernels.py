@@ -280,6 +280,60 @@ def test_flow_blocks_golden(ops, dev, packed, golden):
         assert ok, (bi, err)
 
 
+@pytest.mark.parametrize("M", [256, 1000, 77, 60000])
+def test_flow_tensor_core(ops, dev, packed, M):
+    """tcgen05 flow kernels (fp16 hi/lo split, fp32 accumulation).  Stated tolerance: the same 1e-4 normwise bound as
+    the FP32 kernels against the float64-accumulated emulation (measured ~1e-6), 1e-5 on sb."""
+    x, raw = _flow_inputs(packed, M, M)
+    rawd, ctc, ftc = raw.to(dev), packed["cond_tc"].to(dev), packed["flow_tc"].to(dev)
+    if M <= 1000:
+        sb_ref = emulate.flow_cond(raw, packed["cond"])
+        z_ref, ss_ref = emulate.flow_fwd(x, raw, sb_ref, packed["flow"])
+    else:       # large case: the FP32 FFMA kernels (checked against the emulation above) are the reference
+        sbf = ops.flow_cond(rawd, packed["cond"].to(dev))
+        zf, ssf = ops.flow_fwd(x.to(dev), rawd, sbf, packed["flow"].to(dev))
+        sb_ref, z_ref, ss_ref = sbf.cpu(), zf.cpu(), ssf.cpu()
+    sb = ops.flow_cond(rawd, ctc)
+    assert (sb.cpu() - sb_ref).abs().max() <= 1e-5 * max(1.0, sb_ref.abs().max())
+    assert (sb.cpu()[..., 6:] == 0).all()
+    z, ss = ops.flow_fwd(x.to(dev), rawd, sb, ftc)
+    ok, err = parity.close_norm(z.cpu().numpy()[None], z_ref.numpy()[None], 1e-4)
+    assert ok, err
+    assert (ss.cpu() - ss_ref).abs().max() <= 1e-4 * max(1.0, ss_ref.abs().max())
+    R = 4
+    zin = torch.randn(M * R, 3, generator=torch.Generator().manual_seed(1)) * 0.5
+    if M <= 1000:
+        xi_ref = emulate.flow_inv(zin, raw, sb_ref, packed["flow"], R)
+    else:
+        xi_ref = ops.flow_inv(zin.to(dev), rawd, sb_ref.to(dev), packed["flow"].to(dev), R).cpu()
+    xi = ops.flow_inv(zin.to(dev), rawd, sb, ftc, R)
+    ok, err = parity.close_norm(xi.cpu().numpy()[None], xi_ref.numpy()[None], 1e-4)
+    assert ok, err
+    back = ops.flow_inv(z, rawd, sb, ftc, 1).cpu()
+    assert (back - x).abs().max() < 1e-4
+
+
+def test_flow_tensor_core_golden_and_subsets(ops, dev, packed, golden):
+    """Single FlowBlock forward / inverse on the tensor-core kernels against the unmodified reference."""
+    fl = golden("flows_pu1k.npz")
+    for bi in (0, 1):
+        x = torch.from_numpy(fl[f"b{bi}_x"]).reshape(-1, 3)
+        c = torch.from_numpy(fl[f"b{bi}_c"]).reshape(x.shape[0], -1)
+        raw = ops.linear(c.to(dev), packed["wc"][bi].to(dev))[None].contiguous()
+        cw, fw = packed["cond_tc"][bi:bi + 1].to(dev), packed["flow_tc"][bi:bi + 1].to(dev)
+        sb = ops.flow_cond(raw, cw)
+        y, _ = ops.flow_fwd(x.to(dev), raw, sb, fw)
+        ok, err = parity.close_norm(y.cpu().view(2, 64, 3).numpy(), fl[f"b{bi}_block_fwd"], 1e-4)
+        assert ok, (bi, err)
+        xi = ops.flow_inv(x.to(dev), raw, sb, fw, 1)
+        ok, err = parity.close_norm(xi.cpu().view(2, 64, 3).numpy(), fl[f"b{bi}_block_inv"], 1e-4)
+        assert ok, (bi, err)
+    # empty batch
+    e = ops.flow_inv(torch.empty(0, 3, device=dev), torch.empty(6, 0, 192, device=dev), torch.empty(6, 0, 8, device=dev),
+                     packed["flow_tc"].to(dev), 4)
+    assert e.shape == (0, 3)
+
+
 # ---- (4) interpolation -----------------------------------------------------------------------------
 @pytest.mark.parametrize("Bp,N,R", [(3, 256, 4), (2, 100, 2), (1, 256, 16)])
 def test_interp(ops, dev, packed, Bp, N, R):
