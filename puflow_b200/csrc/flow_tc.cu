@@ -47,17 +47,36 @@ struct Wg {
     int bar_id, e;
 };
 
-// 8 activations (already through LeakyReLU) -> chunk c (K = 8c .. 8c+7) of this thread's operand row
-__device__ __forceinline__ void store_chunk(const Wg& g, int c, const float (&h)[8]) {
-    uint32_t hi[4], lo[4];
+// 64 activations (already through LeakyReLU) -> this thread's operand row.  fp16 saturates at 65,504, and exp(s) of the
+// affine injector can make intermediate coordinates (hence activations) arbitrarily large, so a row whose largest
+// magnitude exceeds 2^14 is scaled by a power of two (exact) before the split; the caller multiplies the row's
+// accumulators by the returned inverse scale (the layer is linear).  Returns 1 for ordinary rows.
+__device__ __forceinline__ float store_row(const Wg& g, float (&h)[64]) {
+    float amax = 0.f;
 #pragma unroll
-    for (int u = 0; u < 4; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
-    *reinterpret_cast<uint4*>(g.a_row_hi + c * 128) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<uint4*>(g.a_row_hi + A_PART + c * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    for (int k = 0; k < 64; k++) amax = fmaxf(amax, fabsf(h[k]));
+    const int ex = (__float_as_int(amax) >> 23) & 0xff;       // biased exponent (NaN/Inf rows stay NaN/Inf)
+    float inv = 1.f;
+    if (ex > 127 + 13) {
+        const int k = min(ex - 140, 120);
+        const float sc = __int_as_float((127 - k) << 23);
+        inv = __int_as_float((127 + k) << 23);
+#pragma unroll
+        for (int i = 0; i < 64; i++) h[i] *= sc;
+    }
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) tc::split2(h[8 * c + 2 * u], h[8 * c + 2 * u + 1], hi[u], lo[u]);
+        *reinterpret_cast<uint4*>(g.a_row_hi + c * 128) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(g.a_row_hi + A_PART + c * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    return inv;
 }
 
 // acc[64] = A[row of this thread] . W^T, W (hi at w_addr, lo W_PART further) in the tc.cuh operand layout.
-// All 128 threads of the warpgroup call this after their store_chunk()s.
+// All 128 threads of the warpgroup call this after store_row().
 __device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[64]) {
     tc::fence_async_smem();
     tc::fence_before_sync();
@@ -170,19 +189,26 @@ __global__ void __launch_bounds__(NT, 1)
             }
             // layer 0: a1 = lrelu(u1 + W1h . h1)   (W1h rows beyond tdim are zero)
             const float h1b = (tdim == 2) ? x1 : 0.f;
+            float inv;
+            {
+                float h[64];
 #pragma unroll
-            for (int c = 0; c < 8; c++) {
-                float u[8], h[8];
-                ldg256(rawrow + 8 * c, u);
-                const float4 wa0 = *reinterpret_cast<const float4*>(fw + 32 + 8 * c);
-                const float4 wa1 = *reinterpret_cast<const float4*>(fw + 32 + 8 * c + 4);
-                const float4 wb0 = *reinterpret_cast<const float4*>(fw + 96 + 8 * c);
-                const float4 wb1 = *reinterpret_cast<const float4*>(fw + 96 + 8 * c + 4);
-                const float wa[8] = {wa0.x, wa0.y, wa0.z, wa0.w, wa1.x, wa1.y, wa1.z, wa1.w};
-                const float wb[8] = {wb0.x, wb0.y, wb0.z, wb0.w, wb1.x, wb1.y, wb1.z, wb1.w};
+                for (int c = 0; c < 8; c++) {
+                    float u[8];
+                    ldg256(rawrow + 8 * c, u);
 #pragma unroll
-                for (int k = 0; k < 8; k++) h[k] = lrelu(fmaf(wb[k], h1b, fmaf(wa[k], x0, u[k])), SLOPE);
-                store_chunk(g, c, h);
+                    for (int k = 0; k < 8; k++) h[8 * c + k] = u[k];
+                }
+#pragma unroll
+                for (int c = 0; c < 16; c++) {
+                    const float4 wa = *reinterpret_cast<const float4*>(fw + 32 + 4 * c);
+                    const float4 wb = *reinterpret_cast<const float4*>(fw + 96 + 4 * c);
+                    h[4 * c + 0] = lrelu(fmaf(wb.x, h1b, fmaf(wa.x, x0, h[4 * c + 0])), SLOPE);
+                    h[4 * c + 1] = lrelu(fmaf(wb.y, h1b, fmaf(wa.y, x0, h[4 * c + 1])), SLOPE);
+                    h[4 * c + 2] = lrelu(fmaf(wb.z, h1b, fmaf(wa.z, x0, h[4 * c + 2])), SLOPE);
+                    h[4 * c + 3] = lrelu(fmaf(wb.w, h1b, fmaf(wa.w, x0, h[4 * c + 3])), SLOPE);
+                }
+                inv = store_row(g, h);
             }
             // layer 2 on the tensor cores, layer 4 per thread
             float acc[64];
@@ -190,7 +216,7 @@ __global__ void __launch_bounds__(NT, 1)
             float o0 = fw[352], o1 = fw[353];
 #pragma unroll
             for (int k = 0; k < H; k++) {
-                const float a = lrelu(acc[k] + fw[160 + k], SLOPE);
+                const float a = lrelu(fmaf(acc[k], inv, fw[160 + k]), SLOPE);
                 const float2 w = *reinterpret_cast<const float2*>(fw + 224 + 2 * k);
                 o0 = fmaf(a, w.x, o0), o1 = fmaf(a, w.y, o1);
             }
@@ -270,13 +296,17 @@ __global__ void __launch_bounds__(NT_C, 1)
         float o[2][3];
 #pragma unroll
         for (int net = 0; net < 2; net++) {
+            float inv;
+            {
+                float h[64];
 #pragma unroll
-            for (int c = 0; c < 8; c++) {
-                float u[8];
-                ldg256(rawrow + net * 64 + 8 * c, u);
+                for (int c = 0; c < 8; c++) {
+                    float u[8];
+                    ldg256(rawrow + net * 64 + 8 * c, u);
 #pragma unroll
-                for (int k = 0; k < 8; k++) u[k] = lrelu(u[k], SLOPE);
-                store_chunk(g, c, u);
+                    for (int k = 0; k < 8; k++) h[8 * c + k] = lrelu(u[k], SLOPE);
+                }
+                inv = store_row(g, h);
             }
             float acc[64];
             hidden_mma(g, sbase + (uint32_t)net * 2 * W_PART, acc);
@@ -286,7 +316,7 @@ __global__ void __launch_bounds__(NT_C, 1)
             float o0 = b4[0], o1 = b4[1], o2 = b4[2];
 #pragma unroll
             for (int k = 0; k < H; k++) {
-                const float a = lrelu(acc[k] + b2[k], SLOPE);
+                const float a = lrelu(fmaf(acc[k], inv, b2[k]), SLOPE);
                 const float4 w = *reinterpret_cast<const float4*>(w4 + 4 * k);
                 o0 = fmaf(a, w.x, o0), o1 = fmaf(a, w.y, o1), o2 = fmaf(a, w.z, o2);
             }
