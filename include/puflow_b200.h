@@ -129,14 +129,21 @@ PF_API int pf_flow_inv(const float* zin, const float* raw, const float* sb, cons
  * accumulation; everything else fp32 as above; tolerance in tests/test_gpu_kernels.py).  Same arguments, except the
  * weights: cond_tc[nblocks][PF_COND_TC_BLOCK bytes], flow_tc[nblocks][PF_FLOW_TC_BLOCK bytes] from
  * puflow_b200/packing.py (pack_cond_tc / pack_flow_tc).  nblocks <= 6 for pf_flow_fwd_tc / pf_flow_inv_tc.
- * raw, sb and the blobs must be 32-byte aligned. */
+ * raw, sb and the blobs must be 32-byte aligned.  ldraw: row stride of raw in floats -- 192 for the layout above, 64
+ * for the compact raw1[nblocks][M][64] written by pf_cond_chain_tc (only columns [0,64) are read by the flow).
+ *
+ * pf_cond_chain_tc fuses, for one block, FeatMergeUnit (interpflow.py:251-258), the conditioning first layers and
+ * pf_flow_cond:  c[M][C] (EdgeConv output, C in {32,64,128}) -> raw1[M][64], sb[M][8].  conv2 of the merge unit (no
+ * bias, no activation) is composed with the first layers on the host (packing.pack_chain_tc, PF_CHAIN_TC_BYTES(C)). */
 #define PF_COND_TC_BLOCK 35360
 #define PF_FLOW_TC_BLOCK 17920
 PF_API int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, void* stream);
-PF_API int pf_flow_fwd_tc(const float* x, const float* raw, const float* sb, const void* flow_tc, float* z, float* ssum,
-                   int64_t M, int nblocks, void* stream);
-PF_API int pf_flow_inv_tc(const float* zin, const float* raw, const float* sb, const void* flow_tc, float* x, int64_t M,
-                   int R, int nblocks, void* stream);
+#define PF_CHAIN_TC_BYTES(C) (2 * (C) * (C) + 2 * 192 * (C) + 4 * 8192 + (64 + 648) * 4)
+PF_API int pf_flow_fwd_tc(const float* x, const float* raw, int ldraw, const float* sb, const void* flow_tc, float* z,
+                   float* ssum, int64_t M, int nblocks, void* stream);
+PF_API int pf_flow_inv_tc(const float* zin, const float* raw, int ldraw, const float* sb, const void* flow_tc, float* x,
+                   int64_t M, int R, int nblocks, void* stream);
+PF_API int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, float* raw1, float* sb, int64_t M, void* stream);
 
 /* ---- (4) latent interpolation -------------------------------------------------------------------------
  * Replaces InterpolationModule.forward (/root/reference/modules/discrete/interpflow.py:162-186) with

@@ -33,8 +33,9 @@ SIGNATURES = {
     "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
     "pf_flow_cond_tc": [_vp, _vp, _vp, _i64, _i, _vp],
-    "pf_flow_fwd_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
-    "pf_flow_inv_tc": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
+    "pf_flow_fwd_tc": [_vp, _vp, _i, _vp, _vp, _vp, _vp, _i64, _i, _vp],
+    "pf_flow_inv_tc": [_vp, _vp, _i, _vp, _vp, _vp, _i64, _i, _i, _vp],
+    "pf_cond_chain_tc": [_vp, _i, _vp, _vp, _vp, _i64, _vp],
     "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
     "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
@@ -55,6 +56,11 @@ PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
 PF_COND_TC_BLOCK = 35360
 PF_FLOW_TC_BLOCK = 17920
+
+
+def chain_tc_bytes(C: int) -> int:
+    return 2 * C * C + 2 * 192 * C + 4 * 8192 + (64 + 648) * 4
+
 PF_INTERP_BLOB = 46304
 PF_EDGECONV_TC_BLOB = 90112
 PF_INTERP_TC_BLOB = 205440

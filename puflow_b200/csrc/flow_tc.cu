@@ -128,7 +128,7 @@ template <bool INVERSE>
 __global__ void __launch_bounds__(NT, 1)
     flow_tc_kernel(const float* __restrict__ xin, const float* __restrict__ raw, const float* __restrict__ sb,
                    const uint8_t* __restrict__ wtc, float* __restrict__ xout, float* __restrict__ ssum, int64_t M,
-                   int R, int nblocks) {
+                   int R, int nblocks, int ldraw) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t w_bytes = (uint32_t)nblocks * FBLK;
     const uint32_t a_off = (w_bytes + 127u) & ~127u;
@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(NT, 1)
             const float* fw = reinterpret_cast<const float*>(smem + (size_t)blk * FBLK + 2 * W_PART);
             const int tdim = (int)fw[27];
             const bool rev = fw[28] != 0.f;
-            const float* rawrow = raw + ((size_t)blk * M + m) * 192;
+            const float* rawrow = raw + ((size_t)blk * M + m) * ldraw;
             const float4 v0 = __ldg(reinterpret_cast<const float4*>(sb + ((size_t)blk * M + m) * 8));
             const float4 v1 = __ldg(reinterpret_cast<const float4*>(sb + ((size_t)blk * M + m) * 8) + 1);
             const float s0 = v0.x, s1 = v0.y, s2 = v0.z, b0 = v0.w, b1 = v1.x, b2 = v1.y;
@@ -333,6 +333,204 @@ __global__ void __launch_bounds__(NT_C, 1)
     if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
 }
 
+// ---- fused conditioning chain per block: FeatMergeUnit + the conditioning first layers + the coupling2 nets ------
+//   c[M][C]  ->  h = relu(c.W1 + b1) [C/2]  ->  raw = h.(W2.[W1c|Ws0|Wb0]) [192]   (conv2 has no bias and no
+//   activation, interpflow.py:251-258, so it is composed with the first layers of the three LinearA1D nets on the host)
+//   -> raw1[M][64] = raw[:, 0:64] (what coupling1 needs) and sb[M][8] from raw[:, 64:192] as in flow_cond_tc_kernel.
+// One kernel per block instead of pf_linear x3 + pf_flow_cond: c is read once, cs / raw never reach HBM.
+// chain blob (bytes): W1 hi|lo [C/2 out][C in] | W2c hi|lo [192 out][C/2 in] | Ws2 hi|lo | Wb2 hi|lo |
+//                     fp32: b1[64] | cond tail (bs2[64] bb2[64] ws4[64][4] wb4[64][4] bs4[4] bb4[4])
+__device__ __forceinline__ void stg256(float* p, const float (&v)[8]) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+                 "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
+}
+// operands published -> one thread issues the 3 split products D[:, dcol..dcol+n) (+)= A[:, 0:16 ks] . W^T -> commit
+__device__ __forceinline__ void issue3(Wg& g, uint32_t d_tmem, uint32_t w_addr, uint32_t w_part, uint32_t w_sbo, int w_k0,
+                                       int ks, int n, bool accumulate) {
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    tc::named_bar(g.bar_id, 128);
+    if (g.e == 0) {
+        tc::fence_after_sync();
+        const uint32_t idesc = tc::idesc_f16(128, n);
+        const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
+        const uint64_t db_hi = tc::smem_desc(w_addr, w_sbo) + 16u * w_k0, db_lo = tc::smem_desc(w_addr + w_part, w_sbo) + 16u * w_k0;
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, (accumulate || s > 0) ? 1u : 0u);
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, 1);
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+        tc::commit(g.mbar);
+    }
+    tc::mbar_wait_bounded(g.mbar, g.phase);
+    g.phase ^= 1;
+    tc::fence_after_sync();
+}
+// chunk c (8 values) of this thread's operand row, plain saturating split
+__device__ __forceinline__ void store_chunk(const Wg& g, int c, const float (&h)[8]) {
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
+    *reinterpret_cast<uint4*>(g.a_row_hi + c * 128) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(g.a_row_hi + A_PART + c * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+constexpr int NWG_CH = 2, NT_CH = NWG_CH * 128;
+__host__ __device__ constexpr uint32_t chain_w1_part(int C) { return (uint32_t)C * C; }          // (C/2) x C halfs
+__host__ __device__ constexpr uint32_t chain_w2_part(int C) { return 192u * C; }                 // 192 x (C/2) halfs
+__host__ __device__ constexpr uint32_t chain_bytes(int C) {
+    return 2 * chain_w1_part(C) + 2 * chain_w2_part(C) + 4 * W_PART + (64 + 648) * 4;
+}
+
+template <int C>
+__global__ void __launch_bounds__(NT_CH, 1)
+    cond_chain_tc_kernel(const float* __restrict__ cin, const uint8_t* __restrict__ wtc, float* __restrict__ raw1,
+                         float* __restrict__ sb, int64_t M) {
+    constexpr int H1 = C / 2;
+    constexpr uint32_t W1P = chain_w1_part(C), W2P = chain_w2_part(C), WBYTES = chain_bytes(C);
+    constexpr uint32_t OFF_W2 = 2 * W1P, OFF_NET = OFF_W2 + 2 * W2P, OFF_F = OFF_NET + 4 * W_PART;
+    constexpr uint32_t a_off = (WBYTES + 127u) & ~127u;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off + NWG_CH * A_WG);
+    uint64_t* mbars = wbar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbars + NWG_CH);
+
+    const int tid = threadIdx.x, warp = tid >> 5, wg = warp >> 2;
+    if (tid == 0) {
+        mbar_init(wbar, 1);
+        for (int i = 0; i < NWG_CH; i++) mbar_init(mbars + i, 1);
+        mbar_fence_init();
+    }
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    if (tid == 0) {
+        mbar_expect_tx(wbar, WBYTES);
+        bulk_g2s_chunked(smem, wtc, WBYTES, wbar);
+    }
+    Wg g;
+    wg_init(g, smem, a_off, mbars, *tmem_slot, tid);
+    g.d_tmem = *tmem_slot + (uint32_t)wg * 256;          // per warpgroup: raw at +0 (192 columns), scratch at +192 (64)
+    const uint32_t d_raw = g.d_tmem, d_s = g.d_tmem + 192;
+    const uint32_t sbase = smem_u32(smem);
+    const float* fb1 = reinterpret_cast<const float*>(smem + OFF_F);
+    const float* cw = fb1 + 64;
+    const int64_t ntiles = (M + TP - 1) / TP;
+    tc::mbar_wait_bounded(wbar, 0);
+
+    for (int64_t t = (int64_t)blockIdx.x * NWG_CH + wg; t < ntiles; t += (int64_t)gridDim.x * NWG_CH) {
+        const int64_t r = t * TP + g.e;
+        const float* crow = cin + (size_t)min(r, M - 1) * C;
+        // ---- stage 1: h = relu(c . W1 + b1), K = C in slices of at most 64 through the 64-wide operand buffer ----
+        constexpr int KS1 = C < 64 ? C : 64;
+#pragma unroll 1
+        for (int k0 = 0; k0 < C; k0 += KS1) {
+#pragma unroll
+            for (int c = 0; c < KS1 / 8; c++) {
+                float u[8];
+                ldg256(crow + k0 + 8 * c, u);
+                store_chunk(g, c, u);
+            }
+            issue3(g, d_s, sbase, W1P, C * 16, k0 / 16, KS1 / 16, H1, k0 > 0);
+        }
+        float inv;
+        {
+            float h[64];
+            if (H1 == 64) {
+                float lo32[32], hi32[32];
+                tc::ld32(d_s + g.lane_sel, lo32), tc::ld32(d_s + g.lane_sel + 32, hi32);
+#pragma unroll
+                for (int i = 0; i < 32; i++) h[i] = lo32[i], h[32 + i] = hi32[i];
+            } else if (H1 == 32) {
+                float lo32[32];
+                tc::ld32(d_s + g.lane_sel, lo32);
+#pragma unroll
+                for (int i = 0; i < 32; i++) h[i] = lo32[i], h[32 + i] = 0.f;
+            } else {
+                float lo16[16];
+                tc::ld16(d_s + g.lane_sel, lo16);
+#pragma unroll
+                for (int i = 0; i < 64; i++) h[i] = i < 16 ? lo16[i < 16 ? i : 0] : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < H1; i++) h[i] = fmaxf(h[i] + fb1[i], 0.f);
+            inv = store_row(g, h);                      // columns beyond H1 are zero and never read by the MMAs
+        }
+        // ---- stage 2: raw = h . W2c  (N = 192) ----
+        issue3(g, d_raw, sbase + OFF_W2, W2P, H1 * 16, 0, H1 / 16, 192, false);
+        {
+            float* dst = raw1 + (size_t)r * 64;
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                float v[32];
+                tc::ld32(d_raw + g.lane_sel + 32 * q, v);
+                if (r < M) {
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const float o[8] = {v[8 * c] * inv, v[8 * c + 1] * inv, v[8 * c + 2] * inv, v[8 * c + 3] * inv,
+                                            v[8 * c + 4] * inv, v[8 * c + 5] * inv, v[8 * c + 6] * inv, v[8 * c + 7] * inv};
+                        stg256(dst + 32 * q + 8 * c, o);
+                    }
+                }
+            }
+        }
+        // ---- stage 3: the two coupling2 nets on raw[:, 64:128] / raw[:, 128:192] ----
+        float o[2][3];
+#pragma unroll
+        for (int net = 0; net < 2; net++) {
+            float inv2;
+            {
+                float h[64], lo32[32], hi32[32];
+                tc::ld32(d_raw + g.lane_sel + 64 + 64 * net, lo32), tc::ld32(d_raw + g.lane_sel + 96 + 64 * net, hi32);
+#pragma unroll
+                for (int i = 0; i < 32; i++) h[i] = lrelu(lo32[i] * inv, SLOPE), h[32 + i] = lrelu(hi32[i] * inv, SLOPE);
+                inv2 = store_row(g, h);
+            }
+            issue3(g, d_s, sbase + OFF_NET + (uint32_t)net * 2 * W_PART, W_PART, H * 16, 0, H / 16, H, false);
+            float acc[64];
+            {
+                float lo32[32], hi32[32];
+                tc::ld32(d_s + g.lane_sel, lo32), tc::ld32(d_s + g.lane_sel + 32, hi32);
+#pragma unroll
+                for (int i = 0; i < 32; i++) acc[i] = lo32[i], acc[32 + i] = hi32[i];
+            }
+            const float* b2 = cw + net * 64;
+            const float* w4 = cw + 128 + net * 256;
+            const float* b4 = cw + 640 + net * 4;
+            float o0 = b4[0], o1 = b4[1], o2 = b4[2];
+#pragma unroll
+            for (int k = 0; k < H; k++) {
+                const float a = lrelu(fmaf(acc[k], inv2, b2[k]), SLOPE);
+                const float4 w = *reinterpret_cast<const float4*>(w4 + 4 * k);
+                o0 = fmaf(a, w.x, o0), o1 = fmaf(a, w.y, o1), o2 = fmaf(a, w.z, o2);
+            }
+            o[net][0] = o0, o[net][1] = o1, o[net][2] = o2;
+        }
+        if (r < M) {
+            float4* dst = reinterpret_cast<float4*>(sb + (size_t)r * 8);
+            dst[0] = make_float4(o[0][0], o[0][1], o[0][2], o[1][0]);
+            dst[1] = make_float4(o[1][1], o[1][2], 0.f, 0.f);
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(*tmem_slot, 512);
+}
+
+template <int C>
+int chain_launch(const float* c, const uint8_t* w, float* raw1, float* sb, int64_t M, int sms, cudaStream_t st) {
+    constexpr size_t smem = ((chain_bytes(C) + 127u) & ~127u) + NWG_CH * A_WG + 64;
+    if (int rc = pf_smem_optin(cond_chain_tc_kernel<C>, smem)) return rc;
+    const int64_t ntiles = (M + TP - 1) / TP;
+    int grid = sms;
+    if ((int64_t)grid * NWG_CH > ntiles) grid = (int)((ntiles + NWG_CH - 1) / NWG_CH);
+    cond_chain_tc_kernel<C><<<grid, NT_CH, smem, st>>>(c, w, raw1, sb, M);
+    return pf_launch_status("cond_chain_tc_kernel");
+}
+
 int sm_count() {
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -359,8 +557,9 @@ extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb,
     return pf_launch_status("flow_cond_tc_kernel");
 }
 
-static int flow_tc_launch(bool inverse, const float* xin, const float* raw, const float* sb, const void* flow_tc,
-                          float* xout, float* ssum, int64_t M, int R, int nblocks, void* stream) {
+static int flow_tc_launch(bool inverse, const float* xin, const float* raw, int ldraw, const float* sb,
+                          const void* flow_tc, float* xout, float* ssum, int64_t M, int R, int nblocks, void* stream) {
+    PF_CHECK_ARG(ldraw >= 64 && ldraw % 8 == 0, "pf_flow_tc: ldraw=%d must be a multiple of 8, >= 64", ldraw);
     PF_CHECK_ARG(xin && raw && sb && flow_tc && xout, "pf_flow_tc: null pointer");
     PF_CHECK_ARG(M >= 0 && R >= 1 && nblocks >= 1 && nblocks <= 6, "pf_flow_tc: bad sizes M=%lld R=%d nblocks=%d (<= 6)",
                  (long long)M, R, nblocks);
@@ -375,20 +574,39 @@ static int flow_tc_launch(bool inverse, const float* xin, const float* raw, cons
     const uint8_t* w = static_cast<const uint8_t*>(flow_tc);
     if (inverse) {
         if (int rc = pf_smem_optin(flow_tc_kernel<true>, smem)) return rc;
-        flow_tc_kernel<true><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, nullptr, M, R, nblocks);
+        flow_tc_kernel<true><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, nullptr, M, R, nblocks, ldraw);
     } else {
         if (int rc = pf_smem_optin(flow_tc_kernel<false>, smem)) return rc;
-        flow_tc_kernel<false><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, ssum, M, 1, nblocks);
+        flow_tc_kernel<false><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, ssum, M, 1, nblocks, ldraw);
     }
     return pf_launch_status("flow_tc_kernel");
 }
 
-extern "C" int pf_flow_fwd_tc(const float* x, const float* raw, const float* sb, const void* flow_tc, float* z,
+extern "C" int pf_flow_fwd_tc(const float* x, const float* raw, int ldraw, const float* sb, const void* flow_tc, float* z,
                               float* ssum, int64_t M, int nblocks, void* stream) {
-    return flow_tc_launch(false, x, raw, sb, flow_tc, z, ssum, M, 1, nblocks, stream);
+    return flow_tc_launch(false, x, raw, ldraw, sb, flow_tc, z, ssum, M, 1, nblocks, stream);
 }
 
-extern "C" int pf_flow_inv_tc(const float* zin, const float* raw, const float* sb, const void* flow_tc, float* x,
-                              int64_t M, int R, int nblocks, void* stream) {
-    return flow_tc_launch(true, zin, raw, sb, flow_tc, x, nullptr, M, R, nblocks, stream);
+extern "C" int pf_flow_inv_tc(const float* zin, const float* raw, int ldraw, const float* sb, const void* flow_tc,
+                              float* x, int64_t M, int R, int nblocks, void* stream) {
+    return flow_tc_launch(true, zin, raw, ldraw, sb, flow_tc, x, nullptr, M, R, nblocks, stream);
+}
+
+extern "C" int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, float* raw1, float* sb, int64_t M,
+                                void* stream) {
+    PF_CHECK_ARG(c && chain_tc && raw1 && sb, "pf_cond_chain_tc: null pointer");
+    PF_CHECK_ARG(M >= 0, "pf_cond_chain_tc: bad size M=%lld", (long long)M);
+    PF_CHECK_ARG(C == 32 || C == 64 || C == 128, "pf_cond_chain_tc: C=%d not in {32, 64, 128}", C);
+    PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(c) | reinterpret_cast<uintptr_t>(chain_tc) |
+                   reinterpret_cast<uintptr_t>(raw1) | reinterpret_cast<uintptr_t>(sb)) & 31) == 0,
+                 "pf_cond_chain_tc: pointers must be 32-byte aligned");
+    if (M == 0) return 0;
+    const uint8_t* w = static_cast<const uint8_t*>(chain_tc);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int sms = sm_count();
+    switch (C) {
+        case 32: return chain_launch<32>(c, w, raw1, sb, M, sms, st);
+        case 64: return chain_launch<64>(c, w, raw1, sb, M, sms, st);
+        default: return chain_launch<128>(c, w, raw1, sb, M, sms, st);
+    }
 }

@@ -74,6 +74,24 @@ class PUFlowEngine:
             cs.append(self.merge(i, c).view(Bp, N, -1))
         return (cs, feats) if return_feats else cs
 
+    def feat_conditioning(self, xyz: torch.Tensor, idx: torch.Tensor, want_cs: bool = False):
+        """feat_extract + conditioning with the merge unit, the conditioning first layers and the coupling2 nets of each
+        block fused into one kernel (pf_cond_chain_tc): cs / the 192-wide raw never reach HBM.
+        -> ((raw1[6, M, 64], sb[6, M, 8]), feats, cs-or-None)."""
+        Bp, N, _ = xyz.shape
+        M = Bp * N
+        raw1 = torch.empty((NUM_BLOCKS, M, 64), dtype=torch.float32, device=self.device)
+        sb = torch.empty((NUM_BLOCKS, M, 8), dtype=torch.float32, device=self.device)
+        c = xyz.reshape(M, 3)
+        feats, cs = [], ([] if want_cs else None)
+        for i in range(NUM_BLOCKS):
+            c = self.edgeconv_block(i, c, idx, Bp, N)
+            feats.append(c.view(Bp, N, -1))
+            ops.cond_chain(c, self.w["chain_tc"][i], raw1[i], sb[i])
+            if want_cs:
+                cs.append(self.merge(i, c).view(Bp, N, -1))
+        return (raw1, sb), feats, cs
+
     def conditioning(self, cs: List[torch.Tensor]):
         """Everything the flow needs from cs, per INPUT point: raw[6, M, 192], sb[6, M, 8]."""
         M = cs[0].shape[0] * cs[0].shape[1]
@@ -127,8 +145,11 @@ class PUFlowEngine:
             raise ValueError(f"expected xyz[B,N,3], got {tuple(xyz.shape)}")
         xyz = xyz.contiguous().float()
         idx = self.knn(xyz, K_MAIN)
-        cs, feats = self.feat_extract(xyz, idx, return_feats=True)
-        cond = self.conditioning(cs)
+        if self.flow_tc:
+            cond, feats, cs = self.feat_conditioning(xyz, idx, want_cs=return_all)
+        else:
+            cs, feats = self.feat_extract(xyz, idx, return_feats=True)
+            cond = self.conditioning(cs)
         z, logp_x = self.log_prob(xyz, cond)
         zup = self.interp(z, xyz, upratio, idx)
         x = self.g(zup, cond, upratio)

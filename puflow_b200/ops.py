@@ -220,18 +220,32 @@ def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
     return sb
 
 
+def cond_chain(c: torch.Tensor, chain_w: torch.Tensor, raw1: torch.Tensor, sb: torch.Tensor):
+    """One block of the fused conditioning chain: c[M, C] (EdgeConv output) -> raw1[M, 64], sb[M, 8] written in place
+    (FeatMergeUnit interpflow.py:251-258 + first layers of the three LinearA1D nets + the coupling2 nets)."""
+    _chk(c, "c"), _chk(chain_w, "chain_w", torch.uint8), _chk(raw1, "raw1"), _chk(sb, "sb")
+    M, C = c.shape
+    if C not in (32, 64, 128) or chain_w.numel() != N.chain_tc_bytes(C) or raw1.shape != (M, 64) or sb.shape != (M, 8):
+        raise ValueError("cond_chain: bad shapes")
+    with _dev(c), _launch(f"cond_chain_tc_c{C}"):
+        N.check(lib.pf_cond_chain_tc(c.data_ptr(), C, chain_w.data_ptr(), raw1.data_ptr(), sb.data_ptr(), M, _stream()),
+                "pf_cond_chain_tc")
+    return raw1, sb
+
+
 def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor):
     """x[M,3] -> (z[M,3], ssum[M]); FlowBlock.forward x nb (interpflow.py:66-74,302-313)."""
     tc = flow_w.dtype == torch.uint8         # tensor-core variant: blob from packing.pack_flow_tc
     _chk(x, "x"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w", torch.uint8 if tc else torch.float32)
-    nb, M, _ = raw.shape
-    if x.shape != (M, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_TC_BLOCK if tc else N.PF_FLOW_BLOB):
+    nb, M, ldraw = raw.shape
+    if x.shape != (M, 3) or sb.shape != (nb, M, 8) or flow_w.shape != (nb, N.PF_FLOW_TC_BLOCK if tc else N.PF_FLOW_BLOB) \
+            or ldraw not in ((64, 192) if tc else (192,)):
         raise ValueError("flow_fwd: bad shapes")
     z = torch.empty_like(x)
     ssum = torch.empty((M,), dtype=torch.float32, device=x.device)
     if tc:
         with _dev(x), _launch("flow_fwd_tc"):
-            N.check(lib.pf_flow_fwd_tc(x.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
+            N.check(lib.pf_flow_fwd_tc(x.data_ptr(), raw.data_ptr(), ldraw, sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
                                        ssum.data_ptr(), M, nb, _stream()), "pf_flow_fwd_tc")
         return z, ssum
     with _dev(x), _launch("flow_fwd"):
@@ -244,14 +258,14 @@ def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: tor
     """zin[M*R,3] (row n*R+r conditioned by input point n) -> x[M*R,3]; FlowBlock.inverse x nb."""
     tc = flow_w.dtype == torch.uint8
     _chk(zin, "zin"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w", torch.uint8 if tc else torch.float32)
-    nb, M, _ = raw.shape
-    if zin.shape != (M * R, 3) or sb.shape != (nb, M, 8) or \
+    nb, M, ldraw = raw.shape
+    if zin.shape != (M * R, 3) or sb.shape != (nb, M, 8) or ldraw not in ((64, 192) if tc else (192,)) or \
             flow_w.shape != (nb, N.PF_FLOW_TC_BLOCK if tc else N.PF_FLOW_BLOB):
         raise ValueError("flow_inv: bad shapes")
     x = torch.empty_like(zin)
     if tc:
         with _dev(zin), _launch("flow_inv_tc"):
-            N.check(lib.pf_flow_inv_tc(zin.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(),
+            N.check(lib.pf_flow_inv_tc(zin.data_ptr(), raw.data_ptr(), ldraw, sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(),
                                        M, R, nb, _stream()), "pf_flow_inv_tc")
         return x
     with _dev(zin), _launch("flow_inv"):

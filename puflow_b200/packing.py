@@ -20,7 +20,7 @@ from typing import Dict
 
 import torch
 
-from ._native import PF_COND_BLOB, PF_COND_TC_BLOCK, PF_FLOW_BLOB, PF_FLOW_TC_BLOCK, PF_INTERP_BLOB
+from ._native import chain_tc_bytes, PF_COND_BLOB, PF_COND_TC_BLOCK, PF_FLOW_BLOB, PF_FLOW_TC_BLOCK, PF_INTERP_BLOB
 
 BN_EPS = 1e-5
 NUM_BLOCKS = 6
@@ -326,6 +326,26 @@ def pack_cond_tc(cond):
     return blob
 
 
+def pack_chain_tc(W1, b1, W2, wc, cond):
+    """Fused conditioning chain of one block (pf_cond_chain_tc).  W1[C/2, C], b1[C/2], W2[cond_dim, C/2]: FeatMergeUnit
+    conv1 / conv2 (interpflow.py:251-258); wc[cond_dim, 192]: first layers of the three LinearA1D nets (k-major);
+    cond: the block's fp32 cond blob.  conv2 (linear, bias-free) is composed with wc in float64."""
+    W1, W2, wc = _f64(W1), _f64(W2), _f64(wc)
+    H1, C = W1.shape
+    assert C in (32, 64, 128) and H1 == C // 2 and W2.shape[1] == H1 and wc.shape == (W2.shape[0], 192)
+    W2c = wc.t() @ W2                                                # [192 out, C/2 in]
+    parts = list(umma_kmajor_fp16(W1)) + list(umma_kmajor_fp16(W2c))
+    for net in range(2):
+        parts.extend(umma_kmajor_fp16(cond[4096 * net:4096 * (net + 1)].reshape(64, 64).t().contiguous().double()))
+    b1p = torch.zeros(64, dtype=torch.float32)
+    b1p[:H1] = _f64(b1).to(torch.float32)
+    parts.append(b1p.view(torch.uint8))
+    parts.append(cond[8192:].to(torch.float32).contiguous().view(torch.uint8))
+    blob = torch.cat(parts)
+    assert blob.numel() == chain_tc_bytes(C), (blob.numel(), C)
+    return blob
+
+
 def _a1d(sd, prefix):
     return (sd[prefix + ".0.weight"], sd[prefix + ".2.weight"], sd[prefix + ".2.bias"], sd[prefix + ".4.weight"],
             sd[prefix + ".4.bias"])
@@ -375,6 +395,9 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
         out["wc"].append(fb["wc"])
         out["wc_tc"].append(pack_linear_tc(fb["wc"]) if linear_tc_ok(*fb["wc"].shape) else None)
         flows.append(fb["flow"]), conds.append(fb["cond"])
+        out.setdefault("chain_tc", []).append(pack_chain_tc(
+            sd[f"merge_convs.{i}.conv1.weight"], sd[f"merge_convs.{i}.conv1.bias"], sd[f"merge_convs.{i}.conv2.weight"],
+            fb["wc"], fb["cond"]))
         out["logdet_const"] += fb["logdet_const"]
     out["flow"] = torch.stack(flows)
     out["cond"] = torch.stack(conds)

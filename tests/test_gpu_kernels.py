@@ -335,6 +335,36 @@ def test_flow_tensor_core_golden_and_subsets(ops, dev, packed, golden):
     assert e.shape == (0, 3)
 
 
+@pytest.mark.parametrize("blk,M", [(0, 300), (1, 128), (2, 1000), (5, 20000)])
+def test_cond_chain_tensor_core(ops, dev, packed, blk, M):
+    """Fused FeatMergeUnit + conditioning first layers + coupling2 nets (pf_cond_chain_tc) against the un-fused,
+    un-composed float64 chain.  Stated tolerance 1e-4 normwise on raw1, 1e-5 * max(1, |sb|) on sb (measured ~1e-6)."""
+    from puflow_b200.packing import FEAT_CFG
+    C = FEAT_CFG[blk][2]
+    gen = torch.Generator().manual_seed(blk * 7 + 1)
+    c = torch.randn(M, C, generator=gen).abs() * 0.7                       # EdgeConv outputs are max-pooled, mostly > 0
+    m = packed["merge"][blk]
+    h = emulate.linear(c.double(), m["w1"].double(), m["b1"].double(), "relu")
+    cs = emulate.linear(h, m["w2"].double())
+    raw = emulate.linear(cs, packed["wc"][blk].double()).float()
+    sb_ref = emulate.flow_cond(raw[None], packed["cond"][blk:blk + 1])[0]
+    raw1 = torch.empty(M, 64, device=dev)
+    sb = torch.empty(M, 8, device=dev)
+    ops.cond_chain(c.to(dev), packed["chain_tc"][blk].to(dev), raw1, sb)
+    ok, err = parity.close_norm(raw1.cpu().numpy()[None], raw[:, :64].numpy()[None], 1e-4)
+    assert ok, err
+    assert (sb.cpu() - sb_ref).abs().max() <= 1e-5 * max(1.0, sb_ref.abs().max())
+    assert (sb.cpu()[:, 6:] == 0).all()
+    # the compact raw1 layout drives the flow kernels exactly like the 192-wide one
+    x = torch.randn(M, 3, generator=gen) * 0.5
+    raw_full = torch.zeros(1, M, 192, device=dev)
+    raw_full[0, :, :64] = raw1
+    ftc = packed["flow_tc"][blk:blk + 1].to(dev)
+    za, _ = ops.flow_fwd(x.to(dev), raw_full, sb[None].contiguous(), ftc)
+    zb, _ = ops.flow_fwd(x.to(dev), raw1[None].contiguous(), sb[None].contiguous(), ftc)
+    assert torch.equal(za, zb)
+
+
 # ---- (4) interpolation -----------------------------------------------------------------------------
 @pytest.mark.parametrize("Bp,N,R", [(3, 256, 4), (2, 100, 2), (1, 256, 16)])
 def test_interp(ops, dev, packed, Bp, N, R):
