@@ -540,6 +540,7 @@ int sm_count() {
 }  // namespace
 
 extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, void* stream) {
+    if (M == 0) return 0;
     PF_CHECK_ARG(raw && cond_tc && sb, "pf_flow_cond_tc: null pointer");
     PF_CHECK_ARG(M >= 0 && nblocks >= 1 && nblocks <= MAXB, "pf_flow_cond_tc: bad sizes M=%lld nblocks=%d", (long long)M,
                  nblocks);
@@ -560,6 +561,7 @@ extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb,
 static int flow_tc_launch(bool inverse, const float* xin, const float* raw, int ldraw, const float* sb,
                           const void* flow_tc, float* xout, float* ssum, int64_t M, int R, int nblocks, void* stream) {
     PF_CHECK_ARG(ldraw >= 64 && ldraw % 8 == 0, "pf_flow_tc: ldraw=%d must be a multiple of 8, >= 64", ldraw);
+    if (M == 0) return 0;
     PF_CHECK_ARG(xin && raw && sb && flow_tc && xout, "pf_flow_tc: null pointer");
     PF_CHECK_ARG(M >= 0 && R >= 1 && nblocks >= 1 && nblocks <= 6, "pf_flow_tc: bad sizes M=%lld R=%d nblocks=%d (<= 6)",
                  (long long)M, R, nblocks);
@@ -594,6 +596,7 @@ extern "C" int pf_flow_inv_tc(const float* zin, const float* raw, int ldraw, con
 
 extern "C" int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, float* raw1, float* sb, int64_t M,
                                 void* stream) {
+    if (M == 0) return 0;
     PF_CHECK_ARG(c && chain_tc && raw1 && sb, "pf_cond_chain_tc: null pointer");
     PF_CHECK_ARG(M >= 0, "pf_cond_chain_tc: bad size M=%lld", (long long)M);
     PF_CHECK_ARG(C == 32 || C == 64 || C == 128, "pf_cond_chain_tc: C=%d not in {32, 64, 128}", C);

@@ -20,7 +20,11 @@
 
 namespace {
 
-constexpr int FT = 1024, NW = FT / 32;
+#ifndef PF_FPS_THREADS
+#define PF_FPS_THREADS 640                   // 20 warps: the 1,280 buckets of a 40,960-point cloud are 2 full warp-iterations each
+#endif
+constexpr int FT = PF_FPS_THREADS, NW = FT / 32;
+static_assert(FT % 32 == 0 && NW <= 32, "per-warp partial results are reduced by one warp");
 constexpr int CELLS = 4096;                  // 16^3 grid
 constexpr float INIT_D = 1e10f;              // fps.py:53
 constexpr float SAFE = 0.9999f;              // box lower bound is scaled down: never above any computed distance
@@ -43,6 +47,18 @@ __device__ __forceinline__ float warp_max(float v) {
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
+
+#ifdef PF_FPS_TIMING
+__device__ long long g_fps_timing[8];
+#define FSTAMP(k)                                            \
+    do {                                                     \
+        long long now_ = clock64();                          \
+        tacc_[k] += now_ - tprev_;                           \
+        tprev_ = now_;                                       \
+    } while (0)
+#else
+#define FSTAMP(k)
+#endif
 
 struct Slot {
     unsigned oidx;
@@ -69,10 +85,14 @@ __global__ void __launch_bounds__(FT, 1)
     const int mdwords = MD_SMEM ? npad : CELLS;            // region 0: md (rounds) aliased by the histogram (setup)
     float* md_s = sm;
     int* hist = reinterpret_cast<int*>(sm);
-    float* bb = sm + (mdwords > CELLS ? mdwords : CELLS);  // [6][NW*KB]
+    // per bucket slot two float4: (lo.x, lo.y, lo.z, max running-min of the bucket) and (hi.x, hi.y, hi.z, -)
+    float4* bbq = reinterpret_cast<float4*>(sm + (mdwords > CELLS ? mdwords : CELLS));
     const int nslot = NW * KB;
-    float* bmax = bb + 6 * nslot;
-    float* red = bmax + nslot;                             // [6*NW] setup reductions, then wmax[NW]
+    unsigned* wc_o = reinterpret_cast<unsigned*>(bbq + 2 * nslot);   // per bucket: the point that attains bmax with the lowest
+    float* wc_x = reinterpret_cast<float*>(wc_o + nslot);         // original index (oidx, x, y, z), refreshed whenever the
+    float* wc_y = wc_x + nslot;                                   // bucket is updated, so that picking the next sample
+    float* wc_z = wc_y + nslot;                                   // needs no trip to L2
+    float* red = wc_z + nslot;                             // [6*NW] setup reductions, then wmax[NW]
     Slot* slots = reinterpret_cast<Slot*>(red + 6 * NW);   // [NW]
     int* scan_tmp = reinterpret_cast<int*>(slots + NW);    // [NW]
 
@@ -94,8 +114,8 @@ __global__ void __launch_bounds__(FT, 1)
     float inv[3];
 #pragma unroll
     for (int a = 0; a < 3; a++) {
-        lo[a] = warp_min(red[a * NW + lane]);
-        hi[a] = warp_max(red[(3 + a) * NW + lane]);
+        lo[a] = warp_min(red[a * NW + min(lane, NW - 1)]);
+        hi[a] = warp_max(red[(3 + a) * NW + min(lane, NW - 1)]);
         const float ext = hi[a] - lo[a];
         inv[a] = ext > 0.f ? 15.999f / ext : 0.f;
     }
@@ -108,9 +128,10 @@ __global__ void __launch_bounds__(FT, 1)
     for (int i = tid; i < n; i += FT) atomicAdd(&hist[cell_of(pb[(size_t)i * 3], pb[(size_t)i * 3 + 1], pb[(size_t)i * 3 + 2])], 1);
     __syncthreads();
     {
-        int v[4], s = 0;
+        constexpr int CPT = (CELLS + FT - 1) / FT;            // cells per thread
+        int v[CPT], s = 0;
 #pragma unroll
-        for (int u = 0; u < 4; u++) v[u] = hist[4 * tid + u], s += v[u];
+        for (int u = 0; u < CPT; u++) v[u] = (CPT * tid + u < CELLS) ? hist[CPT * tid + u] : 0, s += v[u];
         int incl = s;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -119,7 +140,7 @@ __global__ void __launch_bounds__(FT, 1)
         }
         if (lane == 31) scan_tmp[w] = incl;
         __syncthreads();
-        int wsum = scan_tmp[lane];
+        int wsum = lane < NW ? scan_tmp[lane] : 0;
         int wincl = wsum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -129,7 +150,8 @@ __global__ void __launch_bounds__(FT, 1)
         const int wbase = __shfl_sync(0xffffffffu, wincl - wsum, w);
         int run = wbase + incl - s;
 #pragma unroll
-        for (int u = 0; u < 4; u++) hist[4 * tid + u] = run, run += v[u];
+        for (int u = 0; u < CPT; u++)
+            if (CPT * tid + u < CELLS) hist[CPT * tid + u] = run, run += v[u];
     }
     __syncthreads();
     for (int i = tid; i < n; i += FT) {
@@ -146,16 +168,16 @@ __global__ void __launch_bounds__(FT, 1)
             const float x = sx[32 * b + lane], y = sy[32 * b + lane], z = sz[32 * b + lane];
             const float v[6] = {warp_min(x), warp_min(y), warp_min(z), warp_max(x), warp_max(y), warp_max(z)};
             if (lane == 0) {
-#pragma unroll
-                for (int a = 0; a < 6; a++) bb[a * nslot + slot] = v[a];
-                bmax[slot] = INIT_D;
+                bbq[2 * slot] = make_float4(v[0], v[1], v[2], INIT_D);
+                bbq[2 * slot + 1] = make_float4(v[3], v[4], v[5], 0.f);
             }
             const float m0 = (32 * b + lane < n) ? INIT_D : 0.f;
             if (MD_SMEM) md_s[32 * b + lane] = m0; else mdg[32 * b + lane] = m0;
+            const unsigned o = (32 * b + lane < n) ? so[32 * b + lane] : 0xffffffffu;
+            if (o == __reduce_min_sync(0xffffffffu, o)) wc_o[slot] = o, wc_x[slot] = x, wc_y[slot] = y, wc_z[slot] = z;
         } else if (lane == 0) {
-#pragma unroll
-            for (int a = 0; a < 6; a++) bb[a * nslot + slot] = 0.f;
-            bmax[slot] = 0.f;
+            bbq[2 * slot] = bbq[2 * slot + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            wc_o[slot] = 0xffffffffu, wc_x[slot] = 0.f, wc_y[slot] = 0.f, wc_z[slot] = 0.f;
         }
     }
     float cx = pb[0], cy = pb[1], cz = pb[2];
@@ -164,7 +186,12 @@ __global__ void __launch_bounds__(FT, 1)
 
     // ---- rounds ----
     float* wmax = red;
+#ifdef PF_FPS_TIMING
+    long long tacc_[5] = {0, 0, 0, 0, 0};
+    long long tprev_ = clock64();
+#endif
     for (int s = 0; s + 1 < npoint; s++) {
+        FSTAMP(0);
         // (1) update the buckets whose box is closer to the new sample than their current maximum
         float lane_max = 0.f;
         for (int kbase = 0; kbase < KB; kbase += 32) {
@@ -172,16 +199,18 @@ __global__ void __launch_bounds__(FT, 1)
             bool act = false;
             float bm = 0.f;
             if (k < KB) {
-                bm = bmax[slot];
-                const float ex = fmaxf(fmaxf(bb[slot] - cx, cx - bb[3 * nslot + slot]), 0.f);
-                const float ey = fmaxf(fmaxf(bb[nslot + slot] - cy, cy - bb[4 * nslot + slot]), 0.f);
-                const float ez = fmaxf(fmaxf(bb[2 * nslot + slot] - cz, cz - bb[5 * nslot + slot]), 0.f);
+                const float4 blo = bbq[2 * slot], bhi = bbq[2 * slot + 1];
+                bm = blo.w;
+                const float ex = fmaxf(fmaxf(blo.x - cx, cx - bhi.x), 0.f);
+                const float ey = fmaxf(fmaxf(blo.y - cy, cy - bhi.y), 0.f);
+                const float ez = fmaxf(fmaxf(blo.z - cz, cz - bhi.z), 0.f);
                 act = (ex * ex + ey * ey + ez * ez) * SAFE < bm;
             }
             unsigned mask = __ballot_sync(0xffffffffu, act);
             while (mask) {
                 int kk[4];
                 float px[4], py[4], pz[4];
+                unsigned po[4];
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
                     kk[u] = -1;
@@ -189,7 +218,7 @@ __global__ void __launch_bounds__(FT, 1)
                         kk[u] = __ffs(mask) - 1;
                         mask &= mask - 1;
                         const int p = 32 * (w + NW * (kbase + kk[u])) + lane;
-                        px[u] = sx[p], py[u] = sy[p], pz[u] = sz[p];
+                        px[u] = sx[p], py[u] = sy[p], pz[u] = sz[p], po[u] = so[p];
                     }
                 }
 #pragma unroll
@@ -204,63 +233,78 @@ __global__ void __launch_bounds__(FT, 1)
                         }
                         const float nm = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(m)));
                         if (lane == kk[u]) bm = nm;
+                        const unsigned o = (m == nm) ? po[u] : 0xffffffffu;
+                        if (o == __reduce_min_sync(0xffffffffu, o)) {
+                            const int slot_u = w * KB + kbase + kk[u];
+                            wc_o[slot_u] = o, wc_x[slot_u] = px[u], wc_y[slot_u] = py[u], wc_z[slot_u] = pz[u];
+                        }
                     }
                 }
             }
             if (k < KB) {
-                if (act) bmax[slot] = bm;
+                if (act) bbq[2 * slot].w = bm;
                 lane_max = fmaxf(lane_max, bm);
             }
         }
         const float Mw = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(lane_max)));
         if (lane == 0) wmax[w] = Mw;
+        FSTAMP(1);
         __syncthreads();
+        FSTAMP(2);
         // (2) global maximum; the warp(s) owning a bucket that attains it look inside
-        const float M = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(wmax[lane])));
+        const float M = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(wmax[min(lane, NW - 1)])));
         unsigned best = 0xffffffffu;
         float bx = 0.f, by = 0.f, bz = 0.f;
         if (Mw == M) {
             for (int kbase = 0; kbase < KB; kbase += 32) {
-                const int k = kbase + lane;
-                const bool hit = k < KB && (w + NW * k) < nb && bmax[w * KB + k] == M;
-                unsigned mask = __ballot_sync(0xffffffffu, hit);
-                while (mask) {
-                    const int kk = __ffs(mask) - 1;
-                    mask &= mask - 1;
-                    const int p = 32 * (w + NW * (kbase + kk)) + lane;
-                    const float m = MD_SMEM ? md_s[p] : mdg[p];
-                    unsigned o = 0xffffffffu;
-                    float x = 0.f, y = 0.f, z = 0.f;
-                    if (m == M) o = so[p], x = sx[p], y = sy[p], z = sz[p];
-                    const unsigned omin = __reduce_min_sync(0xffffffffu, o);
-                    if (omin < best) {
-                        const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
-                        best = omin;
-                        bx = __shfl_sync(0xffffffffu, x, src), by = __shfl_sync(0xffffffffu, y, src),
-                        bz = __shfl_sync(0xffffffffu, z, src);
-                    }
+                const int k = kbase + lane, slot = w * KB + k;
+                const bool hit = k < KB && (w + NW * k) < nb && bbq[2 * slot].w == M;
+                const unsigned o = hit ? wc_o[slot] : 0xffffffffu;
+                const unsigned omin = __reduce_min_sync(0xffffffffu, o);
+                if (omin < best) {
+                    const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
+                    const float x = hit ? wc_x[slot] : 0.f, y = hit ? wc_y[slot] : 0.f, z = hit ? wc_z[slot] : 0.f;
+                    best = omin;
+                    bx = __shfl_sync(0xffffffffu, x, src), by = __shfl_sync(0xffffffffu, y, src),
+                    bz = __shfl_sync(0xffffffffu, z, src);
                 }
             }
         }
         if (lane == 0) slots[w].oidx = best, slots[w].x = bx, slots[w].y = by, slots[w].z = bz;
+        FSTAMP(3);
         __syncthreads();
+        FSTAMP(4);
         // (3) the lowest original index among the candidates wins (fps.py: torch.max returns the first maximum)
         {
-            const unsigned o = slots[lane].oidx;
+            const unsigned o = slots[min(lane, NW - 1)].oidx;
             const unsigned omin = __reduce_min_sync(0xffffffffu, o);
             const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
             cx = slots[src].x, cy = slots[src].y, cz = slots[src].z;
             if (tid == 0) out[(size_t)cloud * npoint + s + 1] = (int32_t)omin;
         }
     }
+#ifdef PF_FPS_TIMING
+    if (blockIdx.x == 0 && tid == 0)
+        for (int k = 0; k < 5; k++) g_fps_timing[k] += tacc_[k];
+#endif
 }
 
 }  // namespace
 
+#ifdef PF_FPS_TIMING
+extern "C" __attribute__((visibility("default"))) int pf_fps_timing(long long* host8) {
+    cudaDeviceSynchronize();
+    cudaError_t e = cudaMemcpyFromSymbol(host8, g_fps_timing, sizeof(long long) * 8);
+    long long z[8] = {0};
+    cudaMemcpyToSymbol(g_fps_timing, z, sizeof(z));
+    return (int)e;
+}
+#endif
+
 static int fps_bucket_geometry(int n, int* nb, int* KB, size_t* smem_md, size_t* smem_nomd) {
     *nb = (n + 31) / 32;
     *KB = (*nb + NW - 1) / NW;
-    const size_t meta = (size_t)(7 * NW * *KB + 6 * NW) * 4 + NW * sizeof(Slot) + NW * 4;
+    const size_t meta = (size_t)(12 * NW * *KB + 6 * NW) * 4 + NW * sizeof(Slot) + NW * 4;
     const size_t npad = (size_t)*nb * 32;
     *smem_md = ((npad > (size_t)CELLS ? npad : (size_t)CELLS) * 4) + meta;
     *smem_nomd = (size_t)CELLS * 4 + meta;
