@@ -94,10 +94,11 @@ PF_API int pf_linear_tc(const float* A, int64_t lda, const void* wtc, const floa
 PF_API int pf_edgeconv(const float* pq, const int32_t* idx, const float* wd, const float* wo, float* out, int Bp, int N,
                 int K, int G, int C_out, float slope, void* stream);
 
-/* Tensor-core variant of pf_edgeconv for the compute-bound (G, C_out, K) = (32, 128, 16) blocks: the hidden-channel
+/* Tensor-core variant of pf_edgeconv for K = 16, (G, C_out) in {(8,32), (16,64), (32,128)}: the hidden-channel
  * contractions run on tcgen05.mma (fp16 hi/lo split operands, 3 MMAs per product, fp32 accumulation in TMEM; results
- * are fp32-class, tolerance in tests/test_gpu_kernels.py).  Same pq / idx / out as pf_edgeconv;  wtc: PF_EDGECONV_TC_BLOB
- * bytes of pre-split fp16 weights in the tensor-core shared-memory layout (puflow_b200/packing.py pack_edgeconv_tc). */
+ * are fp32-class, tolerance in tests/test_gpu_kernels.py).  Same pq / idx / out as pf_edgeconv;  wtc: pre-split fp16
+ * weights in the tensor-core operand layout (puflow_b200/packing.py pack_edgeconv_tc), 24 gp^2 + 2048 gp bytes with
+ * gp = max(G, 16): PF_EDGECONV_TC_BLOB for G = 32. */
 #define PF_EDGECONV_TC_BLOB 90112
 PF_API int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K, int G,
                    int C_out, float slope, void* stream);

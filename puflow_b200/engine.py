@@ -53,7 +53,8 @@ class PUFlowEngine:
         f = self.w["feat"][i]
         _, g, Co = FEAT_CFG[i]
         pq = self._linear(c, f, "wpq", f["bpq"])
-        if self.use_tc and "wtc" in f and idx.shape[-1] == K_MAIN:
+        small_ffma = g < 32 and os.environ.get("PUFLOW_EDGECONV_SMALL") == "ffma"     # A/B switch for the (8,32), (16,64) blocks
+        if self.use_tc and idx.shape[-1] == K_MAIN and not small_ffma:
             return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05)
         return ops.edgeconv(pq, idx, f["wd"], f["wo"], Bp, N, g, Co, 0.05)
 

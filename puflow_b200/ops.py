@@ -182,14 +182,14 @@ def edgeconv(pq: torch.Tensor, idx: torch.Tensor, wd: torch.Tensor, wo: torch.Te
 
 def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int, Npts: int, G: int, C_out: int,
                 slope: float = 0.05):
-    """Tensor-core (tcgen05, split-fp16) variant of `edgeconv` for (G, C_out, K) = (32, 128, 16);
-    wtc: uint8[PF_EDGECONV_TC_BLOB] from packing.pack_edgeconv_tc."""
+    """Tensor-core (tcgen05, split-fp16) variant of `edgeconv` for K = 16, (G, C_out) in {(8,32), (16,64), (32,128)};
+    wtc: uint8 blob from packing.pack_edgeconv_tc(wd, wo, G, C_out)."""
     _chk(pq, "pq"), _chk(idx, "idx", torch.int32), _chk(wtc, "wtc", torch.uint8)
     K = idx.shape[-1]
     R = 4 * G + C_out
     if pq.shape != (Bp * Npts, 2 * R) or idx.numel() != Bp * Npts * K:
         raise ValueError(f"edgeconv_tc: pq {tuple(pq.shape)} / idx {tuple(idx.shape)} do not match Bp={Bp} N={Npts} R={R}")
-    if wtc.numel() != N.PF_EDGECONV_TC_BLOB:
+    if wtc.numel() != 24 * max(G, 16) ** 2 + 2048 * max(G, 16):
         raise ValueError("edgeconv_tc: packed weight blob has the wrong size")
     out = torch.empty((Bp * Npts, C_out), dtype=torch.float32, device=pq.device)
     with _dev(pq), _launch(f"edgeconv_tc_g{G}_c{C_out}_k{K}"):

@@ -88,20 +88,41 @@ def umma_kmajor_fp16(mat):
     return lay(hi), lay(lo)
 
 
+def edgeconv_tc_blob_bytes(g: int) -> int:
+    gp = max(g, 16)
+    return 24 * gp * gp + 2 * 128 * 4 * gp * 2
+
+
 def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
-    """(wd, wo) of pack_edgeconv -> uint8[PF_EDGECONV_TC_BLOB] for pf_edgeconv_tc:
-    [W1 hi | W1 lo | W2 hi | W2 lo | W3 hi | W3 lo | Wo hi | Wo lo]; W_l as [g out][g*l in] in the shared-memory
-    operand layout, Wo as plain row-major fp16 [C_out][layers*g] (it is copied to tensor memory, one row per lane)."""
+    """(wd, wo) of pack_edgeconv -> uint8[edgeconv_tc_blob_bytes(g)] for pf_edgeconv_tc, (g, C_out) in
+    {(8, 32), (16, 64), (32, 128)}:  [W1 hi | W1 lo | W2 hi | W2 lo | W3 hi | W3 lo | Wo hi | Wo lo].
+    gp = max(g, 16) is the width of one layer's K slice in the activation operand; for g = 8 hidden channel k of layer j
+    sits at K index j*gp + k and the rest of the slice is zero.  W_l: [gp out][gp*l in] in the shared-memory operand
+    layout; Wo: plain row-major fp16 [128][layers*gp] whose row r is conv_out channel r % C_out (it is copied to tensor
+    memory, one row per lane; the kernel reads channel r % C_out for edge group r // C_out from lane r)."""
+    assert (g, C_out) in ((8, 32), (16, 64), (32, 128)) and layers == 4
+    gp = max(g, 16)
+
+    def pad_k(W, nl):            # [rows, nl*g] -> [rows, nl*gp]
+        out = torch.zeros(W.shape[0], nl * gp, dtype=torch.float64)
+        for j in range(nl):
+            out[:, j * gp:j * gp + g] = W[:, j * g:(j + 1) * g]
+        return out
+
     parts, off = [], 0
     for l in range(1, layers):
-        Wl = wd[off:off + g * l * g].reshape(g * l, g).t()           # [g out, g*l in]
+        Wl = wd[off:off + g * l * g].reshape(g * l, g).t().double()   # [g out, g*l in]
         off += g * l * g
-        parts.extend(umma_kmajor_fp16(Wl.double()))
-    wo32 = wo.t().contiguous().to(torch.float32)                      # [C_out, layers*g]
+        Wp = torch.zeros(gp, l * gp, dtype=torch.float64)
+        Wp[:g] = pad_k(Wl, l)
+        parts.extend(umma_kmajor_fp16(Wp))
+    wo_rows = pad_k(wo.t().double(), layers)                          # [C_out, layers*gp]
+    wo32 = wo_rows.repeat(128 // C_out, 1).contiguous().to(torch.float32)   # row r = channel r % C_out
     wo_hi = wo32.to(torch.float16)
     wo_lo = (wo32 - wo_hi.to(torch.float32)).to(torch.float16)
     parts.extend([wo_hi.contiguous().view(torch.uint8).reshape(-1), wo_lo.contiguous().view(torch.uint8).reshape(-1)])
     blob = torch.cat(parts)
+    assert blob.numel() == edgeconv_tc_blob_bytes(g), blob.numel()
     return blob
 
 
@@ -380,8 +401,7 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
     flows, conds = [], []
     for i, (C, g, Co) in enumerate(FEAT_CFG):
         out["feat"].append(pack_edgeconv(sd, f"feat_convs.{i}", C, g, Co))
-        if (g, Co) == (32, 128):
-            out["feat"][-1]["wtc"] = pack_edgeconv_tc(out["feat"][-1]["wd"], out["feat"][-1]["wo"])
+        out["feat"][-1]["wtc"] = pack_edgeconv_tc(out["feat"][-1]["wd"], out["feat"][-1]["wo"], g, Co)
         if linear_tc_ok(*out["feat"][-1]["wpq"].shape):
             out["feat"][-1]["wpq_tc"] = pack_linear_tc(out["feat"][-1]["wpq"])
         out["merge"].append(dict(

@@ -195,7 +195,8 @@ def test_edgeconv_other_k(ops, dev, packed, K):
     assert ok, err
 
 
-@pytest.mark.parametrize("blk,Bp,N", [(2, 3, 256), (3, 2, 256), (5, 1, 250), (4, 37, 64), (3, 600, 256)])
+@pytest.mark.parametrize("blk,Bp,N", [(2, 3, 256), (3, 2, 256), (5, 1, 250), (4, 37, 64), (3, 600, 256),
+                                      (0, 3, 256), (1, 3, 256), (0, 1, 250), (1, 37, 64), (0, 700, 256), (1, 700, 256)])
 def test_edgeconv_tensor_core(ops, dev, packed, blk, Bp, N):
     """pf_edgeconv_tc (tcgen05, fp16 hi/lo split operands, 3 MMAs per product, fp32 accumulate).
     STATED TOLERANCE: 2e-5 normwise per patch against the float64-accumulated emulation (the split drops the
@@ -230,6 +231,9 @@ def test_edgeconv_tensor_core_rejects_other_shapes(ops, dev, packed):
     idx8 = torch.zeros(1, 256, 8, dtype=torch.int32, device=dev)
     with pytest.raises(Exception):
         ops.edgeconv_tc(pq, idx8, f["wtc"].to(dev), 1, 256, 32, 128)
+    idx16 = torch.zeros(1, 256, 16, dtype=torch.int32, device=dev)
+    with pytest.raises(Exception):       # blob of another block shape
+        ops.edgeconv_tc(pq, idx16, packed["feat"][0]["wtc"].to(dev), 1, 256, 32, 128)
 
 
 # ---- (3) flow --------------------------------------------------------------------------------------
