@@ -14,7 +14,8 @@
 //           whose box is closer than their current maximum (exact: a skipped bucket cannot change);
 //           arg-max = max over bucket maxima, then a look inside the bucket(s) holding the maximum.
 // Running minima live in shared memory (164 KB for 40,960 points), sorted coordinates in an L2-resident scratch.
-// Two __syncthreads per round; no clusters, no cross-CTA traffic.
+// Every bucket caches the point that attains its maximum (lowest original index first), so choosing the next sample is a
+// reduction over per-warp candidates: one __syncthreads per round; no clusters, no cross-CTA traffic.
 #include "common.cuh"
 #include "puflow_b200.h"
 
@@ -61,8 +62,10 @@ __device__ long long g_fps_timing[8];
 #endif
 
 struct Slot {
+    float m;
     unsigned oidx;
     float x, y, z;
+    float pad[3];
 };
 
 // work (per cloud, npad = 32 * nb entries each): sx | sy | sz | oidx | md (md only used when !MD_SMEM)
@@ -94,7 +97,7 @@ __global__ void __launch_bounds__(FT, 1)
     float* wc_z = wc_y + nslot;                                   // needs no trip to L2
     float* red = wc_z + nslot;                             // [6*NW] setup reductions, then wmax[NW]
     Slot* slots = reinterpret_cast<Slot*>(red + 6 * NW);   // [NW]
-    int* scan_tmp = reinterpret_cast<int*>(slots + NW);    // [NW]
+    int* scan_tmp = reinterpret_cast<int*>(slots + 2 * NW);    // [NW]
 
     // ---- setup 1: bounding box of the cloud ----
     float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
@@ -185,7 +188,6 @@ __global__ void __launch_bounds__(FT, 1)
     __syncthreads();
 
     // ---- rounds ----
-    float* wmax = red;
 #ifdef PF_FPS_TIMING
     long long tacc_[5] = {0, 0, 0, 0, 0};
     long long tprev_ = clock64();
@@ -193,7 +195,10 @@ __global__ void __launch_bounds__(FT, 1)
     for (int s = 0; s + 1 < npoint; s++) {
         FSTAMP(0);
         // (1) update the buckets whose box is closer to the new sample than their current maximum
-        float lane_max = 0.f;
+        // every lane also tracks the best bucket it has seen: (max running-min, lowest original index attaining it)
+        float lmax = 0.f;
+        unsigned lo_ = 0xffffffffu;
+        int ls = w * KB;
         for (int kbase = 0; kbase < KB; kbase += 32) {
             const int k = kbase + lane, slot = w * KB + k;
             bool act = false;
@@ -207,6 +212,7 @@ __global__ void __launch_bounds__(FT, 1)
                 act = (ex * ex + ey * ey + ez * ez) * SAFE < bm;
             }
             unsigned mask = __ballot_sync(0xffffffffu, act);
+            const bool any_act = mask != 0;
             while (mask) {
                 int kk[4];
                 float px[4], py[4], pz[4];
@@ -241,45 +247,36 @@ __global__ void __launch_bounds__(FT, 1)
                     }
                 }
             }
+            if (any_act) __syncwarp();                  // winner-cache entries written by other lanes of this warp
             if (k < KB) {
                 if (act) bbq[2 * slot].w = bm;
-                lane_max = fmaxf(lane_max, bm);
+                const unsigned o = wc_o[slot];
+                if (bm > lmax || (bm == lmax && o < lo_)) lmax = bm, lo_ = o, ls = slot;
             }
         }
-        const float Mw = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(lane_max)));
-        if (lane == 0) wmax[w] = Mw;
+        // (2) this warp's candidate -> slots[parity][w]
+        Slot* sl = slots + (s & 1) * NW;
+        {
+            const float Mw = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(lmax)));
+            const unsigned cand = (lmax == Mw) ? lo_ : 0xffffffffu;
+            const unsigned omin = __reduce_min_sync(0xffffffffu, cand);
+            const int src = __ffs(__ballot_sync(0xffffffffu, cand == omin && lmax == Mw)) - 1;
+            if (lane == src) sl[w].m = Mw, sl[w].oidx = omin, sl[w].x = wc_x[ls], sl[w].y = wc_y[ls], sl[w].z = wc_z[ls];
+        }
         FSTAMP(1);
         __syncthreads();
         FSTAMP(2);
-        // (2) global maximum; the warp(s) owning a bucket that attains it look inside
-        const float M = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(wmax[min(lane, NW - 1)])));
-        unsigned best = 0xffffffffu;
-        float bx = 0.f, by = 0.f, bz = 0.f;
-        if (Mw == M) {
-            for (int kbase = 0; kbase < KB; kbase += 32) {
-                const int k = kbase + lane, slot = w * KB + k;
-                const bool hit = k < KB && (w + NW * k) < nb && bbq[2 * slot].w == M;
-                const unsigned o = hit ? wc_o[slot] : 0xffffffffu;
-                const unsigned omin = __reduce_min_sync(0xffffffffu, o);
-                if (omin < best) {
-                    const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
-                    const float x = hit ? wc_x[slot] : 0.f, y = hit ? wc_y[slot] : 0.f, z = hit ? wc_z[slot] : 0.f;
-                    best = omin;
-                    bx = __shfl_sync(0xffffffffu, x, src), by = __shfl_sync(0xffffffffu, y, src),
-                    bz = __shfl_sync(0xffffffffu, z, src);
-                }
-            }
-        }
-        if (lane == 0) slots[w].oidx = best, slots[w].x = bx, slots[w].y = by, slots[w].z = bz;
-        FSTAMP(3);
-        __syncthreads();
-        FSTAMP(4);
-        // (3) the lowest original index among the candidates wins (fps.py: torch.max returns the first maximum)
+        // (3) global maximum; the lowest original index among the points attaining it wins (fps.py: torch.max returns
+        //     the first maximum).  slots are double-buffered by round parity, so one barrier per round suffices.
         {
-            const unsigned o = slots[min(lane, NW - 1)].oidx;
-            const unsigned omin = __reduce_min_sync(0xffffffffu, o);
-            const int src = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;
-            cx = slots[src].x, cy = slots[src].y, cz = slots[src].z;
+            const int l = min(lane, NW - 1);
+            const float mw = sl[l].m;
+            const unsigned ow = sl[l].oidx;
+            const float M = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(mw)));
+            const unsigned cand = (mw == M) ? ow : 0xffffffffu;
+            const unsigned omin = __reduce_min_sync(0xffffffffu, cand);
+            const int src = min(__ffs(__ballot_sync(0xffffffffu, cand == omin && mw == M)) - 1, NW - 1);
+            cx = sl[src].x, cy = sl[src].y, cz = sl[src].z;
             if (tid == 0) out[(size_t)cloud * npoint + s + 1] = (int32_t)omin;
         }
     }
@@ -304,7 +301,7 @@ extern "C" __attribute__((visibility("default"))) int pf_fps_timing(long long* h
 static int fps_bucket_geometry(int n, int* nb, int* KB, size_t* smem_md, size_t* smem_nomd) {
     *nb = (n + 31) / 32;
     *KB = (*nb + NW - 1) / NW;
-    const size_t meta = (size_t)(12 * NW * *KB + 6 * NW) * 4 + NW * sizeof(Slot) + NW * 4;
+    const size_t meta = (size_t)(12 * NW * *KB + 6 * NW) * 4 + 2 * NW * sizeof(Slot) + NW * 4;
     const size_t npad = (size_t)*nb * 32;
     *smem_md = ((npad > (size_t)CELLS ? npad : (size_t)CELLS) * 4) + meta;
     *smem_nomd = (size_t)CELLS * 4 + meta;
