@@ -184,14 +184,17 @@ def algorithmic_work(tag, Bc, npts):
         g, c, k = (int(x[1:]) for x in tag.replace("edgeconv_tc_", "edgeconv_").split("_")[1:4])
         R = 4 * g + c
         return "tensor", 2.0 * (6 * g * g + 4 * g * c) * M * k, "FLOP"          # hidden-channel MACs of the dense block
-    if tag.startswith("linear_k"):
-        K, N = int(tag.split("_")[1][1:]), int(tag.split("_")[2][1:])
+    if tag.startswith("linear_k") or tag.startswith("linear_tc_k"):
+        f = tag.replace("linear_tc_", "linear_").split("_")
+        K, N = int(f[1][1:]), int(f[2][1:])
         return "hbm", M * 4.0 * (K + N), "B"
-    if tag == "flow_cond":
+    if tag.startswith("cond_chain_tc_c"):
+        return "hbm", M * 4.0 * (int(tag.rsplit("_c", 1)[1]) + 64 + 8), "B"
+    if tag in ("flow_cond", "flow_cond_tc"):
         return "hbm", 6 * M * 4.0 * (192 + 8), "B"
-    if tag == "flow_fwd":
+    if tag in ("flow_fwd", "flow_fwd_tc"):
         return "hbm", M * (24 + 4.0 * 6 * (64 + 8)), "B"
-    if tag == "flow_inv":
+    if tag in ("flow_inv", "flow_inv_tc"):
         return "hbm", M * (UP * 24 + 4.0 * 6 * (64 + 8)), "B"
     if tag in ("interp", "interp_tc"):
         return "tensor", 2.0 * 81792 * 8 * M, "FLOP"
