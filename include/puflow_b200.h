@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 2
+#define PF_ABI_VERSION 3
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -182,6 +182,17 @@ PF_API int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, floa
 PF_API long long pf_fps_work_floats(int B, int n);
 PF_API int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
+
+/* ---- on-disk format (host code, no CUDA) ------------------------------------------
+ * The reference reads clouds with np.loadtxt(path, dtype=np.float32) (/root/reference/modules/discrete/upsample.py:42)
+ * and writes them with np.savetxt(path, pred, fmt='%.6f') (:57): whitespace-separated text, one point per line,
+ * '#' comments.  Same values bit for bit (parsed as double, narrowed to float) and the same bytes on output
+ * ('%.6f' of the widened value, ' ' between columns, '\n' after each row).
+ *   pf_xyz_count: number of data lines and columns of the file;  pf_xyz_read: fills out[rows][cols] (HOST memory);
+ *   pf_xyz_write: data[rows][cols] (HOST memory) -> file. */
+PF_API int pf_xyz_count(const char* path, int64_t* rows, int* cols);
+PF_API int pf_xyz_read(const char* path, float* out, int64_t rows, int cols);
+PF_API int pf_xyz_write(const char* path, const float* data, int64_t rows, int cols);
 
 #ifdef __cplusplus
 }

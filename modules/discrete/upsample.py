@@ -19,6 +19,7 @@ from pathlib import Path
 sys.path.append(os.getcwd())
 
 from modules.utils.patch import PatchHelper
+from puflow_b200.xyzio import load_xyz, save_xyz
 from modules.discrete.interpflow import PointInterpFlow
 
 
@@ -50,10 +51,10 @@ def upsampling(data_paths: List[str], target_path: str, checkpoint_path: str, up
     for path in sorted(data_paths)[rank::world] if world > 1 else data_paths:
         _, file_name = os.path.split(path)
 
-        pt_input = np.loadtxt(path, dtype=np.float32)
+        pt_input = load_xyz(path)                       # np.loadtxt(path, dtype=np.float32), upsample.py:42
         pt_input = pt_input[torch.randperm(pt_input.shape[0]).numpy()]
         pred = upsample_array(network, patch_helper, pt_input[None], up_ratio, num_outlier, num_upsampling, device)
-        np.savetxt(Path(target_path) / file_name, pred[0], fmt='%.6f')
+        save_xyz(Path(target_path) / file_name, pred[0])  # np.savetxt(..., fmt='%.6f'), upsample.py:57
 
 
 # -----------------------------------------------------------------------------------------

@@ -41,6 +41,9 @@ SIGNATURES = {
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_bucketed": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_knn_patch": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "pf_xyz_count": [ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int)],
+    "pf_xyz_read": [ctypes.c_char_p, _vp, _i64, _i],
+    "pf_xyz_write": [ctypes.c_char_p, _vp, _i64, _i],
 }
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)
@@ -51,7 +54,7 @@ lib.pf_fps_work_floats.restype = ctypes.c_longlong
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 2
+PF_ABI_VERSION = 3
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
 PF_COND_TC_BLOCK = 35360
