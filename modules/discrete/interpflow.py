@@ -380,7 +380,12 @@ class PointInterpFlow(nn.Module):
 
     def forward(self, xyz: Tensor, upratio=4):
         xyz = check_input(xyz, "PointInterpFlow")
-        return self.engine(xyz.device).forward(xyz, upratio)
+        eng = self.engine(xyz.device)
+        # PUFLOW_CUDA_GRAPH=1: replay the launch sequence from a CUDA graph captured per input shape (same result;
+        # for small batches the ~100 launches of a call, not the kernels, bound the latency)
+        if os.environ.get("PUFLOW_CUDA_GRAPH") == "1" and not torch.is_grad_enabled():
+            return eng.forward_graphed(xyz, upratio)
+        return eng.forward(xyz, upratio)
 
     def log_prob(self, xyz: Tensor, cs: List[Tensor]):
         xyz = check_input(xyz, "PointInterpFlow.log_prob")

@@ -27,6 +27,8 @@ LOG_2PI = math.log(2.0 * math.pi)
 
 
 class PUFlowEngine:
+    MAX_GRAPHS = 4
+
     def __init__(self, state_dict: Dict[str, torch.Tensor], device):
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -37,6 +39,7 @@ class PUFlowEngine:
         self.use_tc = os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma"
         # same switch for the flow stack (PUFLOW_FLOW=ffma keeps flow.cu's FP32 kernels)
         self.flow_tc = self.use_tc and os.environ.get("PUFLOW_FLOW", "tc") != "ffma"
+        self._graphs = {}                                # (shape, upratio) -> captured CUDA graph, see forward_graphed
 
     def _linear(self, a, wd, name, bias=None, act=ACT_NONE):
         """Per-point linear layer: tensor-core kernel when a packed blob exists (K in {16..128}), FFMA otherwise."""
@@ -160,3 +163,41 @@ class PUFlowEngine:
 
     def sample(self, xyz: torch.Tensor, upratio: int = 4):
         return self.forward(xyz, upratio)[0]
+
+    # ---- CUDA-graph replay of the whole path ---------------------------------------
+    @torch.no_grad()
+    def forward_graphed(self, xyz: torch.Tensor, upratio: int = 4):
+        """Same result as forward(), bit for bit, with the ~30 kernel launches + tensor plumbing of one call replayed
+        from a CUDA graph captured per (shape, upratio): for small batches (one 2,048-pt cloud = 32 patches) the
+        launch sequence, not the kernels, bounds the latency.  Inputs are copied into the graph's static buffer and
+        the outputs cloned out, so callers see ordinary tensors.  At most MAX_GRAPHS shapes are kept (LRU)."""
+        xyz = xyz.contiguous().float()
+        key = (tuple(xyz.shape), int(upratio))
+        ent = self._graphs.pop(key, None)
+        if ent is None:
+            static_in = xyz.clone()
+            cur = torch.cuda.current_stream(self.device)
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(cur)
+            prev = ops.set_launch_log(None)              # no event records inside warm-up / capture
+            try:
+                with torch.cuda.stream(side):
+                    for _ in range(2):                   # lazy initialisation (smem opt-ins, allocator) before capture
+                        self.forward(static_in, upratio)
+                cur.wait_stream(side)
+                counter = ops.LaunchLog(events=False)
+                ops.set_launch_log(counter)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    x, logp = self.forward(static_in, upratio)
+            finally:
+                ops.set_launch_log(prev)
+            ent = (graph, static_in, x, logp, counter.count)
+            while len(self._graphs) >= self.MAX_GRAPHS:
+                self._graphs.pop(next(iter(self._graphs)))
+        self._graphs[key] = ent                          # most recently used last
+        graph, static_in, x, logp, n_launch = ent
+        static_in.copy_(xyz)
+        graph.replay()
+        ops.count_launches(n_launch)
+        return x.clone(), logp.clone()

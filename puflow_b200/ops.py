@@ -38,6 +38,12 @@ def set_launch_log(log):
     return prev
 
 
+def count_launches(n: int):
+    """Account for `n` kernels launched outside the wrappers below (a CUDA-graph replay)."""
+    if _log is not None:
+        _log.count += n
+
+
 class _launch:
     def __init__(self, tag: str, n: int = 1):
         self.tag, self.n = tag, n
