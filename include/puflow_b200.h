@@ -103,6 +103,18 @@ PF_API int pf_edgeconv(const float* pq, const int32_t* idx, const float* wd, con
 PF_API int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K, int G,
                    int C_out, float slope, void* stream);
 
+/* Pre-split activations.  pf_edgeconv_tc_split is pf_edgeconv_tc that ALSO (or only: out may be NULL) writes its output as
+ * fp16 hi/lo in the tile-blocked tensor-core operand layout: out_split holds ceil(Bp*N / 128) tiles of
+ * PF_SPLIT_TILE_BYTES(C_out) bytes; within a tile hi(r, k) at (k/8)*2048 + r*16 + (k%8)*2, lo at C_out*256 + the same.
+ * pf_linear_tc_split is pf_linear_tc for an input in that layout (K = its channel count, 32 / 64 / 128): a tile is one
+ * TMA bulk copy straight into the MMA operand, no conversion pass (the next block's P|Q projection).  a_split must be
+ * 128-byte aligned, out 32-byte aligned, ldo a multiple of 8. */
+#define PF_SPLIT_TILE_BYTES(K) (512 * (K))
+PF_API int pf_edgeconv_tc_split(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
+                         int N, int K, int G, int C_out, float slope, void* stream);
+PF_API int pf_linear_tc_split(const void* a_split, const void* wtc, const float* bias, float* out, int64_t ldo, int64_t M,
+                       int K, int N, int act, float slope, void* stream);
+
 /* ---- (3) flow stack ---------------------------------------------------------------------------------
  * FlowBlock.forward / inverse x6 (/root/reference/modules/discrete/interpflow.py:66-82,302-321):
  * ActNorm (modules/flows/normalize.py:30-43), InvertibleConv1x1_1D (permutate.py:117-126), additive

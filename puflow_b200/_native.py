@@ -29,6 +29,8 @@ SIGNATURES = {
     "pf_linear_tc": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
     "pf_edgeconv": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
     "pf_edgeconv_tc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
+    "pf_edgeconv_tc_split": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
+    "pf_linear_tc_split": [_vp, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
     "pf_flow_cond": [_vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],

@@ -72,7 +72,8 @@ struct Cfg {
 template <int G, int CO, int NWG>
 __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
     edgeconv_tc_kernel(const float* __restrict__ pq, const int32_t* __restrict__ idx, const uint8_t* __restrict__ wblob,
-                       float* __restrict__ out, int N, int tiles_per_patch, long long total_tiles, float slope) {
+                       float* __restrict__ out, uint8_t* __restrict__ out_split, int N, int tiles_per_patch,
+                       long long total_tiles, float slope) {
     using C = Cfg<G, CO, NWG>;
     constexpr int GP = C::GP, R = C::R, R2 = C::R2, KT = C::KT, QCH = C::QCH;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -354,6 +355,10 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
             };
             load_qchunk(0, qva);
             if (NCH > 1) load_qchunk(1, qvb);
+            float pv[2 * NCH];                                            // conv_out P term of this thread's points
+#pragma unroll
+            for (int i = 0; i < 2 * NCH; i++)
+                pv[i] = __ldg(ppq + (size_t)min(p0 + 2 * grp * NCH + i, N - 1) * R2 + 4 * G + ch);
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
@@ -372,7 +377,19 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
 #pragma unroll
                     for (int u = 1; u < 16; u++) m = fmaxf(m, acc[16 * h + u]);
                     const int pp = p0 + 2 * (grp * NCH + c) + h;
-                    if (pp < N) out[((size_t)patch * N + pp) * CO + ch] = m + __ldg(ppq + (size_t)pp * R2 + 4 * G + ch);
+                    if (pp < N) {
+                        const float val = m + pv[2 * c + h];
+                        const size_t grow = (size_t)patch * N + pp;
+                        if (out) out[grow * CO + ch] = val;
+                        if (out_split) {   // fp16 hi/lo in the tile-blocked operand layout of linear_split.cu (K = CO)
+                            uint32_t hi, lo;
+                            tc::split2(val, 0.f, hi, lo);
+                            uint8_t* tile = out_split + (grow >> 7) * (size_t)(CO * 512) + (size_t)(ch >> 3) * 2048 +
+                                            (grow & 127) * 16 + (ch & 7) * 2;
+                            *reinterpret_cast<uint16_t*>(tile) = (uint16_t)(hi & 0xffffu);
+                            *reinterpret_cast<uint16_t*>(tile + CO * 256) = (uint16_t)(lo & 0xffffu);
+                        }
+                    }
                 }
             }
         }
@@ -388,7 +405,8 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
 }
 
 template <int G, int CO, int NWG>
-int launch(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, float slope, cudaStream_t st) {
+int launch(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp, int N, float slope,
+           cudaStream_t st) {
     using C = Cfg<G, CO, NWG>;
     auto kern = edgeconv_tc_kernel<G, CO, NWG>;
     if (int rc = pf_smem_optin(kern, C::SMEM_BYTES)) return rc;
@@ -399,28 +417,38 @@ int launch(const float* pq, const int32_t* idx, const void* wtc, float* out, int
     PF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const long long want = (total + NWG - 1) / NWG;
     const int grid = (int)(want < sms ? want : sms);
-    kern<<<grid, C::NT, C::SMEM_BYTES, st>>>(pq, idx, static_cast<const uint8_t*>(wtc), out, N, tiles_per_patch, total,
-                                             slope);
+    kern<<<grid, C::NT, C::SMEM_BYTES, st>>>(pq, idx, static_cast<const uint8_t*>(wtc), out, static_cast<uint8_t*>(out_split),
+                                             N, tiles_per_patch, total, slope);
     return pf_launch_status("edgeconv_tc_kernel");
 }
 
 }  // namespace
 
-extern "C" int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K,
-                              int G_, int C_out, float slope, void* stream) {
+static int edgeconv_tc_dispatch(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
+                                int N, int K, int G_, int C_out, float slope, void* stream) {
     PF_CHECK_ARG(Bp >= 0 && N > 0, "pf_edgeconv_tc: bad sizes Bp=%d N=%d", Bp, N);
     if (Bp == 0) return 0;
-    PF_CHECK_ARG(pq && idx && wtc && out, "pf_edgeconv_tc: null pointer");
+    PF_CHECK_ARG(pq && idx && wtc && (out || out_split), "pf_edgeconv_tc: null pointer");
     PF_CHECK_ARG((long long)Bp * N < 0x7fffffffLL, "pf_edgeconv_tc: Bp*N overflows int32");
     PF_CHECK_ARG(N <= 65536, "pf_edgeconv_tc: N=%d > 65536 points per patch", N);
     PF_CHECK_ARG(K == KN, "pf_edgeconv_tc: K=%d, only K = 16", K);
-    PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(pq) | reinterpret_cast<uintptr_t>(wtc) | reinterpret_cast<uintptr_t>(out)) &
-                  15) == 0,
+    PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(pq) | reinterpret_cast<uintptr_t>(wtc) | reinterpret_cast<uintptr_t>(out) |
+                   reinterpret_cast<uintptr_t>(out_split)) & 15) == 0,
                  "pf_edgeconv_tc: pointers must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    if (G_ == 32 && C_out == 128) return launch<32, 128, 2>(pq, idx, wtc, out, Bp, N, slope, st);
-    if (G_ == 16 && C_out == 64) return launch<16, 64, 3>(pq, idx, wtc, out, Bp, N, slope, st);
-    if (G_ == 8 && C_out == 32) return launch<8, 32, 3>(pq, idx, wtc, out, Bp, N, slope, st);
+    if (G_ == 32 && C_out == 128) return launch<32, 128, 2>(pq, idx, wtc, out, out_split, Bp, N, slope, st);
+    if (G_ == 16 && C_out == 64) return launch<16, 64, 3>(pq, idx, wtc, out, out_split, Bp, N, slope, st);
+    if (G_ == 8 && C_out == 32) return launch<8, 32, 3>(pq, idx, wtc, out, out_split, Bp, N, slope, st);
     PF_CHECK_ARG(false, "pf_edgeconv_tc: (G, C_out) = (%d, %d) not in {(8,32), (16,64), (32,128)}", G_, C_out);
     return 0;
+}
+
+extern "C" int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K,
+                              int G_, int C_out, float slope, void* stream) {
+    return edgeconv_tc_dispatch(pq, idx, wtc, out, nullptr, Bp, N, K, G_, C_out, slope, stream);
+}
+
+extern "C" int pf_edgeconv_tc_split(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
+                                    int N, int K, int G_, int C_out, float slope, void* stream) {
+    return edgeconv_tc_dispatch(pq, idx, wtc, out, out_split, Bp, N, K, G_, C_out, slope, stream);
 }

@@ -51,14 +51,21 @@ class PUFlowEngine:
     def knn(self, xyz: torch.Tensor, K: int = K_MAIN):
         return ops.knn_topk(xyz, xyz, K, return_dist=False)[1]
 
-    def edgeconv_block(self, i: int, c: torch.Tensor, idx: torch.Tensor, Bp: int, N: int):
-        """FeatureExtractUnit i on c[Bp*N, C_in] -> [Bp*N, C_out]."""
+    def edgeconv_block(self, i: int, c: torch.Tensor, idx: torch.Tensor, Bp: int, N: int, split_in=None, split_out=None):
+        """FeatureExtractUnit i on c[Bp*N, C_in] -> [Bp*N, C_out].  split_in: the same input pre-split in the operand
+        layout (written by the previous block, ops.split_tiles) -- the P|Q projection then runs TMA-fed with no conversion
+        pass; split_out: buffer that receives this block's output pre-split for the next block."""
         f = self.w["feat"][i]
-        _, g, Co = FEAT_CFG[i]
-        pq = self._linear(c, f, "wpq", f["bpq"])
+        Cin, g, Co = FEAT_CFG[i]
         small_ffma = g < 32 and os.environ.get("PUFLOW_EDGECONV_SMALL") == "ffma"     # A/B switch for the (8,32), (16,64) blocks
-        if self.use_tc and idx.shape[-1] == K_MAIN and not small_ffma:
-            return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05)
+        tc = self.use_tc and idx.shape[-1] == K_MAIN and not small_ffma
+        if split_in is not None and "wpq_tc" in f:
+            pq = ops.linear_tc_split(split_in, Bp * N, Cin, f["wpq_tc"], f["wpq"].shape[1], f["bpq"])
+        else:
+            pq = self._linear(c, f, "wpq", f["bpq"])
+        if tc:
+            return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05, split=split_out)
+        assert split_out is None
         return ops.edgeconv(pq, idx, f["wd"], f["wo"], Bp, N, g, Co, 0.05)
 
     def merge(self, i: int, c: torch.Tensor):
@@ -88,8 +95,13 @@ class PUFlowEngine:
         sb = torch.empty((NUM_BLOCKS, M, 8), dtype=torch.float32, device=self.device)
         c = xyz.reshape(M, 3)
         feats, cs = [], ([] if want_cs else None)
+        presplit = idx.shape[-1] == K_MAIN and os.environ.get("PUFLOW_PRESPLIT", "1") != "0" and \
+            os.environ.get("PUFLOW_EDGECONV_SMALL") != "ffma"
+        split = None
         for i in range(NUM_BLOCKS):
-            c = self.edgeconv_block(i, c, idx, Bp, N)
+            nxt = ops.split_tiles(M, FEAT_CFG[i][2], self.device) if presplit and i + 1 < NUM_BLOCKS else None
+            c = self.edgeconv_block(i, c, idx, Bp, N, split_in=split, split_out=nxt)
+            split = nxt
             feats.append(c.view(Bp, N, -1))
             ops.cond_chain(c, self.w["chain_tc"][i], raw1[i], sb[i])
             if want_cs:

@@ -186,8 +186,30 @@ def edgeconv(pq: torch.Tensor, idx: torch.Tensor, wd: torch.Tensor, wo: torch.Te
     return out
 
 
+def split_tiles(M: int, K: int, device):
+    """Uninitialised buffer for M rows of K channels in the pre-split operand layout (ceil(M/128) tiles of 512 K bytes)."""
+    return torch.empty(((M + 127) // 128, 512 * K), dtype=torch.uint8, device=device)
+
+
+def linear_tc_split(a_split: torch.Tensor, M: int, K: int, wtc: torch.Tensor, Nout: int, bias=None, act: int = N.ACT_NONE,
+                    slope: float = 0.0):
+    """out[M, Nout] = act(A . W + bias) for A given pre-split (split_tiles layout, written by edgeconv_tc(split=...))."""
+    _chk(a_split, "a_split", torch.uint8), _chk(wtc, "wtc", torch.uint8)
+    if a_split.numel() != ((M + 127) // 128) * 512 * K or K not in (32, 64, 128) or Nout % 16:
+        raise ValueError("linear_tc_split: bad shapes")
+    if wtc.numel() != ((Nout + 127) // 128) * 128 * K * 4:
+        raise ValueError("linear_tc_split: packed weight blob has the wrong size")
+    if bias is not None:
+        _chk(bias, "bias")
+    out = torch.empty((M, Nout), dtype=torch.float32, device=a_split.device)
+    with _dev(a_split), _launch(f"linear_split_k{K}_n{Nout}"):
+        N.check(lib.pf_linear_tc_split(a_split.data_ptr(), wtc.data_ptr(), bias.data_ptr() if bias is not None else None,
+                                       out.data_ptr(), Nout, M, K, Nout, act, float(slope), _stream()), "pf_linear_tc_split")
+    return out
+
+
 def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int, Npts: int, G: int, C_out: int,
-                slope: float = 0.05):
+                slope: float = 0.05, split: torch.Tensor = None):
     """Tensor-core (tcgen05, split-fp16) variant of `edgeconv` for K = 16, (G, C_out) in {(8,32), (16,64), (32,128)};
     wtc: uint8 blob from packing.pack_edgeconv_tc(wd, wo, G, C_out)."""
     _chk(pq, "pq"), _chk(idx, "idx", torch.int32), _chk(wtc, "wtc", torch.uint8)
@@ -198,9 +220,14 @@ def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int,
     if wtc.numel() != 24 * max(G, 16) ** 2 + 2048 * max(G, 16):
         raise ValueError("edgeconv_tc: packed weight blob has the wrong size")
     out = torch.empty((Bp * Npts, C_out), dtype=torch.float32, device=pq.device)
+    if split is not None:       # also write the output pre-split (split_tiles(Bp * Npts, C_out)) for linear_tc_split
+        _chk(split, "split", torch.uint8)
+        if split.numel() != ((Bp * Npts + 127) // 128) * 512 * C_out:
+            raise ValueError("edgeconv_tc: split buffer has the wrong size")
     with _dev(pq), _launch(f"edgeconv_tc_g{G}_c{C_out}_k{K}"):
-        N.check(lib.pf_edgeconv_tc(pq.data_ptr(), idx.data_ptr(), wtc.data_ptr(), out.data_ptr(), Bp, Npts, K, G, C_out,
-                                   float(slope), _stream()), "pf_edgeconv_tc")
+        N.check(lib.pf_edgeconv_tc_split(pq.data_ptr(), idx.data_ptr(), wtc.data_ptr(), out.data_ptr(),
+                                         split.data_ptr() if split is not None else None, Bp, Npts, K, G, C_out,
+                                         float(slope), _stream()), "pf_edgeconv_tc")
     return out
 
 

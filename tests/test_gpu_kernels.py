@@ -236,6 +236,58 @@ def test_edgeconv_tensor_core_rejects_other_shapes(ops, dev, packed):
         ops.edgeconv_tc(pq, idx16, packed["feat"][0]["wtc"].to(dev), 1, 256, 32, 128)
 
 
+def _split_ref(x):
+    """[M, K] fp32 -> uint8 tiles in the pre-split operand layout (include/puflow_b200.h, PF_SPLIT_TILE_BYTES)."""
+    M, K = x.shape
+    T = (M + 127) // 128
+    xp = torch.zeros(T * 128, K)
+    xp[:M] = x.clamp(-65000.0, 65000.0)
+    hi = xp.to(torch.float16)
+    lo = (xp - hi.float()).to(torch.float16)
+
+    def lay(h):     # [T*128, K] -> [T][K/8][128][8]
+        return h.view(T, 128, K // 8, 8).permute(0, 2, 1, 3).contiguous().view(T, -1)
+    return torch.cat([lay(hi), lay(lo)], 1).contiguous().view(torch.uint8).view(T, 512 * K)
+
+
+@pytest.mark.parametrize("M,K,N,act", [(1000, 128, 512, 0), (300, 64, 512, 2), (129, 32, 256, 1), (128, 128, 16, 0),
+                                       (40000, 128, 512, 0), (5000, 64, 48, 0)])
+def test_linear_tensor_core_presplit(ops, dev, M, K, N, act):
+    """pf_linear_tc_split (TMA-fed, input pre-split in the operand layout) is bit-identical to pf_linear_tc on the same
+    values: same hi/lo operands, same MMA order."""
+    from puflow_b200.packing import pack_linear_tc
+    gen = torch.Generator().manual_seed(M + K + N)
+    a = torch.randn(M, K, generator=gen) * 3
+    W = torch.randn(K, N, generator=gen) / K ** 0.5
+    b = torch.randn(N, generator=gen)
+    wtc = pack_linear_tc(W).to(dev)
+    ref = ops.linear_tc(a.to(dev), wtc, N, b.to(dev), act, 0.05)
+    got = ops.linear_tc_split(_split_ref(a).to(dev), M, K, wtc, N, b.to(dev), act, 0.05)
+    assert torch.equal(ref, got)
+    got2 = ops.linear_tc_split(_split_ref(a).to(dev), M, K, wtc, N, None, 0)
+    ref2 = ops.linear_tc(a.to(dev), wtc, N, None, 0)
+    assert torch.equal(ref2, got2)
+
+
+@pytest.mark.parametrize("blk,Bp,N", [(0, 3, 256), (1, 5, 256), (3, 2, 256), (4, 3, 250)])
+def test_edgeconv_presplit_output(ops, dev, packed, blk, Bp, N):
+    """pf_edgeconv_tc_split writes the same values twice: fp32 rows and fp16 hi/lo tiles in the operand layout."""
+    from puflow_b200.packing import FEAT_CFG
+    C, g, Co = FEAT_CFG[blk]
+    gen = torch.Generator().manual_seed(blk)
+    x = torch.randn(Bp * N, C, generator=gen)
+    p = synth.make_patches(Bp, N, seed=blk, shape="uniform")
+    idx = torch.from_numpy(po.knn(p, p, 16)[1]).int()
+    f = packed["feat"][blk]
+    pq = emulate.linear(x, f["wpq"], f["bpq"]).to(dev)
+    split = ops.split_tiles(Bp * N, Co, dev)
+    split.zero_()
+    out = ops.edgeconv_tc(pq, idx.to(dev), f["wtc"].to(dev), Bp, N, g, Co, split=split)
+    plain = ops.edgeconv_tc(pq, idx.to(dev), f["wtc"].to(dev), Bp, N, g, Co)
+    assert torch.equal(out, plain)
+    assert torch.equal(split.cpu(), _split_ref(out.cpu()))
+
+
 # ---- (3) flow --------------------------------------------------------------------------------------
 def _flow_inputs(packed, M, seed):
     gen = torch.Generator().manual_seed(seed)
