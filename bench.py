@@ -204,7 +204,7 @@ def algorithmic_work(tag, Bc, npts):
     if tag == "knn_patch":
         return "hbm", Bc * (npts * 12.0 + n_patch * (12 + 4 * PATCH)), "B"
     if tag == "chamfer_nn":
-        return "hbm", Bc * (npts * (UP + 1) + N_OUTLIER) * 20.0, "B"
+        return "hbm", Bc * ((npts * UP + N_OUTLIER) * 20.0 + npts * 12.0), "B"       # a -> b direction only
     return "hbm", 0.0, "B"
 
 

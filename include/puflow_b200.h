@@ -62,7 +62,7 @@ PF_API int pf_knn_topk(const float* q, const float* p, int B, int nq, int np, in
  * Replaces chamfer_3D.forward / NmDistanceKernel,
  * /root/reference/metric/PyTorchCD/chamfer3D/chamfer3D.cu:12-154 (both directions, one call).
  * a[B][n][3], b[B][m][3] -> dist1[B][n], idx1[B][n] (nearest in b), dist2[B][m], idx2[B][m]
- * (nearest in a); squared distances; the lowest index wins ties (strict <, chamfer3D.cu:36-69,126). */
+ * (nearest in a); squared distances; the lowest index wins ties (strict <, chamfer3D.cu:36-69,126).  dist2 and idx2 may both be NULL: only the a -> b direction is computed. */
 PF_API int pf_chamfer_nn(const float* a, int n, const float* b, int m, int B, float* dist1, int32_t* idx1, float* dist2,
                   int32_t* idx2, void* stream);
 

@@ -163,7 +163,7 @@ class PatchHelper(object):
         """Drop the num_outliers generated points farthest from the input, keeping the survivors' order;
         reference patch.py:198-214 with chamfer_3DDist -> pf_chamfer_nn."""
         (B, N, _), device = sr.shape, sr.device
-        dist1, _, _, _ = ops.chamfer_nn(sr.contiguous().float(), lr.contiguous().float())
+        dist1, _, _, _ = ops.chamfer_nn(sr.contiguous().float(), lr.contiguous().float(), both=False)
         idx_dist1 = torch.argsort(dist1, dim=-1, descending=True, stable=True)
         idx_outliers = idx_dist1[:, :num_outliers]
         idxb = torch.arange(B, device=device).view(-1, 1)

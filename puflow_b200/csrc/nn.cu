@@ -137,11 +137,11 @@ extern "C" int pf_knn_topk(const float* q, const float* p, int B, int nq, int np
 
 extern "C" int pf_chamfer_nn(const float* a, int n, const float* b, int m, int B, float* dist1, int32_t* idx1,
                              float* dist2, int32_t* idx2, void* stream) {
-    PF_CHECK_ARG(a && b && dist1 && idx1 && dist2 && idx2, "pf_chamfer_nn: null pointer");
+    PF_CHECK_ARG(a && b && dist1 && idx1 && (!dist2 == !idx2), "pf_chamfer_nn: null pointer");
     PF_CHECK_ARG(B >= 0 && n > 0 && m > 0 && B <= 65535, "pf_chamfer_nn: bad sizes B=%d n=%d m=%d", B, n, m);
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int rc = launch_knn<1>(a, b, B, n, m, 1, idx1, dist1, st);
-    if (rc) return rc;
+    if (rc || !dist2) return rc;          // dist2 == idx2 == NULL: a -> b direction only (what remove_outliers consumes)
     return launch_knn<1>(b, a, B, m, n, 1, idx2, dist2, st);
 }

@@ -107,21 +107,23 @@ def knn_topk(q: torch.Tensor, p: torch.Tensor, K: int, return_dist: bool = True)
 
 
 # ---- (5) Chamfer ---------------------------------------------------------------------------------
-def chamfer_nn(a: torch.Tensor, b: torch.Tensor):
+def chamfer_nn(a: torch.Tensor, b: torch.Tensor, both: bool = True):
     """a[B,n,3], b[B,m,3] -> (dist1[B,n], dist2[B,m], idx1 int32, idx2 int32); chamfer_3DDist forward
-    (metric/PyTorchCD/chamfer3D/dist_chamfer_3D.py:29-81)."""
+    (metric/PyTorchCD/chamfer3D/dist_chamfer_3D.py:29-81).  both=False computes the a -> b direction only
+    (dist2 / idx2 are None): PatchHelper.remove_outliers reads nothing else (patch.py:201-203)."""
     _chk(a, "a"), _chk(b, "b")
     if a.dim() != 3 or b.dim() != 3 or a.shape[2] != 3 or b.shape[2] != 3 or a.shape[0] != b.shape[0]:
         raise ValueError(f"chamfer_nn: expected a[B,n,3], b[B,m,3]; got {tuple(a.shape)}, {tuple(b.shape)}")
     B, n, _ = a.shape
     m = b.shape[1]
     d1 = torch.empty((B, n), dtype=torch.float32, device=a.device)
-    d2 = torch.empty((B, m), dtype=torch.float32, device=a.device)
+    d2 = torch.empty((B, m), dtype=torch.float32, device=a.device) if both else None
     i1 = torch.empty((B, n), dtype=torch.int32, device=a.device)
-    i2 = torch.empty((B, m), dtype=torch.int32, device=a.device)
-    with _dev(a), _launch("chamfer_nn", 2):
-        N.check(lib.pf_chamfer_nn(a.data_ptr(), n, b.data_ptr(), m, B, d1.data_ptr(), i1.data_ptr(), d2.data_ptr(),
-                                  i2.data_ptr(), _stream()), "pf_chamfer_nn")
+    i2 = torch.empty((B, m), dtype=torch.int32, device=a.device) if both else None
+    with _dev(a), _launch("chamfer_nn", 2 if both else 1):
+        N.check(lib.pf_chamfer_nn(a.data_ptr(), n, b.data_ptr(), m, B, d1.data_ptr(), i1.data_ptr(),
+                                  d2.data_ptr() if both else None, i2.data_ptr() if both else None, _stream()),
+                "pf_chamfer_nn")
     return d1, d2, i1, i2
 
 
