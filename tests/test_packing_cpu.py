@@ -62,3 +62,60 @@ def test_flow_blocks_match_reference_layers(golden, state_dict):
         assert ok, (bi, "inv", err)
         back = emulate.flow_inv(y, raw, sb, w["flow"][bi:bi + 1], 1)
         assert (back - x).abs().max() < 1e-5
+
+
+# ---- tensor-core blobs: decode the operand layout on the CPU and compare with the float64 source ---------------
+def _umma_decode(buf, rows, Kt):
+    """inverse of packing.umma_kmajor_fp16's layout: uint8 -> [rows, Kt] float32 (one part)."""
+    h = buf.view(torch.float16).view(rows // 8, Kt // 8, 8, 8).permute(0, 2, 1, 3).reshape(rows, Kt)
+    return h.float()
+
+
+def test_tensor_core_blobs_decode_to_the_weights(state_dict):
+    w = packing.pack_state_dict(state_dict, "cpu")
+    from puflow_b200 import _native as N
+    # flow: W2 hi + lo == W2 to fp16-pair precision; fp32 tail is the head of the fp32 blob
+    for i in range(6):
+        b = w["flow_tc"][i]
+        assert b.numel() == N.PF_FLOW_TC_BLOCK
+        W2 = w["flow"][i][384:4480].view(64, 64).t()
+        dec = _umma_decode(b[:8192], 64, 64) + _umma_decode(b[8192:16384], 64, 64)
+        assert (dec - W2).abs().max() <= 2.0 ** -21 * W2.abs().max()
+        assert torch.equal(b[16384:].view(torch.float32), w["flow"][i][:384])
+        c = w["cond_tc"][i]
+        assert c.numel() == N.PF_COND_TC_BLOCK
+        assert torch.equal(c[32768:].view(torch.float32), w["cond"][i][8192:])
+    # chain: composed layer W2c = (conv2^T . wc)^T
+    for i, (C, g, Co) in enumerate(packing.FEAT_CFG):
+        b = w["chain_tc"][i]
+        assert b.numel() == N.chain_tc_bytes(Co)
+        H1 = Co // 2
+        W1 = state_dict[f"merge_convs.{i}.conv1.weight"].double()
+        dec = _umma_decode(b[:Co * Co], H1, Co) + _umma_decode(b[Co * Co:2 * Co * Co], H1, Co)
+        assert (dec.double() - W1).abs().max() <= 2.0 ** -21 * W1.abs().max()
+        W2c = (w["wc"][i].double().t() @ state_dict[f"merge_convs.{i}.conv2.weight"].double())
+        o = 2 * Co * Co
+        dec = _umma_decode(b[o:o + 192 * Co], 192, H1) + _umma_decode(b[o + 192 * Co:o + 384 * Co], 192, H1)
+        assert (dec.double() - W2c).abs().max() <= 1e-6 * W2c.abs().max()
+    # EdgeConv: K slices padded to 16 for g = 8, Wo rows repeated for C_out < 128
+    for i, (C, g, Co) in enumerate(packing.FEAT_CFG):
+        f = w["feat"][i]
+        gp = max(g, 16)
+        assert f["wtc"].numel() == packing.edgeconv_tc_blob_bytes(g)
+        off, woff = 0, 0
+        for l in range(1, 4):
+            part = 2 * gp * gp * l
+            dec = _umma_decode(f["wtc"][off:off + part], gp, gp * l) + _umma_decode(f["wtc"][off + part:off + 2 * part], gp, gp * l)
+            Wl = f["wd"][woff:woff + g * l * g].view(g * l, g).t()
+            woff += g * l * g
+            for j in range(l):
+                assert (dec[:g, j * gp:j * gp + g] - Wl[:, j * g:(j + 1) * g]).abs().max() <= 2.0 ** -21 * Wl.abs().max()
+                assert (dec[:g, j * gp + g:(j + 1) * gp] == 0).all() and (dec[g:] == 0).all()
+            off += 2 * part
+        KT = 4 * gp
+        hi = f["wtc"][off:off + 128 * KT * 2].view(torch.float16).view(128, KT).float()
+        lo = f["wtc"][off + 128 * KT * 2:].view(torch.float16).view(128, KT).float()
+        wo = f["wo"].t()                                               # [C_out, 4g]
+        for r in (0, Co - 1, Co % 128, 127):
+            for j in range(4):
+                assert ((hi + lo)[r, j * gp:j * gp + g] - wo[r % Co, j * g:(j + 1) * g]).abs().max() <= 2.0 ** -21 * wo.abs().max()
