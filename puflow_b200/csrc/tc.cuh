@@ -143,14 +143,17 @@ __device__ __forceinline__ void named_bar(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-// x -> (hi, lo) fp16 pair with hi + lo == x to ~2^-22 relative (|x| < 65504; saturating beyond)
+// x -> (hi, lo) fp16 pair with hi + lo == x to ~2^-22 relative (|x| < 65504; saturating beyond: cvt.satfinite clamps to
+// the largest finite fp16 instead of producing inf, at no extra instruction; NaN stays NaN).  Low half = a, high half = b.
+__device__ __forceinline__ uint32_t cvt_f16x2_sat(float a, float b) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-    a = fminf(fmaxf(a, -65000.f), 65000.f), b = fminf(fmaxf(b, -65000.f), 65000.f);
-    __half2 h = __floats2half2_rn(a, b);
-    float2 hf = __half22float2(h);
-    __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
-    hi = *reinterpret_cast<uint32_t*>(&h);
-    lo = *reinterpret_cast<uint32_t*>(&l);
+    hi = cvt_f16x2_sat(a, b);
+    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    lo = cvt_f16x2_sat(a - hf.x, b - hf.y);
 }
 
 }  // namespace tc

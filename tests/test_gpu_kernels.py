@@ -241,7 +241,7 @@ def _split_ref(x):
     M, K = x.shape
     T = (M + 127) // 128
     xp = torch.zeros(T * 128, K)
-    xp[:M] = x.clamp(-65000.0, 65000.0)
+    xp[:M] = x.clamp(-65504.0, 65504.0)
     hi = xp.to(torch.float16)
     lo = (xp - hi.float()).to(torch.float16)
 
