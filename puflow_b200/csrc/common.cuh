@@ -145,7 +145,8 @@ __device__ __forceinline__ void ldg_vec(const float* __restrict__ p, float (&v)[
     }
 }
 
-__device__ __forceinline__ float lrelu(float v, float slope) { return v > 0.f ? v : v * slope; }
+// LeakyReLU for 0 <= slope <= 1 (checked at the C-ABI): max(v, slope v) -- one FMUL + one FMNMX, same value as the select form
+__device__ __forceinline__ float lrelu(float v, float slope) { return fmaxf(v, v * slope); }
 
 // ---- register-tiled FFMA micro-kernel ----------------------------------------------------------
 // acc[e][o] += sum_k hs[k*ldh + row(e)] * w[k*ldw + o]   for e < TE, o < TO, k < kdim.

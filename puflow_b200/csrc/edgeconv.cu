@@ -196,6 +196,7 @@ int launch_k(const float* pq, const int32_t* idx, const float* wd, const float* 
 
 extern "C" int pf_edgeconv(const float* pq, const int32_t* idx, const float* wd, const float* wo, float* out, int Bp,
                            int N, int K, int G, int C_out, float slope, void* stream) {
+    PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(pq && idx && wd && wo && out, "pf_edgeconv: null pointer");
     PF_CHECK_ARG(Bp >= 0 && N > 0, "pf_edgeconv: bad sizes Bp=%d N=%d", Bp, N);
     PF_CHECK_ARG((long long)Bp * N < 0x7fffffffLL, "pf_edgeconv: Bp*N overflows int32");

@@ -426,6 +426,7 @@ int launch(const float* pq, const int32_t* idx, const void* wtc, float* out, voi
 
 static int edgeconv_tc_dispatch(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
                                 int N, int K, int G_, int C_out, float slope, void* stream) {
+    PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(Bp >= 0 && N > 0, "pf_edgeconv_tc: bad sizes Bp=%d N=%d", Bp, N);
     if (Bp == 0) return 0;
     PF_CHECK_ARG(pq && idx && wtc && (out || out_split), "pf_edgeconv_tc: null pointer");

@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(NT) linear_kernel(const float* __restrict__ A,
 
 extern "C" int pf_linear(const float* A, int64_t lda, const float* W, const float* bias, float* out, int64_t ldo,
                          int64_t M, int K, int N, int act, float slope, void* stream) {
+    PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(A && W && out, "pf_linear: null pointer");
     PF_CHECK_ARG(M >= 0 && K > 0 && N > 0, "pf_linear: bad sizes M=%lld K=%d N=%d", (long long)M, K, N);
     PF_CHECK_ARG((N & 3) == 0 && (ldo & 3) == 0, "pf_linear: N=%d and ldo=%lld must be multiples of 4", N,

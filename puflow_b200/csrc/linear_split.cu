@@ -180,6 +180,7 @@ int launch(const uint8_t* a, const uint8_t* w, const float* bias, float* out, in
 
 extern "C" int pf_linear_tc_split(const void* a_split, const void* wtc, const float* bias, float* out, int64_t ldo, int64_t M,
                                   int K, int N, int act, float slope, void* stream) {
+    PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(M >= 0 && N > 0, "pf_linear_tc_split: bad sizes M=%lld N=%d", (long long)M, N);
     if (M == 0) return 0;
     PF_CHECK_ARG(a_split && wtc && out, "pf_linear_tc_split: null pointer");

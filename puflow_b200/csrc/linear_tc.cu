@@ -216,6 +216,7 @@ int launch(const float* A, int64_t lda, const uint8_t* w, const float* bias, flo
 
 extern "C" int pf_linear_tc(const float* A, int64_t lda, const void* wtc, const float* bias, float* out, int64_t ldo,
                             int64_t M, int K, int N, int act, float slope, void* stream) {
+    PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(A && wtc && out, "pf_linear_tc: null pointer");
     PF_CHECK_ARG(M >= 0 && N > 0, "pf_linear_tc: bad sizes M=%lld N=%d", (long long)M, N);
     PF_CHECK_ARG(K == 16 || K == 32 || K == 64 || K == 128, "pf_linear_tc: K=%d not in {16,32,64,128}", K);
