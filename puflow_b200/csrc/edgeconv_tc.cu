@@ -197,11 +197,11 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
         patch = (int)(tt / tpp);
         p0 = (int)(tt - (uint32_t)patch * tpp) * PT;
     };
-    auto load_j = [&](int patch, int p0) {
-        const int pi = min(p0 + (e >> 4), N - 1);
-        const int j = __ldg(idx + ((size_t)patch * N + pi) * KN + (e & 15));
-        return (uint16_t)min(max(j, 0), N - 1);
+    auto load_j = [&](int patch, int p0) {                                 // raw index: clamp at the use (clamp_j), not here,
+        const int pi = min(p0 + (e >> 4), N - 1);                         // so that the load's latency is not waited for
+        return __ldg(idx + ((size_t)patch * N + pi) * KN + (e & 15));
     };
+    auto clamp_j = [&](int j) { return (uint16_t)min(max(j, 0), N - 1); };
     const uint64_t da_hi = tc::smem_desc(a_hi, C::A_SBO), da_lo = tc::smem_desc(a_lo, C::A_SBO);
     // D[128 edges x GP] = H[:, 0:GP l] . W_l^T   (3 split products; K-step s is 256 B = 16 descriptor units further)
     auto issue_dense = [&](int l) {
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
     if (t < total_tiles) {   // prologue: indices, P and Q0 of the first tile
         int patch, p0;
         tile_coords(t, patch, p0);
-        jb[e] = load_j(patch, p0);
+        jb[e] = clamp_j(load_j(patch, p0));
         tc::named_bar(bar_id, 128);
         const float* ppq = pq + (size_t)patch * N * R2;
         stage_p(ppq, p0);
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
         const uint16_t* jl = jb + tb * TM;
         const bool has_next = t + stride < total_tiles;
         int patch_n = 0, p0_n = 0;
-        uint16_t j_next = 0;
+        int j_next = 0;
         if (has_next) {
             tile_coords(t + stride, patch_n, p0_n);
             j_next = load_j(patch_n, p0_n);
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
             else if (has_next)
                 stage_q(ppq_n, jb + (tb ^ 1) * TM, 0, 0);                 // next tile's Q0
             tc::cp_async_commit();
-            if (l == 1 && has_next) jb[(tb ^ 1) * TM + e] = j_next;       // published by this layer's closing barrier
+            if (l == 1 && has_next) jb[(tb ^ 1) * TM + e] = clamp_j(j_next);       // published by this layer's closing barrier
             float q[G];
             read_q(l & 1, q);
             add_p(l, q);
