@@ -202,18 +202,36 @@ __global__ void __launch_bounds__(NT, 1)
         };
         tc::mbar_wait_bounded(wbar, 0);   // biases live in the weight blob
 
+        // neighbour index and coordinates of a tile are fetched one tile ahead (two dependent global round trips)
+        auto tile_rows = [&](long long tt, int& p0_, size_t& row_i_) {
+            const int patch_ = (int)((uint32_t)tt / (uint32_t)tiles_per_patch);
+            p0_ = (int)((uint32_t)tt - (uint32_t)patch_ * (uint32_t)tiles_per_patch) * PT;
+            row_i_ = (size_t)patch_ * N + min(p0_ + (e >> 3), N - 1);
+            return (size_t)patch_ * N;
+        };
+        int p0_n = 0, j_n = 0;
+        size_t row_i_n = 0, base_n = 0;
+        float xi_n[3] = {0.f, 0.f, 0.f}, xj_n[3] = {0.f, 0.f, 0.f};
+        if (t < total_tiles) {
+            base_n = tile_rows(t, p0_n, row_i_n);
+            j_n = min(max(__ldg(idx + row_i_n * ldidx + (e & 7)), 0), N - 1);
+#pragma unroll
+            for (int a = 0; a < 3; a++) xi_n[a] = __ldg(xyz + row_i_n * 3 + a), xj_n[a] = __ldg(xyz + (base_n + j_n) * 3 + a);
+        }
         for (; t < total_tiles; t += stride) {
-            const int patch = (int)((uint32_t)t / (uint32_t)tiles_per_patch);
-            const int p0 = (int)((uint32_t)t - (uint32_t)patch * (uint32_t)tiles_per_patch) * PT;
-            const int pi = min(p0 + (e >> 3), N - 1);
-            const size_t row_i = (size_t)patch * N + pi;
-            int j = __ldg(idx + row_i * ldidx + (e & 7));
-            j = min(max(j, 0), N - 1);
-            const size_t row_j = (size_t)patch * N + j;
+            const int p0 = p0_n;
+            const size_t row_i = row_i_n, row_j = base_n + j_n;
+            const float xi0 = xi_n[0], xi1 = xi_n[1], xi2 = xi_n[2], xj0 = xj_n[0], xj1 = xj_n[1], xj2 = xj_n[2];
+            const bool has_next = t + stride < total_tiles;
+            int j_raw = 0;
+            if (has_next) {
+                base_n = tile_rows(t + stride, p0_n, row_i_n);
+                j_raw = __ldg(idx + row_i_n * ldidx + (e & 7));             // consumed after stage 2 below
+#pragma unroll
+                for (int a = 0; a < 3; a++) xi_n[a] = __ldg(xyz + row_i_n * 3 + a);
+            }
             // ---- geo slice ----
             {
-                const float xi0 = __ldg(xyz + row_i * 3), xi1 = __ldg(xyz + row_i * 3 + 1), xi2 = __ldg(xyz + row_i * 3 + 2);
-                const float xj0 = __ldg(xyz + row_j * 3), xj1 = __ldg(xyz + row_j * 3 + 1), xj2 = __ldg(xyz + row_j * 3 + 2);
                 const float dx = xi0 - xj0, dy = xi1 - xj1, dz = xi2 - xj2;
                 const float dist = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
                 const float g0[8] = {xi0, xi1, xi2, xj0, xj1, xj2, -dx, -dy};
@@ -251,6 +269,11 @@ __global__ void __launch_bounds__(NT, 1)
                 for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] + bd3[32 * c + u], S_DEF);
 #pragma unroll
                 for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
+            }
+            if (has_next) {                                              // second hop of the prefetch: x_j of the next tile
+                j_n = min(max(j_raw, 0), N - 1);
+#pragma unroll
+                for (int a = 0; a < 3; a++) xj_n[a] = __ldg(xyz + (base_n + j_n) * 3 + a);
             }
 #pragma unroll 1
             for (int l = 1; l < 8; l++) {
