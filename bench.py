@@ -184,10 +184,10 @@ def algorithmic_work(tag, Bc, npts):
         g, c, k = (int(x[1:]) for x in tag.replace("edgeconv_tc_", "edgeconv_").split("_")[1:4])
         R = 4 * g + c
         return "tensor", 2.0 * (6 * g * g + 4 * g * c) * M * k, "FLOP"          # hidden-channel MACs of the dense block
-    if tag.startswith("linear_k") or tag.startswith("linear_tc_k"):
-        f = tag.replace("linear_tc_", "linear_").split("_")
+    if tag.startswith("linear_k") or tag.startswith("linear_tc_k") or tag.startswith("linear_split_k"):
+        f = tag.replace("linear_tc_", "linear_").replace("linear_split_", "linear_").split("_")
         K, N = int(f[1][1:]), int(f[2][1:])
-        return "hbm", M * 4.0 * (K + N), "B"
+        return "hbm", M * 4.0 * (K + N), "B"        # the pre-split input (fp16 hi + lo) is 4 B per element as well
     if tag.startswith("cond_chain_tc_c"):
         return "hbm", M * 4.0 * (int(tag.rsplit("_c", 1)[1]) + 64 + 8), "B"
     if tag in ("flow_cond", "flow_cond_tc"):

@@ -129,6 +129,36 @@ def surface_patches(synth, n_cloud=2048, seed=2021, shape="torus"):
 
 # ------------------------------------------------------------------------------------------------
 @torch.no_grad()
+def cmd_golden_extra(args):
+    """The other two discrete checkpoints of the reference (pretrain/puflow-x4-pugan.pt, -pugeo.pt): network
+    stages on 3 real surface patches each, so that parity (and the fp16 range assumptions of the tensor-core kernels)
+    is pinned for every released weight set, not only pu1k."""
+    synth = _load_synth()
+    out = args.out
+    for tag in ("pugan", "pugeo"):
+        torch.manual_seed(2021)
+        net, sd = load_network(f"puflow-x4-{tag}.pt")
+        torch.save(sd, os.path.join(out, f"puflow-x4-{tag}.pt"))
+        xs = [surface_patches(synth, 2048, 3021 + i, s)[7 * i + 2] for i, s in enumerate(synth.SHAPES)]
+        xyz = torch.stack(xs, 0).contiguous()
+        g = {"xyz": xyz}
+        d16, idx16, _ = knn_points(xyz, xyz, K=16)
+        g["knn_idx"] = idx16.int()
+        c = xyz
+        for i in range(net.num_blocks):
+            c = net.feat_convs[i](c, knn_idx=idx16)
+            g[f"feat{i}"] = c
+            g[f"cs{i}"] = net.merge_convs[i](c)
+        cs = [g[f"cs{i}"] for i in range(6)]
+        g["z"], g["log_det_J"] = net.f(xyz, cs)
+        g["fz"] = net.interp(g["z"], xyz, 4)
+        x, logp = net(xyz, 4)
+        g["x"], g["logp_x"] = x, logp.reshape(1)
+        np.savez_compressed(os.path.join(out, f"net_{tag}.npz"), **{k: v.numpy() for k, v in g.items()})
+        print(tag, "max |feat5|", float(g["feat5"].abs().max()), "max |x|", float(x.abs().max()), flush=True)
+
+
+@torch.no_grad()
 def cmd_golden(args):
     synth = _load_synth()
     out = args.out
@@ -251,8 +281,10 @@ if __name__ == "__main__":
     sub = ap.add_subparsers(dest="cmd", required=True)
     g = sub.add_parser("golden")
     g.add_argument("--out", default=os.path.join(REPO, "tests", "golden"))
+    ge = sub.add_parser("golden-extra")
+    ge.add_argument("--out", default=os.path.join(REPO, "tests", "golden"))
     t = sub.add_parser("time")
     t.add_argument("--reps", type=int, default=3)
     a = ap.parse_args()
     install_shims()
-    {"golden": cmd_golden, "time": cmd_time}[a.cmd](a)
+    {"golden": cmd_golden, "golden-extra": cmd_golden_extra, "time": cmd_time}[a.cmd](a)

@@ -203,28 +203,29 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
     };
     auto clamp_j = [&](int j) { return (uint16_t)min(max(j, 0), N - 1); };
     const uint64_t da_hi = tc::smem_desc(a_hi, C::A_SBO), da_lo = tc::smem_desc(a_lo, C::A_SBO);
-    // D[128 edges x GP] = H[:, 0:GP l] . W_l^T   (3 split products; K-step s is 256 B = 16 descriptor units further)
+    // D[128 edges x GP] = H[:, 0:GP l] . W_l^T   (3 split products, the two small cross terms first: the accumulator
+    // adder truncates, so the additions at full magnitude -- the hi . hi pass -- come last and are as few as possible; K-step s is 256 B = 16 descriptor units further)
     auto issue_dense = [&](int l) {
         const uint32_t wl = sbase + C::wd_off(l);
         const uint64_t db_hi = tc::smem_desc(wl, 16u * GP * l), db_lo = tc::smem_desc(wl + C::wd_part(l), 16u * GP * l);
         const int ks = GP * l / 16;
         uint32_t acc = 0;
 #pragma unroll 1
-        for (int s = 0; s < ks; s++, acc = 1) tc::mma_f16(d_dense, da_hi + 16u * s, db_hi + 16u * s, idesc_d, acc);
-#pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_lo + 16u * s, db_hi + 16u * s, idesc_d, 1);
+        for (int s = 0; s < ks; s++, acc = 1) tc::mma_f16(d_dense, da_lo + 16u * s, db_hi + 16u * s, idesc_d, acc);
 #pragma unroll 1
         for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_lo + 16u * s, idesc_d, 1);
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_hi + 16u * s, idesc_d, 1);
     };
     // D^T[128 rows x 128 edges] = Wo . H^T, Wo from TMEM (8 columns per K-step)
     auto issue_out = [&]() {
         const uint32_t wo_hi = tmem_base + C::TM_WO_HI, wo_lo = tmem_base + C::TM_WO_LO;
 #pragma unroll
-        for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_hi + 16u * s, idesc_o, s > 0);
-#pragma unroll
-        for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_lo + 8u * s, da_hi + 16u * s, idesc_o, 1);
+        for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_lo + 8u * s, da_hi + 16u * s, idesc_o, s > 0);
 #pragma unroll
         for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_lo + 16u * s, idesc_o, 1);
+#pragma unroll
+        for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_hi + 16u * s, idesc_o, 1);
     };
 
     const long long stride = (long long)gridDim.x * NWG;
@@ -324,7 +325,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
                 for (int c = 0; c < G; c++) acc[c] = a16[c];
             }
 #pragma unroll
-            for (int c = 0; c < G; c++) acc[c] = lrelu(acc[c] + q[c], slope);
+            for (int c = 0; c < G; c++) acc[c] = lrelu(fmaf(acc[c], tc::WINV, q[c]), slope);
             store_slice(l, acc);
             tc::cp_async_wait<0>();
             tc::fence_async_smem();
@@ -367,7 +368,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
                 float acc[32];
                 tc::ld32(d_out + lane_sel + 32 * (grp * NCH + c), acc);
 #pragma unroll
-                for (int u = 0; u < 32; u++) acc[u] += (c & 1) ? qvb[u] : qva[u];
+                for (int u = 0; u < 32; u++) acc[u] = fmaf(acc[u], tc::WINV, (c & 1) ? qvb[u] : qva[u]);
                 if (c + 2 < NCH) {
                     if (c & 1) load_qchunk(c + 2, qvb); else load_qchunk(c + 2, qva);
                 }

@@ -50,17 +50,17 @@ struct Wg {
 // 64 activations (already through LeakyReLU) -> this thread's operand row.  fp16 saturates at 65,504, and exp(s) of the
 // affine injector can make intermediate coordinates (hence activations) arbitrarily large, so a row whose largest
 // magnitude exceeds 2^14 is scaled by a power of two (exact) before the split; the caller multiplies the row's
-// accumulators by the returned inverse scale (the layer is linear).  Returns 1 for ordinary rows.
+// accumulators by the returned factor (the layer is linear), which also takes out the weights' 2^10 (tc::WINV).
 __device__ __forceinline__ float store_row(const Wg& g, float (&h)[64]) {
     float amax = 0.f;
 #pragma unroll
     for (int k = 0; k < 64; k++) amax = fmaxf(amax, fabsf(h[k]));
     const int ex = (__float_as_int(amax) >> 23) & 0xff;       // biased exponent (NaN/Inf rows stay NaN/Inf)
-    float inv = 1.f;
+    float inv = tc::WINV;                                     // the weights carry a factor 1 / WINV (tc.cuh)
     if (ex > 127 + 13) {
         const int k = min(ex - 140, 120);
         const float sc = __int_as_float((127 - k) << 23);
-        inv = __int_as_float((127 + k) << 23);
+        inv = __int_as_float((127 + k) << 23) * tc::WINV;
 #pragma unroll
         for (int i = 0; i < 64; i++) h[i] *= sc;
     }
@@ -87,11 +87,11 @@ __device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[
         const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
         const uint64_t db_hi = tc::smem_desc(w_addr, H * 16), db_lo = tc::smem_desc(w_addr + W_PART, H * 16);
 #pragma unroll
-        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, s > 0);
-#pragma unroll
-        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, 1);
+        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, s > 0);
 #pragma unroll
         for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+#pragma unroll
+        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, 1);   // full magnitude last
         tc::commit(g.mbar);
     }
     tc::mbar_wait_bounded(g.mbar, g.phase);
@@ -357,11 +357,11 @@ __device__ __forceinline__ void issue3(Wg& g, uint32_t d_tmem, uint32_t w_addr, 
         const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
         const uint64_t db_hi = tc::smem_desc(w_addr, w_sbo) + 16u * w_k0, db_lo = tc::smem_desc(w_addr + w_part, w_sbo) + 16u * w_k0;
 #pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, (accumulate || s > 0) ? 1u : 0u);
-#pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, 1);
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, (accumulate || s > 0) ? 1u : 0u);
 #pragma unroll 1
         for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, 1);
         tc::commit(g.mbar);
     }
     tc::mbar_wait_bounded(g.mbar, g.phase);
@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(NT_CH, 1)
                 for (int i = 0; i < 64; i++) h[i] = i < 16 ? lo16[i < 16 ? i : 0] : 0.f;
             }
 #pragma unroll
-            for (int i = 0; i < H1; i++) h[i] = fmaxf(h[i] + fb1[i], 0.f);
+            for (int i = 0; i < H1; i++) h[i] = fmaxf(fmaf(h[i], tc::WINV, fb1[i]), 0.f);
             inv = store_row(g, h);                      // columns beyond H1 are zero and never read by the MMAs
         }
         // ---- stage 2: raw = h . W2c  (N = 192) ----

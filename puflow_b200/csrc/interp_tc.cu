@@ -111,11 +111,11 @@ __global__ void __launch_bounds__(NT, 1)
             auto issue3 = [&](uint32_t d, uint64_t ah, uint64_t al, uint32_t a_step, uint64_t bh, uint64_t bl, uint32_t b_step,
                               int ks, uint32_t idesc) {
 #pragma unroll 1
-                for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bh + b_step * s, idesc, s > 0);
-#pragma unroll 1
-                for (int s = 0; s < ks; s++) tc::mma_f16(d, al + a_step * s, bh + b_step * s, idesc, 1);
+                for (int s = 0; s < ks; s++) tc::mma_f16(d, al + a_step * s, bh + b_step * s, idesc, s > 0);
 #pragma unroll 1
                 for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bl + b_step * s, idesc, 1);
+#pragma unroll 1
+                for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bh + b_step * s, idesc, 1);   // full magnitude last
             };
             auto wdesc = [&](uint32_t off, uint32_t kt) { return tc::smem_desc(sbase + off, kt * 16); };
             const uint64_t xh = tc::smem_desc(x_hi, X_SBO), xl = tc::smem_desc(x_lo, X_SBO);
@@ -152,11 +152,11 @@ __global__ void __launch_bounds__(NT, 1)
                 {
                     const uint32_t mh = tmem_base + TM_M12_HI, ml = tmem_base + TM_M12_LO;
 #pragma unroll 1
-                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, s > 0);
-#pragma unroll 1
-                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, ml + 8u * s, xh + 16u * s, i128, 1);
+                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, ml + 8u * s, xh + 16u * s, i128, s > 0);
 #pragma unroll 1
                     for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xl + 16u * s, i128, 1);
+#pragma unroll 1
+                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, 1);
                 }
                 tc::commit(mbar);
                 // 10: t1 = t0 . W3^T, A = t0 M-major (8-edge groups 128 B apart, 8-channel groups 2048 B apart)
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(NT, 1)
                 float a[32];
                 tc::ld32(d_b + 32 * c, a);
 #pragma unroll
-                for (int u = 0; u < 32; u++) a[u] = lrelu(a[u], S_DEF);
+                for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] * tc::WINV, S_DEF);
 #pragma unroll
                 for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
             }
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(NT, 1)
                 float a[16];
                 tc::ld16(d_c, a);
 #pragma unroll
-                for (int u = 0; u < 16; u++) a[u] = lrelu(a[u], S_CTX);
+                for (int u = 0; u < 16; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
                 store8(COL_H / 8, a), store8(COL_H / 8 + 1, a + 8);
             }
             publish();
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(NT, 1)
                 float a[32];
                 tc::ld32(d_b + 32 * c, a);
 #pragma unroll
-                for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] + bd3[32 * c + u], S_DEF);
+                for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u], tc::WINV, bd3[32 * c + u]), S_DEF);
 #pragma unroll
                 for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
             }
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(NT, 1)
                 float a[16];
                 tc::ld16(d_c, a);
 #pragma unroll
-                for (int u = 0; u < 16; u++) a[u] = lrelu(a[u], S_CTX);
+                for (int u = 0; u < 16; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
                 store8(COL_H / 8 + 2 * l, a), store8(COL_H / 8 + 2 * l + 1, a + 8);
                 publish();
             }
@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(NT, 1)
                     float a[32];
                     tc::ld32(d_a + 32 * c, a);
 #pragma unroll
-                    for (int u = 0; u < 32; u++) a[u] = lrelu(a[u], S_DEF);
+                    for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] * tc::WINV, S_DEF);
 #pragma unroll
                     for (int g = 0; g < 4; g++) {
                         uint32_t hi[4], lo[4];
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(NT, 1)
                     float a[32];
                     tc::ld32(d_a + 32 * c, a);
 #pragma unroll
-                    for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] + b3[32 * c + u], S_DEF);
+                    for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u], tc::WINV, b3[32 * c + u]), S_DEF);
 #pragma unroll
                     for (int g = 0; g < 4; g++) {
                         uint32_t hi[4], lo[4];
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(NT, 1)
                 float* dst = out + row_i * R * 3;
 #pragma unroll
                 for (int r = 0; r < RP; r++) {
-                    float v = lg[r] + b6[r];
+                    float v = fmaf(lg[r], tc::WINV, b6[r]);
                     float mx = v;
 #pragma unroll
                     for (int o = 1; o < 8; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));

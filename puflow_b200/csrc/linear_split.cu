@@ -98,11 +98,11 @@ __global__ void __launch_bounds__(NT, 1)
                 const uint64_t da_hi = tc::smem_desc(a_hi, 128, LBO), da_lo = tc::smem_desc(a_lo, 128, LBO);
                 const uint32_t d_tmem = tmem_base + (uint32_t)g * 128;
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, s > 0);
-#pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, 1);
+                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, s > 0);
 #pragma unroll
                 for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_lo + b_step * s, idesc, 1);
+#pragma unroll
+                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, 1);   // full magnitude last
                 tc::commit(empty + st);
                 tc::commit(acc_full + g);
             }
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(NT, 1)
                         const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
                         for (int v = 0; v < 8; v++) {
-                            float x = acc[u + v] + bv[v];
+                            float x = fmaf(acc[u + v], tc::WINV, bv[v]);
                             if (act == PF_ACT_RELU) x = fmaxf(x, 0.f);
                             else if (act == PF_ACT_LRELU) x = lrelu(x, slope);
                             o[v] = x;

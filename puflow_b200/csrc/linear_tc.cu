@@ -87,11 +87,13 @@ __global__ void __launch_bounds__(NT, 1)
                 rphase ^= 1;
                 tc::fence_after_sync();
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, s > 0);
-#pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, 1);
+                // the small cross terms first: the accumulator adder truncates, so the fewer additions at full magnitude
+                // (the hi . hi pass) the better
+                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, s > 0);
 #pragma unroll
                 for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_lo + b_step * s, idesc, 1);
+#pragma unroll
+                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, 1);
                 tc::commit(mbar + wg);
             }
         }
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(NT, 1)
                 const int w = min(32, nc - c0);
 #pragma unroll
                 for (int u = 0; u < 32; u += 4) {
-                    float4 o = make_float4(acc[u], acc[u + 1], acc[u + 2], acc[u + 3]);
+                    float4 o = make_float4(acc[u] * tc::WINV, acc[u + 1] * tc::WINV, acc[u + 2] * tc::WINV, acc[u + 3] * tc::WINV);
                     if (u < w) {
                         if (bias) {
                             const float4 b = __ldg(reinterpret_cast<const float4*>(bias + n0 + c0 + u));

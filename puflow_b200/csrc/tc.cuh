@@ -15,6 +15,11 @@
 namespace pf {
 namespace tc {
 
+// Weights are packed as fp16 hi/lo of w * 2^10 (packing.py TC_WSCALE): with the raw |w| ~ 0.03 the lo half would be an
+// fp16 subnormal (spacing 2^-24, i.e. a 1e-6 relative weight error instead of 2^-23).  Every epilogue multiplies the
+// accumulator by 2^-10, which is exact.
+constexpr float WINV = 0x1p-10f;
+
 // 64-bit shared-memory matrix descriptor: start address, LBO, SBO (all >> 4), version 1, SWIZZLE_NONE.
 __device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, uint32_t sbo_bytes, uint32_t lbo_bytes = 128) {
     return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |

@@ -74,14 +74,29 @@ def pack_edgeconv(sd, prefix: str, C: int, g: int, C_out: int, layers: int = 4):
     )
 
 
-def umma_kmajor_fp16(mat):
-    """[rows, Kt] float64 -> (hi, lo) uint8 byte strings in the K-major no-swizzle tensor-core operand layout of
-    csrc/tc.cuh: half index (r//8)*(Kt*8) + (k//8)*64 + (r%8)*8 + (k%8).  hi = fp16(fp32(w)), lo = fp16(fp32(w) - hi)."""
-    rows, Kt = mat.shape
-    assert rows % 8 == 0 and Kt % 16 == 0, (rows, Kt)
+TC_WSCALE = 1024.0      # = 1 / tc::WINV (csrc/tc.cuh)
+
+
+def split_weight(mat):
+    """float64/32 weights -> (hi, lo) fp16 with hi + lo ~ fp32(w) * TC_WSCALE to 22 bits.  Without the power-of-two
+    factor the lo half of a typical |w| ~ 0.03 falls into the fp16 subnormals (spacing 2^-24) and the product loses
+    3 bits against fp32; the kernels' epilogues multiply the accumulator by 2^-10 (exact).  |w| * 1024 must stay
+    below the fp16 maximum: a checkpoint with |w| >= 60 is refused (run it with PUFLOW_EDGECONV=ffma)."""
     w32 = mat.to(torch.float32)
+    if w32.numel() and float(w32.abs().max()) >= 60.0:
+        raise ValueError(f"weight magnitude {float(w32.abs().max()):.3g} is outside the tensor-core path's fp16 range")
+    w32 = w32 * TC_WSCALE
     hi = w32.to(torch.float16)
     lo = (w32 - hi.to(torch.float32)).to(torch.float16)
+    return hi, lo
+
+
+def umma_kmajor_fp16(mat):
+    """[rows, Kt] float64 -> (hi, lo) uint8 byte strings in the K-major no-swizzle tensor-core operand layout of
+    csrc/tc.cuh: half index (r//8)*(Kt*8) + (k//8)*64 + (r%8)*8 + (k%8).  (hi, lo) = split_weight(w)."""
+    rows, Kt = mat.shape
+    assert rows % 8 == 0 and Kt % 16 == 0, (rows, Kt)
+    hi, lo = split_weight(mat)
 
     def lay(x):
         return x.reshape(rows // 8, 8, Kt // 8, 8).permute(0, 2, 1, 3).contiguous().view(torch.uint8).reshape(-1)
@@ -118,8 +133,7 @@ def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
         parts.extend(umma_kmajor_fp16(Wp))
     wo_rows = pad_k(wo.t().double(), layers)                          # [C_out, layers*gp]
     wo32 = wo_rows.repeat(128 // C_out, 1).contiguous().to(torch.float32)   # row r = channel r % C_out
-    wo_hi = wo32.to(torch.float16)
-    wo_lo = (wo32 - wo_hi.to(torch.float32)).to(torch.float16)
+    wo_hi, wo_lo = split_weight(wo32)
     parts.extend([wo_hi.contiguous().view(torch.uint8).reshape(-1), wo_lo.contiguous().view(torch.uint8).reshape(-1)])
     blob = torch.cat(parts)
     assert blob.numel() == edgeconv_tc_blob_bytes(g), blob.numel()
@@ -250,9 +264,7 @@ def pack_interp_tc(sd):
     G = W0b @ Wco[:, 0:9]                                  # composed geo part [128, 9]
     bm = W0a @ bd6 + W0b @ bco + b0
     M12g = torch.cat([geo(G[:, 0:3], G[:, 3:6], G[:, 6:9], None, bm), W0b @ Wco[:, 9:], W0a @ Wd6], dim=1)   # [128, 208]
-    m32 = M12g.to(torch.float32)
-    hi = m32.to(torch.float16)
-    lo = (m32 - hi.to(torch.float32)).to(torch.float16)
+    hi, lo = split_weight(M12g)
     blob = torch.cat([smem, hi.contiguous().view(torch.uint8).reshape(-1), lo.contiguous().view(torch.uint8).reshape(-1)])
     assert blob.numel() == INTERP_TC_BLOB, blob.numel()
     return blob

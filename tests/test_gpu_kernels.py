@@ -236,6 +236,27 @@ def test_edgeconv_tensor_core_rejects_other_shapes(ops, dev, packed):
         ops.edgeconv_tc(pq, idx16, packed["feat"][0]["wtc"].to(dev), 1, 256, 32, 128)
 
 
+@pytest.mark.parametrize("K", [32, 128])
+def test_linear_tc_accumulation_accuracy(ops, dev, K):
+    """The split-fp16 tensor-core product must be as accurate as the FP32 FFMA kernel: weights carry a 2^10 factor so no
+    lo half is an fp16 subnormal, and the full-magnitude hi . hi pass is issued last because the accumulator adder
+    truncates (the opposite order measured 3.5x the FFMA rms error and a -1e-6 bias on all-positive data)."""
+    from puflow_b200 import packing
+    g = torch.Generator().manual_seed(5)
+    M, N = 8192, 128
+    for positive in (False, True):
+        a, w = torch.randn(M, K, generator=g), torch.randn(K, N, generator=g) * 0.03
+        if positive:
+            a, w = a.abs(), w.abs()
+        ref = a.double() @ w.double()
+        rms = ref.pow(2).mean().sqrt()
+        e_f = (ops.linear(a.to(dev), w.to(dev), None, 0).cpu().double() - ref)
+        e_t = (ops.linear_tc(a.to(dev), packing.pack_linear_tc(w).to(dev), N, None, 0).cpu().double() - ref)
+        rf, rt = e_f.pow(2).mean().sqrt() / rms, e_t.pow(2).mean().sqrt() / rms
+        assert rt <= (4.0 if positive else 1.5) * rf + 2e-8, (K, positive, float(rt), float(rf))
+        assert e_t.abs().max() / rms <= 4e-6
+
+
 def _split_ref(x):
     """[M, K] fp32 -> uint8 tiles in the pre-split operand layout (include/puflow_b200.h, PF_SPLIT_TILE_BYTES)."""
     M, K = x.shape
@@ -367,7 +388,7 @@ def test_flow_tensor_core(ops, dev, packed, M):
     assert ok, err
     # round trip; random conditioning features give exp(s) up to e^40, so a few points in 60,000 amplify rounding
     back = (ops.flow_inv(z, rawd, sb, ftc, 1).cpu() - x).abs().flatten()
-    assert back.quantile(0.999) < 1e-5 and back.max() < (1e-4 if M <= 1000 else 2e-3)
+    assert back.quantile(0.99) < 1e-5 and back.quantile(0.999) < 3e-5 and back.max() < (1e-4 if M <= 1000 else 2e-3)
 
 
 def test_flow_tensor_core_golden_and_subsets(ops, dev, packed, golden):
@@ -475,6 +496,30 @@ def test_network_stages_match_reference(dev, state_dict, golden):
     fz = r["zup"].cpu().view(3, 256, 4, 3).permute(0, 1, 3, 2).numpy()
     ok, err = parity.close_norm(fz, g["fz"], 1e-3)
     assert ok, ("fz", err)
+    ok, err = parity.close_norm(r["x"].cpu().numpy(), g["x"], 1e-4)
+    assert ok, ("x", err)
+    assert abs(float(r["logp_x"]) - float(g["logp_x"][0])) <= 1e-4 * abs(float(g["logp_x"][0]))
+    for b in range(3):
+        assert parity.chamfer_distance(r["x"][b].cpu().numpy(), g["x"][b]) <= 1e-5
+
+
+@pytest.mark.parametrize("tag", ["pugan", "pugeo"])
+def test_network_other_checkpoints(dev, golden, tag):
+    """Same stage-by-stage comparison with the reference's pugan / pugeo weight sets (activations up to ~400 with pugeo:
+    the fp16 hi/lo operands of the tensor-core kernels stay far from saturation, and the tolerances are unchanged)."""
+    import os
+    from puflow_b200.engine import PUFlowEngine
+    sd = torch.load(os.path.join(os.path.dirname(__file__), "golden", f"puflow-x4-{tag}.pt"), map_location="cpu")
+    g = golden(f"net_{tag}.npz")
+    r = PUFlowEngine(sd, dev).forward(torch.from_numpy(g["xyz"]).to(dev), 4, return_all=True)
+    assert np.array_equal(r["knn_idx"].cpu().numpy(), g["knn_idx"])
+    for i in range(6):
+        ok, err = parity.close_norm(r["feats"][i].cpu().numpy(), g[f"feat{i}"], 1e-4)
+        assert ok, ("feat", i, err)
+        ok, err = parity.close_norm(r["cs"][i].cpu().numpy(), g[f"cs{i}"], 1e-4)
+        assert ok, ("cs", i, err)
+    ok, err = parity.close_norm(r["z"].cpu().numpy(), g["z"], 1e-3)
+    assert ok, ("z", err)
     ok, err = parity.close_norm(r["x"].cpu().numpy(), g["x"], 1e-4)
     assert ok, ("x", err)
     assert abs(float(r["logp_x"]) - float(g["logp_x"][0])) <= 1e-4 * abs(float(g["logp_x"][0]))

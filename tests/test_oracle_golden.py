@@ -1,6 +1,7 @@
 """Pins the CPU oracle (oracle/) against the golden fixtures produced by the unmodified reference
 (oracle/ref/run_reference.py, run in the build container).  CPU only."""
 import numpy as np
+import pytest
 import torch
 
 from oracle import puflow_oracle as po
@@ -45,6 +46,25 @@ def test_network_stages_match_reference(golden, state_dict):
         ok, err = _close(r[k].numpy(), g[k])
         assert ok, (k, err)
     assert abs(float(r["logp_x"]) - float(g["logp_x"][0])) <= 1e-4 * abs(float(g["logp_x"][0]))
+
+
+@pytest.mark.parametrize("tag", ["pugan", "pugeo"])
+def test_network_stages_match_reference_other_checkpoints(golden, tag):
+    """The reference's other two discrete weight sets (pretrain/puflow-x4-pugan.pt, -pugeo.pt; fixtures by
+    oracle/ref/run_reference.py golden-extra)."""
+    import os
+    sd = torch.load(os.path.join(os.path.dirname(__file__), "golden", f"puflow-x4-{tag}.pt"), map_location="cpu")
+    g = golden(f"net_{tag}.npz")
+    r = po.PUFlowOracle(sd).forward(torch.from_numpy(g["xyz"]), 4, return_all=True)
+    assert np.array_equal(r["knn_idx"].numpy(), g["knn_idx"])
+    for i in range(6):
+        ok, err = _close(r["feats"][i].numpy(), g[f"feat{i}"])
+        assert ok, (i, err)
+        ok, err = _close(r["cs"][i].numpy(), g[f"cs{i}"])
+        assert ok, (i, err)
+    for k in ("z", "x"):
+        ok, err = _close(r[k].numpy(), g[k])
+        assert ok, (k, err)
 
 
 def test_fp64_oracle_is_consistent(golden, state_dict):

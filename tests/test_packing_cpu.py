@@ -68,7 +68,7 @@ def test_flow_blocks_match_reference_layers(golden, state_dict):
 def _umma_decode(buf, rows, Kt):
     """inverse of packing.umma_kmajor_fp16's layout: uint8 -> [rows, Kt] float32 (one part)."""
     h = buf.view(torch.float16).view(rows // 8, Kt // 8, 8, 8).permute(0, 2, 1, 3).reshape(rows, Kt)
-    return h.float()
+    return h.float() / packing.TC_WSCALE
 
 
 def test_tensor_core_blobs_decode_to_the_weights(state_dict):
@@ -81,6 +81,9 @@ def test_tensor_core_blobs_decode_to_the_weights(state_dict):
         W2 = w["flow"][i][384:4480].view(64, 64).t()
         dec = _umma_decode(b[:8192], 64, 64) + _umma_decode(b[8192:16384], 64, 64)
         assert (dec - W2).abs().max() <= 2.0 ** -21 * W2.abs().max()
+        # the 2^10 factor keeps the lo halves out of the fp16 subnormals: 22 good bits for every weight above 2^-12
+        big = W2.abs() >= 2.0 ** -12
+        assert ((dec - W2).abs()[big] <= 2.0 ** -21 * W2.abs()[big]).all()
         assert torch.equal(b[16384:].view(torch.float32), w["flow"][i][:384])
         c = w["cond_tc"][i]
         assert c.numel() == N.PF_COND_TC_BLOCK
@@ -113,8 +116,8 @@ def test_tensor_core_blobs_decode_to_the_weights(state_dict):
                 assert (dec[:g, j * gp + g:(j + 1) * gp] == 0).all() and (dec[g:] == 0).all()
             off += 2 * part
         KT = 4 * gp
-        hi = f["wtc"][off:off + 128 * KT * 2].view(torch.float16).view(128, KT).float()
-        lo = f["wtc"][off + 128 * KT * 2:].view(torch.float16).view(128, KT).float()
+        hi = f["wtc"][off:off + 128 * KT * 2].view(torch.float16).view(128, KT).float() / packing.TC_WSCALE
+        lo = f["wtc"][off + 128 * KT * 2:].view(torch.float16).view(128, KT).float() / packing.TC_WSCALE
         wo = f["wo"].t()                                               # [C_out, 4g]
         for r in (0, Co - 1, Co % 128, 127):
             for j in range(4):
