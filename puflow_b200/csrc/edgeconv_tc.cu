@@ -209,12 +209,11 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
         const uint32_t wl = sbase + C::wd_off(l);
         const uint64_t db_hi = tc::smem_desc(wl, 16u * GP * l), db_lo = tc::smem_desc(wl + C::wd_part(l), 16u * GP * l);
         const int ks = GP * l / 16;
-        uint32_t acc = 0;
-#pragma unroll 1
-        for (int s = 0; s < ks; s++, acc = 1) tc::mma_f16(d_dense, da_lo + 16u * s, db_hi + 16u * s, idesc_d, acc);
-#pragma unroll 1
+#pragma unroll
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_lo + 16u * s, db_hi + 16u * s, idesc_d, s > 0);
+#pragma unroll
         for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_lo + 16u * s, idesc_d, 1);
-#pragma unroll 1
+#pragma unroll
         for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_hi + 16u * s, idesc_d, 1);
     };
     // D^T[128 rows x 128 edges] = Wo . H^T, Wo from TMEM (8 columns per K-step)
@@ -231,12 +230,13 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
     const long long stride = (long long)gridDim.x * NWG;
     long long t = (long long)blockIdx.x * NWG + wg;
     if (is_mma_warp) {
-        // ---- MMA-issuing warp of warpgroup wg: one thread; waits for "operands ready", issues, commits ----
-        if ((tid & 31) == 0) {
-            tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
+        // ---- MMA-issuing warp of warpgroup wg: one elected thread (elect_one, not lane == 0: tc.cuh) waits for
+        // "operands ready", issues, commits ----
+        tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
+        if (tc::elect_one()) {
             uint32_t rphase = 0;
             for (; t < total_tiles; t += stride) {
-#pragma unroll 1
+#pragma unroll
                 for (int l = 1; l < 4; l++) {
                     tc::mbar_wait_bounded(ready + wg, rphase);
                     rphase ^= 1;
@@ -251,6 +251,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
                 tc::commit(mbar + wg);
             }
         }
+        __syncwarp();
     } else {
     int tb = 0;
     if (t < total_tiles) {   // prologue: indices, P and Q0 of the first tile

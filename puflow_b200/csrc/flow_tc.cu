@@ -81,7 +81,7 @@ __device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[
     tc::fence_async_smem();
     tc::fence_before_sync();
     tc::named_bar(g.bar_id, 128);        // operand rows written; previous accumulators read by everyone
-    if (g.e == 0) {
+    if (g.e < 32 && tc::elect_one()) {       // first warp of the warpgroup, one elected lane (tc.cuh)
         tc::fence_after_sync();
         const uint32_t idesc = tc::idesc_f16(128, H);
         const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
@@ -351,7 +351,7 @@ __device__ __forceinline__ void issue3(Wg& g, uint32_t d_tmem, uint32_t w_addr, 
     tc::fence_async_smem();
     tc::fence_before_sync();
     tc::named_bar(g.bar_id, 128);
-    if (g.e == 0) {
+    if (g.e < 32 && tc::elect_one()) {       // first warp of the warpgroup, one elected lane (tc.cuh)
         tc::fence_after_sync();
         const uint32_t idesc = tc::idesc_f16(128, n);
         const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);

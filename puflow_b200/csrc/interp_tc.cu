@@ -19,6 +19,9 @@
 //      in TMEM as the A operand); thread = channel; t0 is written back as an M-major (edge-contiguous) operand
 //  10  t1 = lrelu(t0.W3 + b3)  (A = t0 M-major, N=64, K=128)      11  logits = t1.W6 + b6  (N=32, K=64)
 //  then softmax over the 8 neighbours (8 consecutive lanes) and the weighted sum of the neighbours' latents.
+// Per-stage clock64() totals (tools/dev_interp_prof.py, -DPF_INTERP_PROF) showed the MMA-issuing thread, not the tensor
+// pipe, bounding the N = 16 layers (69 cycles per tcgen05.mma issued from an `if (lane == 0)` region: an ELECT/branch
+// loop around every instruction), hence elect_one() and the 2-MMA split form below.
 #include "common.cuh"
 #include "puflow_b200.h"
 #include "tc.cuh"
@@ -43,8 +46,19 @@ constexpr uint32_t BAR_OFF = X_OFF + 2 * X_PART;          // 205,568
 constexpr uint32_t SMEM_BYTES = BAR_OFF + 64;
 constexpr uint32_t COL_H = 16, COL_D = 144;               // K offsets inside X
 // ---- tensor memory map (columns) ----
-constexpr uint32_t TM_M12_HI = 0, TM_M12_LO = 104, TM_DA = 208, TM_DB = 336, TM_DC = 400, TM_COLS = 512;
+constexpr uint32_t TM_M12_HI = 0, TM_M12_LO = 104, TM_DA = 208, TM_DB = 336, TM_DC = 464, TM_COLS = 512;   // DA 128, DB 128, DC 32
 constexpr uint32_t M12_GLOBAL = W_BYTES, M12_PART = 128 * 104 * 4;
+
+#ifdef PF_INTERP_PROF   // dev builds only: per-stage clock64() totals of CTA 0 (epilogue thread 0 and the MMA thread)
+__device__ long long g_prof[32];
+#define PROF_DECL long long pacc[16] = {0}; long long pt0 = clock64();
+#define PROF_TICK(k) { const long long pt1 = clock64(); pacc[k] += pt1 - pt0; pt0 = pt1; }
+#define PROF_DUMP(base, n) if (blockIdx.x == 0) { for (int i = 0; i < n; i++) g_prof[base + i] = pacc[i]; }
+#else
+#define PROF_DECL
+#define PROF_TICK(k)
+#define PROF_DUMP(base, n)
+#endif
 
 template <int RP>   // logits evaluated per edge (R rounded up to 4 / 8 / 16 / 32)
 __global__ void __launch_bounds__(NT, 1)
@@ -105,72 +119,79 @@ __global__ void __launch_bounds__(NT, 1)
     long long t = blockIdx.x;
 
     if (is_mma_warp) {
-        if (lane == 0) {
-            tc::mbar_wait_bounded(wbar, 0);
-            // SS product with the three split passes; K-step = 16 halfs: +a_step / +b_step descriptor units (16 B)
-            auto issue3 = [&](uint32_t d, uint64_t ah, uint64_t al, uint32_t a_step, uint64_t bh, uint64_t bl, uint32_t b_step,
-                              int ks, uint32_t idesc) {
-#pragma unroll 1
-                for (int s = 0; s < ks; s++) tc::mma_f16(d, al + a_step * s, bh + b_step * s, idesc, s > 0);
-#pragma unroll 1
-                for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bl + b_step * s, idesc, 1);
-#pragma unroll 1
-                for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bh + b_step * s, idesc, 1);   // full magnitude last
+        tc::mbar_wait_bounded(wbar, 0);
+        if (tc::elect_one()) {
+            // Split products.  3-pass form (t0): al.bh, ah.bl, then ah.bh (full magnitude last, see tc.cuh).  2-MMA form for
+            // the narrow layers: hi and lo of a weight matrix are adjacent 8-row groups of ONE K-major operand, so
+            // ah . [bh | bl] is a single MMA of width 2n (big term in columns [0, n), ah.bl in [n, 2n)), and al . bh
+            // accumulates into [n, 2n); the epilogue adds the two halves.  A third fewer instructions to issue (the
+            // N = 16 layers are issue-bound, not tensor-bound) and the small terms never meet the big accumulator.
+            auto issue2 = [&](uint32_t d, uint64_t ah, uint64_t al, uint32_t a_step, uint64_t bh, uint32_t b_step, int ks,
+                              uint32_t idesc_2n, uint32_t idesc_n, uint32_t n) {
+#pragma unroll
+                for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bh + b_step * s, idesc_2n, s > 0);
+#pragma unroll
+                for (int s = 0; s < ks; s++) tc::mma_f16(d + n, al + a_step * s, bh + b_step * s, idesc_n, 1);
             };
             auto wdesc = [&](uint32_t off, uint32_t kt) { return tc::smem_desc(sbase + off, kt * 16); };
             const uint64_t xh = tc::smem_desc(x_hi, X_SBO), xl = tc::smem_desc(x_lo, X_SBO);
             const uint32_t d_a = tmem_base + TM_DA, d_b = tmem_base + TM_DB, d_c = tmem_base + TM_DC;
-            const uint32_t i64 = tc::idesc_f16(128, 64), i16 = tc::idesc_f16(128, 16), i128 = tc::idesc_f16(128, 128),
-                           i32 = tc::idesc_f16(128, 32);
+            constexpr uint32_t i64 = tc::idesc_f16(128, 64), i16 = tc::idesc_f16(128, 16), i128 = tc::idesc_f16(128, 128),
+                               i32 = tc::idesc_f16(128, 32), AT = 1u << 15;
             uint32_t rphase = 0;
+            PROF_DECL
             auto wait_ready = [&]() {
+                PROF_TICK(1)
                 tc::mbar_wait_bounded(ready, rphase);
                 rphase ^= 1;
                 tc::fence_after_sync();
+                PROF_TICK(0)
             };
             for (; t < total_tiles; t += stride) {
                 // 1: d1, h0 from the geo slice
                 wait_ready();
-                issue3(d_b, xh, xl, 16, wdesc(W_D1, 16), wdesc(W_D1 + 2048, 16), 16, 1, i64);
-                issue3(d_c, xh, xl, 16, wdesc(wh_off(0), 16), wdesc(wh_off(0) + wh_part(0), 16), 16, 1, i16);
+                issue2(d_b, xh, xl, 16, wdesc(W_D1, 16), 16, 1, i128, i64, 64);
+                issue2(d_c, xh, xl, 16, wdesc(wh_off(0), 16), 16, 1, i32, i16, 16);
                 tc::commit(mbar);
                 // 2: d2 (A = X columns [144, 208)), h1
                 wait_ready();
-                issue3(d_b, xh + (COL_D / 8) * 8, xl + (COL_D / 8) * 8, 16, wdesc(W_D2, 64), wdesc(W_D2 + 8192, 64), 16, 4, i64);
-                issue3(d_c, xh, xl, 16, wdesc(wh_off(1), 32), wdesc(wh_off(1) + wh_part(1), 32), 16, 2, i16);
+                issue2(d_b, xh + (COL_D / 8) * 8, xl + (COL_D / 8) * 8, 16, wdesc(W_D2, 64), 16, 4, i128, i64, 64);
+                issue2(d_c, xh, xl, 16, wdesc(wh_off(1), 32), 16, 2, i32, i16, 16);
                 tc::commit(mbar);
                 // 3..8: h_l
-#pragma unroll 1
+#pragma unroll
                 for (int l = 2; l < 8; l++) {
                     wait_ready();
-                    issue3(d_c, xh, xl, 16, wdesc(wh_off(l), 16 + 16 * l), wdesc(wh_off(l) + wh_part(l), 16 + 16 * l), 16, l + 1,
-                           i16);
+                    issue2(d_c, xh, xl, 16, wdesc(wh_off(l), 16 + 16 * l), 16, l + 1, i32, i16, 16);
                     tc::commit(mbar);
                 }
                 // 9: t0^T = M12g . X^T, A from tensor memory (8 columns per K-step)
                 wait_ready();
                 {
                     const uint32_t mh = tmem_base + TM_M12_HI, ml = tmem_base + TM_M12_LO;
-#pragma unroll 1
+#pragma unroll
                     for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, ml + 8u * s, xh + 16u * s, i128, s > 0);
-#pragma unroll 1
+#pragma unroll
                     for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xl + 16u * s, i128, 1);
-#pragma unroll 1
+#pragma unroll
                     for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, 1);
                 }
                 tc::commit(mbar);
                 // 10: t1 = t0 . W3^T, A = t0 M-major (8-edge groups 128 B apart, 8-channel groups 2048 B apart)
                 wait_ready();
-                issue3(d_a, tc::smem_desc(sbase + T0_OFF, 128, 2048), tc::smem_desc(sbase + T0_OFF + T0_PART, 128, 2048), 256,
-                       wdesc(W_3, 128), wdesc(W_3 + 16384, 128), 16, 8, i64 | (1u << 15));
+                issue2(d_a, tc::smem_desc(sbase + T0_OFF, 128, 2048), tc::smem_desc(sbase + T0_OFF + T0_PART, 128, 2048), 256,
+                       wdesc(W_3, 128), 16, 8, i128 | AT, i64 | AT, 64);
                 tc::commit(mbar);
                 // 11: logits = t1 . W6^T
                 wait_ready();
-                issue3(d_a + 64, tc::smem_desc(sbase + T1_OFF, T1_SBO), tc::smem_desc(sbase + T1_OFF + T1_PART, T1_SBO), 16,
-                       wdesc(W_6, 64), wdesc(W_6 + 4096, 64), 16, 4, i32);
+                issue2(d_a, tc::smem_desc(sbase + T1_OFF, T1_SBO), tc::smem_desc(sbase + T1_OFF + T1_PART, T1_SBO), 16,
+                       wdesc(W_6, 64), 16, 4, i64, i32, 32);
                 tc::commit(mbar);
             }
+            PROF_TICK(1)
+            PROF_DUMP(16, 2)
         }
+        __syncwarp();
     } else {
         // ---- epilogue warps: thread e = edge row of the tile (point e / 8, neighbour e % 8) ----
         uint8_t* xh_p = smem + X_OFF;
@@ -218,6 +239,7 @@ __global__ void __launch_bounds__(NT, 1)
 #pragma unroll
             for (int a = 0; a < 3; a++) xi_n[a] = __ldg(xyz + row_i_n * 3 + a), xj_n[a] = __ldg(xyz + (base_n + j_n) * 3 + a);
         }
+        PROF_DECL
         for (; t < total_tiles; t += stride) {
             const int p0 = p0_n;
             const size_t row_i = row_i_n, row_j = base_n + j_n;
@@ -240,33 +262,37 @@ __global__ void __launch_bounds__(NT, 1)
                 store8(1, g1);
             }
             publish();
+            PROF_TICK(0)
             // ---- 1: d1 -> X[:, 144:208), h0 -> X[:, 16:32) ----
             wait_mma();
+            PROF_TICK(1)
 #pragma unroll
             for (int c = 0; c < 2; c++) {
-                float a[32];
-                tc::ld32(d_b + 32 * c, a);
+                float a[32], b[32];                                      // big half, small half (see issue2)
+                tc::ld32(d_b + 32 * c, a), tc::ld32(d_b + 64 + 32 * c, b);
 #pragma unroll
-                for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] * tc::WINV, S_DEF);
+                for (int u = 0; u < 32; u++) a[u] = lrelu((a[u] + b[u]) * tc::WINV, S_DEF);
 #pragma unroll
                 for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
             }
             {
-                float a[16];
-                tc::ld16(d_c, a);
+                float a[32];
+                tc::ld32(d_c, a);
 #pragma unroll
-                for (int u = 0; u < 16; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
+                for (int u = 0; u < 16; u++) a[u] = lrelu((a[u] + a[16 + u]) * tc::WINV, S_CTX);
                 store8(COL_H / 8, a), store8(COL_H / 8 + 1, a + 8);
             }
             publish();
+            PROF_TICK(2)
             // ---- 2: d2 (overwrites d1), h1 ----
             wait_mma();
+            PROF_TICK(3)
 #pragma unroll
             for (int c = 0; c < 2; c++) {
-                float a[32];
-                tc::ld32(d_b + 32 * c, a);
+                float a[32], b[32];
+                tc::ld32(d_b + 32 * c, a), tc::ld32(d_b + 64 + 32 * c, b);
 #pragma unroll
-                for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u], tc::WINV, bd3[32 * c + u]), S_DEF);
+                for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u] + b[u], tc::WINV, bd3[32 * c + u]), S_DEF);
 #pragma unroll
                 for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
             }
@@ -277,16 +303,21 @@ __global__ void __launch_bounds__(NT, 1)
             }
 #pragma unroll 1
             for (int l = 1; l < 8; l++) {
-                if (l > 1) wait_mma();
-                float a[16];
-                tc::ld16(d_c, a);
+                if (l > 1) {
+                    wait_mma();
+                    PROF_TICK(5)
+                }
+                float a[32];
+                tc::ld32(d_c, a);
 #pragma unroll
-                for (int u = 0; u < 16; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
+                for (int u = 0; u < 16; u++) a[u] = lrelu((a[u] + a[16 + u]) * tc::WINV, S_CTX);
                 store8(COL_H / 8 + 2 * l, a), store8(COL_H / 8 + 2 * l + 1, a + 8);
                 publish();
+                if (l > 1) { PROF_TICK(6) } else { PROF_TICK(4) }
             }
             // ---- 9: t0^T: thread = channel e; write t0 back as an M-major operand (aliases X, dead now) ----
             wait_mma();
+            PROF_TICK(7)
             {
                 uint8_t* th = smem + T0_OFF + (uint32_t)(e >> 3) * 2048 + (uint32_t)(e & 7) * 16;
 #pragma unroll 1
@@ -306,16 +337,18 @@ __global__ void __launch_bounds__(NT, 1)
                 }
             }
             publish();
+            PROF_TICK(8)
             // ---- 10: t1 (thread = edge again) -> K-major operand ----
             wait_mma();
+            PROF_TICK(9)
             {
                 uint8_t* t1h = smem + T1_OFF + (uint32_t)(e >> 3) * T1_SBO + (uint32_t)(e & 7) * 16;
 #pragma unroll
                 for (int c = 0; c < 2; c++) {
-                    float a[32];
-                    tc::ld32(d_a + 32 * c, a);
+                    float a[32], b[32];
+                    tc::ld32(d_a + 32 * c, a), tc::ld32(d_a + 64 + 32 * c, b);
 #pragma unroll
-                    for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u], tc::WINV, b3[32 * c + u]), S_DEF);
+                    for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u] + b[u], tc::WINV, b3[32 * c + u]), S_DEF);
 #pragma unroll
                     for (int g = 0; g < 4; g++) {
                         uint32_t hi[4], lo[4];
@@ -327,20 +360,23 @@ __global__ void __launch_bounds__(NT, 1)
                 }
             }
             publish();
+            PROF_TICK(10)
             // ---- 11: logits -> softmax over the 8 neighbours (8 consecutive lanes) -> weighted latent sum ----
             const float z0 = __ldg(z + row_j * 3), z1 = __ldg(z + row_j * 3 + 1), z2 = __ldg(z + row_j * 3 + 2);
             wait_mma();
+            PROF_TICK(11)
             {
                 float lg[RP];
                 if constexpr (RP == 32) {
-                    tc::ld32(d_a + 64, lg);
-                } else if constexpr (RP == 16) {
-                    tc::ld16(d_a + 64, lg);
-                } else {
-                    float a16[16];
-                    tc::ld16(d_a + 64, a16);
+                    float sm[32];
+                    tc::ld32(d_a, lg), tc::ld32(d_a + 32, sm);
 #pragma unroll
-                    for (int r = 0; r < RP; r++) lg[r] = a16[r];
+                    for (int r = 0; r < RP; r++) lg[r] += sm[r];
+                } else {
+                    float a16[16], s16[16];
+                    tc::ld16(d_a, a16), tc::ld16(d_a + 32, s16);
+#pragma unroll
+                    for (int r = 0; r < RP; r++) lg[r] = a16[r] + s16[r];
                 }
                 const bool writer = (e & 7) == 0 && (p0 + (e >> 3)) < N;
                 float* dst = out + row_i * R * 3;
@@ -367,7 +403,9 @@ __global__ void __launch_bounds__(NT, 1)
             }
             tc::fence_before_sync();
             tc::named_bar(1, 128);     // X / t1 / D are free for the next tile
+            PROF_TICK(12)
         }
+        if (tid == 0) { PROF_DUMP(0, 13) }
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -390,6 +428,12 @@ int launch(const float* xyz, const float* z, const int32_t* idx, int ldidx, cons
 }
 
 }  // namespace
+
+#ifdef PF_INTERP_PROF
+extern "C" __attribute__((visibility("default"))) int pf_debug_interp_prof(long long* host32) {
+    return cudaMemcpyFromSymbol(host32, g_prof, sizeof(long long) * 32) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 extern "C" int pf_interp_tc(const float* xyz, const float* z, const int32_t* idx, int ldidx, const void* wtc, float* out,
                             int Bp, int N, int R, void* stream) {

@@ -83,8 +83,8 @@ __global__ void __launch_bounds__(NT, 1)
         }
     } else if (warp == 9) {
         // ---- MMA issuer ----
-        if ((tid & 31) == 0) {
-            tc::mbar_wait_bounded(wbar, 0);
+        tc::mbar_wait_bounded(wbar, 0);
+        if (tc::elect_one()) {             // not `lane == 0`: see tc.cuh
             const uint32_t idesc = tc::idesc_f16(128, nc);
             const uint64_t db_hi = tc::smem_desc(sbase, K * 16), db_lo = tc::smem_desc(sbase + w_part, K * 16);
             constexpr uint32_t a_step = (2 * LBO) >> 4, b_step = 256 >> 4;
@@ -107,6 +107,7 @@ __global__ void __launch_bounds__(NT, 1)
                 tc::commit(acc_full + g);
             }
         }
+        __syncwarp();
     } else {
         // ---- epilogue warpgroup g: thread = row ----
         const int g = warp >> 2, wq = warp & 3, e = tid & 127;

@@ -75,8 +75,8 @@ __global__ void __launch_bounds__(NT, 1)
     const uint32_t a_hi = sbase + W_MAX + (uint32_t)wg * A_WG, a_lo = a_hi + A_PART;
 
     if (is_mma_warp) {
-        if ((tid & 31) == 0) {
-            tc::mbar_wait_bounded(wbar, 0);
+        tc::mbar_wait_bounded(wbar, 0);
+        if (tc::elect_one()) {             // not `lane == 0`: see tc.cuh
             const uint32_t idesc = tc::idesc_f16(128, nc);
             const uint64_t da_hi = tc::smem_desc(a_hi, 128, LBO), da_lo = tc::smem_desc(a_lo, 128, LBO);
             const uint64_t db_hi = tc::smem_desc(sbase, K * 16), db_lo = tc::smem_desc(sbase + w_part, K * 16);
@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(NT, 1)
                 tc::commit(mbar + wg);
             }
         }
+        __syncwarp();
     } else {
         uint8_t* a_hi_p = a_base + (size_t)wg * A_WG;
         uint8_t* a_lo_p = a_hi_p + A_PART;

@@ -45,6 +45,20 @@ __device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence
 // generic-proxy shared-memory writes -> visible to the async proxy (tensor core operand reads)
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// One lane of a CONVERGED warp (all 32 lanes must reach this).  Issuing tcgen05.mma under this predicate instead of
+// `lane == 0` lets ptxas keep descriptors in uniform registers without a per-instruction ELECT/branch loop.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        "  .reg .pred p;\n"
+        "  elect.sync _|p, 0xffffffff;\n"
+        "  selp.b32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // D[tmem] (+)= A[smem] * B[smem]; one elected thread.
 __device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                         uint32_t accumulate) {
