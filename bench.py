@@ -343,6 +343,16 @@ def run_ours(args):
     net_ms = float(tn.item())
     network_only = {"value": world * patches.shape[0] * PATCH * UP / (net_ms * 1e-3), "unit": "generated points/s",
                     "ms_per_step": net_ms, "patches_per_gpu": int(patches.shape[0])}
+    # the same network through the single C-ABI entry point (pf_upsample_patches), rank-local figure
+    with torch.no_grad():
+        eng = net.engine(dev)
+        eng.forward_c(patches, UP)
+        e0.record()
+        for _ in range(nrep):
+            eng.forward_c(patches, UP)
+        e1.record()
+        torch.cuda.synchronize()
+    network_only["c_abi_one_call_ms"] = e0.elapsed_time(e1) / nrep
 
     # ---- e2e: host buffers in and out through the public API ----------------------------------------------------
     for _ in range(2):

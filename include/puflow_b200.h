@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 3
+#define PF_ABI_VERSION 4
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -194,6 +194,25 @@ PF_API int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, floa
 PF_API long long pf_fps_work_floats(int B, int n);
 PF_API int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
+
+/* ---- whole network in one call --------------------------------------------------------------------------------
+ * pf_upsample_patches replaces PointInterpFlow.forward (/root/reference/modules/discrete/interpflow.py:327-337:
+ * knn_points -> feat_extract -> log_prob -> interp -> g) for a batch of patches:
+ *   xyz[Bp][N][3] (normalised patch coordinates) -> x[Bp][N*R][3] (row n*R + r), logp[1] (may be NULL: -mean log-likelihood,
+ *   interpflow.py:339-345).  16 <= N <= 65535, 1 <= R <= 32.
+ * It launches this library's tensor-core kernels on `stream`, allocates nothing and never synchronises (CUDA-graph
+ * capturable).  workspace: pf_upsample_workspace_bytes(Bp, N, R) bytes of device scratch, 256-byte aligned.
+ * model: the packed weights as ONE device blob of pf_model_bytes() bytes, 256-byte aligned; pf_model_entry(i, ...) for
+ * i in [0, PF_MODEL_ENTRIES) gives the name (<= 31 chars), byte offset and size of every piece, in blob order:
+ *   feat0.wpq (fp32 [3][128]) | per block i: feat<i>.bpq (fp32 [2R]) | feat<i>.wpq_tc (i >= 1, pf_linear_tc layout) |
+ *   feat<i>.wtc (pf_edgeconv_tc) | chain<i> (pf_cond_chain_tc) | flow_tc (6 x PF_FLOW_TC_BLOCK) | interp_tc | logdet_const
+ * (puflow_b200/packing.py pack_model_blob fills it from a reference state dict and can save it to a file). */
+#define PF_MODEL_ENTRIES 27
+PF_API int64_t pf_model_bytes(void);
+PF_API int pf_model_entry(int i, char* name32, int64_t* offset, int64_t* bytes);
+PF_API int64_t pf_upsample_workspace_bytes(int Bp, int N, int R);
+PF_API int pf_upsample_patches(const void* model, const float* xyz, int Bp, int N, int R, void* workspace,
+                        int64_t workspace_bytes, float* x, float* logp, void* stream);
 
 /* ---- on-disk format (host code, no CUDA) ------------------------------------------
  * The reference reads clouds with np.loadtxt(path, dtype=np.float32) (/root/reference/modules/discrete/upsample.py:42)

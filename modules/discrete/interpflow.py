@@ -385,6 +385,9 @@ class PointInterpFlow(nn.Module):
         # for small batches the ~100 launches of a call, not the kernels, bound the latency)
         if os.environ.get("PUFLOW_CUDA_GRAPH") == "1" and not torch.is_grad_enabled():
             return eng.forward_graphed(xyz, upratio)
+        # PUFLOW_ONE_CALL=1: the whole network through the single C-ABI entry point pf_upsample_patches
+        if os.environ.get("PUFLOW_ONE_CALL") == "1" and eng.flow_tc:
+            return eng.forward_c(xyz, upratio)
         return eng.forward(xyz, upratio)
 
     def log_prob(self, xyz: Tensor, cs: List[Tensor]):

@@ -46,6 +46,8 @@ SIGNATURES = {
     "pf_xyz_count": [ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int)],
     "pf_xyz_read": [ctypes.c_char_p, _vp, _i64, _i],
     "pf_xyz_write": [ctypes.c_char_p, _vp, _i64, _i],
+    "pf_model_entry": [_i, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)],
+    "pf_upsample_patches": [_vp, _vp, _i, _i, _i, _vp, _i64, _vp, _vp, _vp],
 }
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)
@@ -53,10 +55,15 @@ for _name, _args in SIGNATURES.items():
     _fn.restype = ctypes.c_int
 lib.pf_fps_work_floats.argtypes = [_i, _i]
 lib.pf_fps_work_floats.restype = ctypes.c_longlong
+lib.pf_model_bytes.argtypes = []
+lib.pf_model_bytes.restype = ctypes.c_int64
+lib.pf_upsample_workspace_bytes.argtypes = [_i, _i, _i]
+lib.pf_upsample_workspace_bytes.restype = ctypes.c_int64
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 3
+PF_ABI_VERSION = 4
+PF_MODEL_ENTRIES = 27
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
 PF_COND_TC_BLOCK = 35360
@@ -73,6 +80,18 @@ ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
 
 if lib.pf_abi_version() != PF_ABI_VERSION:
     raise ImportError(f"{LIB_PATH}: ABI version {lib.pf_abi_version()} != {PF_ABI_VERSION}; rebuild")
+
+
+def model_entries():
+    """[(name, offset, bytes)] of the packed-model blob, in blob order (the layout lives in csrc/model.cu)."""
+    out = []
+    for i in range(PF_MODEL_ENTRIES):
+        name = ctypes.create_string_buffer(32)
+        off, nbytes = ctypes.c_int64(), ctypes.c_int64()
+        if lib.pf_model_entry(i, name, ctypes.byref(off), ctypes.byref(nbytes)) != 0:
+            raise ImportError(f"pf_model_entry({i}) failed: {lib.pf_last_error().decode()}")
+        out.append((name.value.decode(), off.value, nbytes.value))
+    return out
 
 
 class PuflowError(RuntimeError):

@@ -35,6 +35,10 @@
 // takes channel r % CO for the edges [CO * (r / CO), CO * (r / CO + 1)) of the tile, so no epilogue thread idles.
 // Text below uses the (32, 128) numbers.
 
+#ifdef PF_PROF
+__device__ long long g_prof[32];
+#endif
+
 namespace {
 
 using namespace pf;
@@ -235,21 +239,28 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
         tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
         if (tc::elect_one()) {
             uint32_t rphase = 0;
+            PROF_DECL
             for (; t < total_tiles; t += stride) {
 #pragma unroll
                 for (int l = 1; l < 4; l++) {
+                    PROF_TICK(1)
                     tc::mbar_wait_bounded(ready + wg, rphase);
                     rphase ^= 1;
                     tc::fence_after_sync();
+                    PROF_TICK(0)
                     issue_dense(l);
                     tc::commit(mbar + wg);
                 }
+                PROF_TICK(1)
                 tc::mbar_wait_bounded(ready + wg, rphase);
                 rphase ^= 1;
                 tc::fence_after_sync();
+                PROF_TICK(0)
                 issue_out();
                 tc::commit(mbar + wg);
             }
+            PROF_TICK(1)
+            if (wg == 0) { PROF_DUMP(16, 2) }
         }
         __syncwarp();
     } else {
@@ -268,6 +279,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
     }
     tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
 
+    PROF_DECL
     for (; t < total_tiles; t += stride, tb ^= 1) {
         int patch, p0;
         tile_coords(t, patch, p0);
@@ -293,11 +305,13 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
             for (int c = 0; c < G; c++) q[c] = lrelu(q[c], slope);
             store_slice(0, q);
         }
+        PROF_TICK(0)
         tc::cp_async_wait<0>();
         tc::fence_async_smem();
         tc::fence_before_sync();
         tc::named_bar(bar_id, 128);
         if (e == 0) mbar_arrive(ready + wg);
+        PROF_TICK(1)
 
         // ---- layers 1..3 ----
 #pragma unroll 1
@@ -311,9 +325,11 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
             float q[G];
             read_q(l & 1, q);
             add_p(l, q);
+            PROF_TICK(2)
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
+            PROF_TICK(3)
             float acc[G];
             if constexpr (G == 32) {
                 tc::ld32(d_dense + lane_sel, acc);
@@ -328,11 +344,13 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
 #pragma unroll
             for (int c = 0; c < G; c++) acc[c] = lrelu(fmaf(acc[c], tc::WINV, q[c]), slope);
             store_slice(l, acc);
+            PROF_TICK(4)
             tc::cp_async_wait<0>();
             tc::fence_async_smem();
             tc::fence_before_sync();
             tc::named_bar(bar_id, 128);
             if (e == 0) mbar_arrive(ready + wg);
+            PROF_TICK(5)
         }
 
         // ---- conv_out (transposed) + max over the 16 neighbours ----
@@ -361,9 +379,11 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
 #pragma unroll
             for (int i = 0; i < 2 * NCH; i++)
                 pv[i] = __ldg(ppq + (size_t)min(p0 + 2 * grp * NCH + i, N - 1) * R2 + 4 * G + ch);
+            PROF_TICK(6)
             tc::mbar_wait_bounded(mbar + wg, phase);
             phase ^= 1;
             tc::fence_after_sync();
+            PROF_TICK(7)
 #pragma unroll
             for (int c = 0; c < NCH; c++) {                               // 32 edges = 2 points per chunk
                 float acc[32];
@@ -395,10 +415,13 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG>::NT, 1)
                 }
             }
         }
+        PROF_TICK(8)
         tc::cp_async_wait<0>();
         tc::fence_before_sync();
         tc::named_bar(bar_id, 128);          // D, H and jbuf[tb] are free; ps / qs[0] / jbuf[tb^1] hold the next tile
+        PROF_TICK(9)
     }
+    if (tid == 0) { PROF_DUMP(0, 10) }
     }   // epilogue warpgroups
 
     tc::fence_before_sync();
@@ -445,6 +468,12 @@ static int edgeconv_tc_dispatch(const float* pq, const int32_t* idx, const void*
     PF_CHECK_ARG(false, "pf_edgeconv_tc: (G, C_out) = (%d, %d) not in {(8,32), (16,64), (32,128)}", G_, C_out);
     return 0;
 }
+
+#ifdef PF_PROF
+extern "C" __attribute__((visibility("default"))) int pf_debug_edgeconv_prof(long long* host32) {
+    return cudaMemcpyFromSymbol(host32, g_prof, sizeof(long long) * 32) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 extern "C" int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K,
                               int G_, int C_out, float slope, void* stream) {

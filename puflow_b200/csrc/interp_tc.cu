@@ -49,15 +49,8 @@ constexpr uint32_t COL_H = 16, COL_D = 144;               // K offsets inside X
 constexpr uint32_t TM_M12_HI = 0, TM_M12_LO = 104, TM_DA = 208, TM_DB = 336, TM_DC = 464, TM_COLS = 512;   // DA 128, DB 128, DC 32
 constexpr uint32_t M12_GLOBAL = W_BYTES, M12_PART = 128 * 104 * 4;
 
-#ifdef PF_INTERP_PROF   // dev builds only: per-stage clock64() totals of CTA 0 (epilogue thread 0 and the MMA thread)
+#ifdef PF_PROF   // dev builds only: per-stage clock64() totals of CTA 0 (epilogue thread 0 and the MMA thread), tc.cuh
 __device__ long long g_prof[32];
-#define PROF_DECL long long pacc[16] = {0}; long long pt0 = clock64();
-#define PROF_TICK(k) { const long long pt1 = clock64(); pacc[k] += pt1 - pt0; pt0 = pt1; }
-#define PROF_DUMP(base, n) if (blockIdx.x == 0) { for (int i = 0; i < n; i++) g_prof[base + i] = pacc[i]; }
-#else
-#define PROF_DECL
-#define PROF_TICK(k)
-#define PROF_DUMP(base, n)
 #endif
 
 template <int RP>   // logits evaluated per edge (R rounded up to 4 / 8 / 16 / 32)
@@ -429,7 +422,7 @@ int launch(const float* xyz, const float* z, const int32_t* idx, int ldidx, cons
 
 }  // namespace
 
-#ifdef PF_INTERP_PROF
+#ifdef PF_PROF
 extern "C" __attribute__((visibility("default"))) int pf_debug_interp_prof(long long* host32) {
     return cudaMemcpyFromSymbol(host32, g_prof, sizeof(long long) * 32) == cudaSuccess ? 0 : 1;
 }

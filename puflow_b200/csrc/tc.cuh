@@ -12,6 +12,18 @@
 
 #include "common.cuh"
 
+// Dev-only stage timers (make EXTRA=-DPF_PROF): a thread accumulates clock64() deltas per stage and CTA 0 dumps them into
+// the file's `__device__ long long g_prof[32]`, read back through a pf_debug_*_prof export (tools/dev_*_prof.py).
+#ifdef PF_PROF
+#define PROF_DECL long long pacc[16] = {0}; long long pt0 = clock64();
+#define PROF_TICK(k) { const long long pt1 = clock64(); pacc[k] += pt1 - pt0; pt0 = pt1; }
+#define PROF_DUMP(base, n) if (blockIdx.x == 0) { for (int i = 0; i < n; i++) g_prof[base + i] = pacc[i]; }
+#else
+#define PROF_DECL
+#define PROF_TICK(k)
+#define PROF_DUMP(base, n)
+#endif
+
 namespace pf {
 namespace tc {
 

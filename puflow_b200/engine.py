@@ -40,6 +40,7 @@ class PUFlowEngine:
         # same switch for the flow stack (PUFLOW_FLOW=ffma keeps flow.cu's FP32 kernels)
         self.flow_tc = self.use_tc and os.environ.get("PUFLOW_FLOW", "tc") != "ffma"
         self._graphs = {}                                # (shape, upratio) -> captured CUDA graph, see forward_graphed
+        self._model_blob = None                          # packed once on first use of forward_c
 
     def _linear(self, a, wd, name, bias=None, act=ACT_NONE):
         """Per-point linear layer: tensor-core kernel when a packed blob exists (K in {16..128}), FFMA otherwise."""
@@ -172,6 +173,17 @@ class PUFlowEngine:
         if return_all:
             return dict(knn_idx=idx, feats=feats, cs=cs, z=z, logp_x=logp_x, zup=zup, x=x)
         return x, logp_x
+
+    @torch.no_grad()
+    def forward_c(self, xyz: torch.Tensor, upratio: int = 4):
+        """forward() through ONE C-ABI call (pf_upsample_patches, csrc/model.cu): same kernels, same results bit for bit
+        in x; logp_x reduced in float64 on the device.  What a non-Python host would call."""
+        if xyz.dim() != 3 or xyz.shape[2] != 3:
+            raise ValueError(f"expected xyz[B,N,3], got {tuple(xyz.shape)}")
+        if self._model_blob is None:
+            from .packing import pack_model_blob
+            self._model_blob = pack_model_blob(self.w).to(self.device)
+        return ops.upsample_patches(self._model_blob, xyz.contiguous().float(), upratio)
 
     def sample(self, xyz: torch.Tensor, upratio: int = 4):
         return self.forward(xyz, upratio)[0]

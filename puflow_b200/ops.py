@@ -341,6 +341,42 @@ def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.
     return out
 
 
+# ---- whole network in one C call ---------------------------------------------------------------------
+_workspaces = {}
+
+
+def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_logp: bool = True):
+    """pf_upsample_patches: xyz[Bp,N,3] -> (x[Bp, N*R, 3], logp scalar tensor or None) with the whole of
+    PointInterpFlow.forward (interpflow.py:327-337) launched from C on the current stream.  model_blob: uint8 CUDA tensor
+    from packing.pack_model_blob.  The scratch buffer is kept per (device, size) and re-used by later calls on the same
+    stream order; 24 kernel launches (22 without logp)."""
+    _chk(model_blob, "model_blob", torch.uint8), _chk(xyz, "xyz")
+    if xyz.dim() != 3 or xyz.shape[2] != 3:
+        raise ValueError(f"upsample_patches: expected xyz[Bp,N,3], got {tuple(xyz.shape)}")
+    if model_blob.numel() != lib.pf_model_bytes():
+        raise ValueError("upsample_patches: model blob has the wrong size")
+    Bp, Npts, _ = xyz.shape
+    need = lib.pf_upsample_workspace_bytes(Bp, Npts, R)
+    if need < 0:
+        raise ValueError(f"upsample_patches: bad sizes Bp={Bp} N={Npts} R={R}")
+    key = (xyz.device, need)
+    ws = _workspaces.get(key)
+    if ws is None:
+        _workspaces.clear()                      # one live workspace: shapes rarely alternate, GBs do not pile up
+        ws = _workspaces[key] = torch.empty((max(need, 1),), dtype=torch.uint8, device=xyz.device)
+    x = torch.empty((Bp, Npts * R, 3), dtype=torch.float32, device=xyz.device)
+    logp = torch.empty((), dtype=torch.float32, device=xyz.device) if want_logp else None
+    with _dev(xyz):
+        N.check(lib.pf_upsample_patches(model_blob.data_ptr(), xyz.data_ptr(), Bp, Npts, R, ws.data_ptr(), need,
+                                        x.data_ptr(), logp.data_ptr() if want_logp else None, _stream()),
+                "pf_upsample_patches")
+    if Bp:
+        count_launches(((Bp + 65534) // 65535) + 3 * 6 + 3 + (2 if want_logp else 0))
+    elif want_logp:
+        logp.fill_(float("nan"))
+    return x, logp
+
+
 # ---- caller side ---------------------------------------------------------------------------------
 def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
     """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0).

@@ -449,3 +449,31 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
             return [cast(v) for v in o]
         return o
     return cast(out)
+
+
+def pack_model_blob(w: Dict) -> torch.Tensor:
+    """pack_state_dict(...) result -> the single uint8 blob pf_upsample_patches takes (layout: csrc/model.cu, enumerated
+    through pf_model_entry so that C and Python cannot disagree).  CPU tensor; `.to(device)` it, or `.numpy().tofile(path)`
+    for a host that is not Python."""
+    from . import _native
+
+    def piece(name):
+        if name == "flow_tc":
+            return w["flow_tc"]
+        if name == "interp_tc":
+            return w["interp"]["tc"]
+        if name == "logdet_const":
+            return torch.tensor([float(w["logdet_const"])], dtype=torch.float32)
+        if name.startswith("chain"):
+            return w["chain_tc"][int(name[5:])]
+        blk, key = name.split(".")
+        return w["feat"][int(blk[4:])][key]
+
+    blob = torch.zeros(_native.lib.pf_model_bytes(), dtype=torch.uint8)
+    for name, off, nbytes in _native.model_entries():
+        t = piece(name).detach().cpu().contiguous()
+        raw = t.view(torch.uint8).reshape(-1) if t.dtype != torch.uint8 else t.reshape(-1)
+        if raw.numel() != nbytes:
+            raise ValueError(f"model blob entry {name}: {raw.numel()} bytes packed, {nbytes} expected")
+        blob[off:off + nbytes] = raw
+    return blob

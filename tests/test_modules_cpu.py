@@ -12,13 +12,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "puflow_b200.h")).read()
-    declared = set(re.findall(r"PF_API\s+(?:const\s+char\s*\*|int|long\s+long)\s+(pf_\w+)\s*\(", hdr))
+    declared = set(re.findall(r"PF_API\s+(?:const\s+char\s*\*|int|int64_t|long\s+long)\s+(pf_\w+)\s*\(", hdr))
     assert len(declared) >= 12, declared
     lib = ctypes.CDLL(os.path.join(ROOT, "puflow_b200", "_lib", "libpuflow_b200.so"))
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
     from puflow_b200 import _native
-    assert set(_native.SIGNATURES) | {"pf_last_error", "pf_fps_work_floats"} == declared
+    assert set(_native.SIGNATURES) | {"pf_last_error", "pf_fps_work_floats", "pf_model_bytes",
+                                      "pf_upsample_workspace_bytes"} == declared
     assert lib.pf_abi_version() == _native.PF_ABI_VERSION
 
 
@@ -26,7 +27,7 @@ def test_header_constants_match_binding():
     hdr = open(os.path.join(ROOT, "include", "puflow_b200.h")).read()
     from puflow_b200 import _native
     for name in ("PF_COND_BLOB", "PF_FLOW_BLOB", "PF_INTERP_BLOB", "PF_ABI_VERSION", "PF_COND_TC_BLOCK",
-                 "PF_FLOW_TC_BLOCK", "PF_EDGECONV_TC_BLOB", "PF_INTERP_TC_BLOB"):
+                 "PF_FLOW_TC_BLOCK", "PF_EDGECONV_TC_BLOB", "PF_INTERP_TC_BLOB", "PF_MODEL_ENTRIES"):
         assert int(re.search(rf"#define {name} (\d+)", hdr).group(1)) == getattr(_native, name)
 
 
@@ -90,3 +91,23 @@ def test_upsample_entry_point_signature():
     params = list(inspect.signature(upsample.upsampling).parameters)
     assert params[:8] == ["data_paths", "target_path", "checkpoint_path", "up_ratio", "num_outlier", "num_patch",
                           "num_upsampling", "seed"]
+
+
+def _build_c_host(tmp_path):
+    import subprocess
+    exe = str(tmp_path / "upsample_patches")
+    libdir = os.path.join(ROOT, "puflow_b200", "_lib")
+    cmd = ["gcc", "-O2", "-I" + os.path.join(ROOT, "include"), "-I/usr/local/cuda/include",
+           os.path.join(ROOT, "examples", "upsample_patches.c"), "-o", exe, "-L" + libdir, "-lpuflow_b200",
+           "-L/usr/local/cuda/lib64", "-lcudart", "-Wl,-rpath," + libdir]
+    subprocess.run(cmd, check=True, capture_output=True)
+    return exe
+
+
+def test_header_is_plain_c_and_the_c_host_links(tmp_path):
+    """include/puflow_b200.h compiles as C and examples/upsample_patches.c (a host with no Python) links against the
+    library; without arguments it prints its usage and exits 1 (no GPU needed)."""
+    import subprocess
+    exe = _build_c_host(tmp_path)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and "usage" in r.stderr

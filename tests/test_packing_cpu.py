@@ -1,6 +1,7 @@
 """CPU: the packed / factored arithmetic the kernels implement (tests/emulate.py on
 puflow_b200.packing output) reproduces the unmodified reference's stage outputs (tests/golden)."""
 import numpy as np
+import pytest
 import torch
 
 from puflow_b200 import packing
@@ -122,3 +123,33 @@ def test_tensor_core_blobs_decode_to_the_weights(state_dict):
         for r in (0, Co - 1, Co % 128, 127):
             for j in range(4):
                 assert ((hi + lo)[r, j * gp:j * gp + g] - wo[r % Co, j * g:(j + 1) * g]).abs().max() <= 2.0 ** -21 * wo.abs().max()
+
+
+def test_model_blob_layout(state_dict):
+    """The single blob of pf_upsample_patches: the layout is enumerated by the C library (pf_model_entry), entries are
+    256-byte aligned, in order, non-overlapping, and each holds exactly the bytes of the piece the per-kernel path uses."""
+    from puflow_b200 import _native
+    w = packing.pack_state_dict(state_dict, "cpu")
+    blob = packing.pack_model_blob(w)
+    ents = _native.model_entries()
+    assert len(ents) == _native.PF_MODEL_ENTRIES and blob.numel() == _native.lib.pf_model_bytes()
+    end = 0
+    for name, off, nbytes in ents:
+        assert off % 256 == 0 and off >= end and nbytes > 0, (name, off, nbytes)
+        end = off + nbytes
+    assert end <= blob.numel() < end + 256
+    by = {n: (o, b) for n, o, b in ents}
+    o, b = by["feat3.wtc"]
+    assert torch.equal(blob[o:o + b], w["feat"][3]["wtc"])
+    o, b = by["feat0.wpq"]
+    assert torch.equal(blob[o:o + b].view(torch.float32).view(3, 128), w["feat"][0]["wpq"])
+    o, b = by["chain5"]
+    assert torch.equal(blob[o:o + b], w["chain_tc"][5])
+    o, b = by["flow_tc"]
+    assert torch.equal(blob[o:o + b].view(6, -1), w["flow_tc"])
+    o, b = by["logdet_const"]
+    assert blob[o:o + b].view(torch.float32).item() == pytest.approx(float(w["logdet_const"]), rel=1e-7)
+    assert "feat0.wpq_tc" not in by and "feat1.wpq_tc" in by
+    # workspace size: monotone, -1 for nonsense
+    f = _native.lib.pf_upsample_workspace_bytes
+    assert f(32, 256, 4) > 0 and f(64, 256, 4) > f(32, 256, 4) and f(-1, 256, 4) == -1

@@ -1,4 +1,4 @@
-"""Per-stage clock64() totals of interp_tc (library built with EXTRA=-DPF_INTERP_PROF)."""
+"""Per-stage clock64() totals of interp_tc (library built with EXTRA=-DPF_PROF)."""
 import ctypes, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
