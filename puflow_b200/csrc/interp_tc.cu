@@ -31,7 +31,7 @@ namespace {
 using namespace pf;
 
 constexpr int KN = 8, PT = 16, TM = 128;
-constexpr int NT = 160;                                   // 4 epilogue warps + 1 MMA-issuing warp
+constexpr int NT = 288;                                   // 2 x 4 epilogue warps (column halves of one tile) + 1 MMA-issuing warp
 constexpr float S_CTX = 0.05f, S_DEF = 0.01f;             // interpflow.py:206,217 / nn.LeakyReLU() default :94,97,147,150
 
 // ---- shared memory map (bytes) ----
@@ -65,11 +65,12 @@ __global__ void __launch_bounds__(NT, 1)
     uint64_t* ready = wbar + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wbar + 3);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const bool is_mma_warp = warp == 4;
-    const int e = tid & 127;
+    const bool is_mma_warp = warp == 8;
+    const int e = tid & 127;          // row of the tile (TMEM lane)
+    const int half = (warp >> 2) & 1;  // which half of every stage's columns this epilogue warpgroup handles
 
     if (tid == 0) {
-        mbar_init(wbar, 1), mbar_init(mbar, 1), mbar_init(ready, 1);
+        mbar_init(wbar, 1), mbar_init(mbar, 1), mbar_init(ready, 8);   // ready: one arrive per epilogue warp
         mbar_fence_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, TM_COLS);
@@ -83,8 +84,8 @@ __global__ void __launch_bounds__(NT, 1)
         bulk_g2s_chunked(smem, wblob, W_BYTES, wbar);
     }
     if (!is_mma_warp) {   // M12g -> TMEM: thread = lane = output channel; 104 columns per part (32+32+32+8)
-#pragma unroll 1
-        for (int part = 0; part < 2; part++) {
+        {
+            const int part = half;
             const uint32_t* src = reinterpret_cast<const uint32_t*>(wblob + M12_GLOBAL + (size_t)part * M12_PART) + e * 104;
             const uint32_t dst = tmem_base + lane_sel + (part ? TM_M12_LO : TM_M12_HI);
 #pragma unroll 1
@@ -203,11 +204,13 @@ __global__ void __launch_bounds__(NT, 1)
             *reinterpret_cast<uint4*>(xh_p + x_row + chunk * 128) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4*>(xl_p + x_row + chunk * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         };
-        auto publish = [&]() {   // operands written -> MMA warp may issue
+        // This warp's operand rows are written and its accumulator reads are done.  No block barrier: epilogue threads never
+        // read each other's shared-memory writes (only the MMA does), and the MMA warp waits for all 8 warps' arrivals.
+        auto publish = [&]() {
             tc::fence_async_smem();
             tc::fence_before_sync();
-            tc::named_bar(1, 128);
-            if (e == 0) mbar_arrive(ready);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(ready);
         };
         auto wait_mma = [&]() {
             tc::mbar_wait_bounded(mbar, phase);
@@ -251,16 +254,15 @@ __global__ void __launch_bounds__(NT, 1)
                 const float dist = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
                 const float g0[8] = {xi0, xi1, xi2, xj0, xj1, xj2, -dx, -dy};
                 const float g1[8] = {-dz, dist, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                store8(0, g0);
-                store8(1, g1);
+                if (half == 0) store8(0, g0); else store8(1, g1);
             }
             publish();
             PROF_TICK(0)
             // ---- 1: d1 -> X[:, 144:208), h0 -> X[:, 16:32) ----
             wait_mma();
             PROF_TICK(1)
-#pragma unroll
-            for (int c = 0; c < 2; c++) {
+            {
+                const int c = half;
                 float a[32], b[32];                                      // big half, small half (see issue2)
                 tc::ld32(d_b + 32 * c, a), tc::ld32(d_b + 64 + 32 * c, b);
 #pragma unroll
@@ -269,19 +271,19 @@ __global__ void __launch_bounds__(NT, 1)
                 for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
             }
             {
-                float a[32];
-                tc::ld32(d_c, a);
+                float a[8];
+                tc::ld8_sum(d_c + 8 * half, d_c + 16 + 8 * half, a);
 #pragma unroll
-                for (int u = 0; u < 16; u++) a[u] = lrelu((a[u] + a[16 + u]) * tc::WINV, S_CTX);
-                store8(COL_H / 8, a), store8(COL_H / 8 + 1, a + 8);
+                for (int u = 0; u < 8; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
+                store8(COL_H / 8 + half, a);
             }
             publish();
             PROF_TICK(2)
             // ---- 2: d2 (overwrites d1), h1 ----
             wait_mma();
             PROF_TICK(3)
-#pragma unroll
-            for (int c = 0; c < 2; c++) {
+            {
+                const int c = half;
                 float a[32], b[32];
                 tc::ld32(d_b + 32 * c, a), tc::ld32(d_b + 64 + 32 * c, b);
 #pragma unroll
@@ -300,11 +302,11 @@ __global__ void __launch_bounds__(NT, 1)
                     wait_mma();
                     PROF_TICK(5)
                 }
-                float a[32];
-                tc::ld32(d_c, a);
+                float a[8];
+                tc::ld8_sum(d_c + 8 * half, d_c + 16 + 8 * half, a);
 #pragma unroll
-                for (int u = 0; u < 16; u++) a[u] = lrelu((a[u] + a[16 + u]) * tc::WINV, S_CTX);
-                store8(COL_H / 8 + 2 * l, a), store8(COL_H / 8 + 2 * l + 1, a + 8);
+                for (int u = 0; u < 8; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
+                store8(COL_H / 8 + 2 * l + half, a);
                 publish();
                 if (l > 1) { PROF_TICK(6) } else { PROF_TICK(4) }
             }
@@ -314,7 +316,7 @@ __global__ void __launch_bounds__(NT, 1)
             {
                 uint8_t* th = smem + T0_OFF + (uint32_t)(e >> 3) * 2048 + (uint32_t)(e & 7) * 16;
 #pragma unroll 1
-                for (int c = 0; c < 4; c++) {
+                for (int c = 2 * half; c < 2 * half + 2; c++) {
                     float a[32];
                     tc::ld32(d_a + 32 * c, a);
 #pragma unroll
@@ -336,8 +338,8 @@ __global__ void __launch_bounds__(NT, 1)
             PROF_TICK(9)
             {
                 uint8_t* t1h = smem + T1_OFF + (uint32_t)(e >> 3) * T1_SBO + (uint32_t)(e & 7) * 16;
-#pragma unroll
-                for (int c = 0; c < 2; c++) {
+                {
+                    const int c = half;
                     float a[32], b[32];
                     tc::ld32(d_a + 32 * c, a), tc::ld32(d_a + 64 + 32 * c, b);
 #pragma unroll
@@ -359,23 +361,26 @@ __global__ void __launch_bounds__(NT, 1)
             wait_mma();
             PROF_TICK(11)
             {
-                float lg[RP];
-                if constexpr (RP == 32) {
-                    float sm[32];
-                    tc::ld32(d_a, lg), tc::ld32(d_a + 32, sm);
-#pragma unroll
-                    for (int r = 0; r < RP; r++) lg[r] += sm[r];
-                } else {
+                constexpr int RH = RP / 2;                                 // logits per warpgroup: r in [r0, r0 + RH)
+                const int r0 = half * RH;
+                float lg[RH];
+                if constexpr (RH == 16) {
                     float a16[16], s16[16];
-                    tc::ld16(d_a, a16), tc::ld16(d_a + 32, s16);
+                    tc::ld16(d_a + r0, a16), tc::ld16(d_a + 32 + r0, s16);
 #pragma unroll
-                    for (int r = 0; r < RP; r++) lg[r] = a16[r] + s16[r];
+                    for (int r = 0; r < RH; r++) lg[r] = a16[r] + s16[r];
+                } else {
+                    float a8[8], s8[8];
+                    tc::ld8(d_a + r0, a8), tc::ld8(d_a + 32 + r0, s8);
+#pragma unroll
+                    for (int r = 0; r < RH; r++) lg[r] = a8[r] + s8[r];
                 }
                 const bool writer = (e & 7) == 0 && (p0 + (e >> 3)) < N;
                 float* dst = out + row_i * R * 3;
 #pragma unroll
-                for (int r = 0; r < RP; r++) {
-                    float v = fmaf(lg[r], tc::WINV, b6[r]);
+                for (int rr = 0; rr < RH; rr++) {
+                    const int r = r0 + rr;
+                    float v = fmaf(lg[rr], tc::WINV, b6[r]);
                     float mx = v;
 #pragma unroll
                     for (int o = 1; o < 8; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -394,8 +399,8 @@ __global__ void __launch_bounds__(NT, 1)
                     if (writer && r < R) dst[r * 3] = o0, dst[r * 3 + 1] = o1, dst[r * 3 + 2] = o2;
                 }
             }
-            tc::fence_before_sync();
-            tc::named_bar(1, 128);     // X / t1 / D are free for the next tile
+            // no barrier at the tile end either: every MMA that reads X / t0 / t1 has completed (the logits commit was waited
+            // for), and the next tile's first MMA is issued only after all 8 warps have arrived again
             PROF_TICK(12)
         }
         if (tid == 0) { PROF_DUMP(0, 13) }
