@@ -25,6 +25,10 @@ namespace {
 #define PF_FPS_THREADS 640                   // 20 warps: the 1,280 buckets of a 40,960-point cloud are 2 full warp-iterations each
 #endif
 constexpr int FT = PF_FPS_THREADS, NW = FT / 32;
+#ifndef PF_FPS_BPL
+#define PF_FPS_BPL 2
+#endif
+constexpr int BPL = PF_FPS_BPL;              // buckets per lane held in registers (REGBOX path)
 static_assert(FT % 32 == 0 && NW <= 32, "per-warp partial results are reduced by one warp");
 constexpr int CELLS = 4096;                  // 16^3 grid
 constexpr float INIT_D = 1e10f;              // fps.py:53
@@ -69,7 +73,10 @@ struct Slot {
 };
 
 // work (per cloud, npad = 32 * nb entries each): sx | sy | sz | oidx | md (md only used when !MD_SMEM)
-template <bool MD_SMEM>
+// REGBOX (KB <= 32 BPL): every lane keeps the box, the running maximum and the cached winner of its own (at most BPL)
+// buckets in registers for the whole kernel -- the bucket -> lane map never changes -- so a round's scan of the 1,280
+// boxes touches no shared memory at all (the scan, not the distance updates, is what a round spends its issue slots on).
+template <bool MD_SMEM, bool REGBOX>
 __global__ void __launch_bounds__(FT, 1)
     fps_bucket_kernel(const float* __restrict__ xyz, int n, int npoint, int32_t* __restrict__ out, float* work, int nb,
                       int KB) {
@@ -192,6 +199,96 @@ __global__ void __launch_bounds__(FT, 1)
     long long tacc_[5] = {0, 0, 0, 0, 0};
     long long tprev_ = clock64();
 #endif
+    if constexpr (REGBOX) {
+        // per-lane copy of its buckets' metadata (h = 0: bucket k = lane, h = 1: k = lane + 32 of this warp)
+        float blx[BPL], bly[BPL], blz[BPL], bhx[BPL], bhy[BPL], bhz[BPL], bmr[BPL], wx[BPL], wy[BPL], wz[BPL];
+        unsigned wo[BPL];
+#pragma unroll
+        for (int h = 0; h < BPL; h++) {
+            const int k = lane + 32 * h, slot = w * KB + min(k, KB - 1);
+            const float4 blo = bbq[2 * slot], bhi = bbq[2 * slot + 1];
+            const bool ok = k < KB;
+            blx[h] = blo.x, bly[h] = blo.y, blz[h] = blo.z, bhx[h] = bhi.x, bhy[h] = bhi.y, bhz[h] = bhi.z;
+            bmr[h] = ok ? blo.w : 0.f;                                  // 0: never active, never the maximum
+            wo[h] = ok ? wc_o[slot] : 0xffffffffu;
+            wx[h] = wc_x[slot], wy[h] = wc_y[slot], wz[h] = wc_z[slot];
+        }
+        for (int s = 0; s + 1 < npoint; s++) {
+            bool act[BPL];
+#pragma unroll
+            for (int h = 0; h < BPL; h++) {
+                const float ex = fmaxf(fmaxf(blx[h] - cx, cx - bhx[h]), 0.f);
+                const float ey = fmaxf(fmaxf(bly[h] - cy, cy - bhy[h]), 0.f);
+                const float ez = fmaxf(fmaxf(blz[h] - cz, cz - bhz[h]), 0.f);
+                act[h] = (ex * ex + ey * ey + ez * ez) * SAFE < bmr[h];
+            }
+#pragma unroll
+            for (int h = 0; h < BPL; h++) {
+                unsigned mask = __ballot_sync(0xffffffffu, act[h]);
+                while (mask) {
+                    int kk[4];
+                    float px[4], py[4], pz[4];
+                    unsigned po[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        kk[u] = -1;
+                        if (mask) {
+                            kk[u] = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            const int p = 32 * (w + NW * (32 * h + kk[u])) + lane;
+                            px[u] = sx[p], py[u] = sy[p], pz[u] = sz[p], po[u] = so[p];
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (kk[u] >= 0) {
+                            const int p = 32 * (w + NW * (32 * h + kk[u])) + lane;
+                            const float d = sqdist(px[u], py[u], pz[u], cx, cy, cz);
+                            float m = MD_SMEM ? md_s[p] : mdg[p];
+                            if (d < m) {
+                                m = d;
+                                if (MD_SMEM) md_s[p] = d; else mdg[p] = d;
+                            }
+                            const float nm = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(m)));
+                            const unsigned o = (m == nm) ? po[u] : 0xffffffffu;
+                            const unsigned omin = __reduce_min_sync(0xffffffffu, o);
+                            const int srcl = __ffs(__ballot_sync(0xffffffffu, o == omin)) - 1;   // lane holding the winner
+                            const float tx = __shfl_sync(0xffffffffu, px[u], srcl), ty = __shfl_sync(0xffffffffu, py[u], srcl),
+                                        tz = __shfl_sync(0xffffffffu, pz[u], srcl);
+                            if (lane == kk[u]) bmr[h] = nm, wo[h] = omin, wx[h] = tx, wy[h] = ty, wz[h] = tz;
+                        }
+                    }
+                }
+            }
+            // this lane's better bucket, then the warp's, then (after the barrier) the block's
+            float lmax = bmr[0], bx = wx[0], by = wy[0], bz = wz[0];
+            unsigned lo_ = wo[0];
+#pragma unroll
+            for (int h = 1; h < BPL; h++)
+                if (bmr[h] > lmax || (bmr[h] == lmax && wo[h] < lo_)) lmax = bmr[h], lo_ = wo[h], bx = wx[h], by = wy[h], bz = wz[h];
+            Slot* sl = slots + (s & 1) * NW;
+            {
+                const float Mw = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(lmax)));
+                const unsigned cand = (lmax == Mw) ? lo_ : 0xffffffffu;
+                const unsigned omin = __reduce_min_sync(0xffffffffu, cand);
+                const int src = __ffs(__ballot_sync(0xffffffffu, cand == omin && lmax == Mw)) - 1;
+                if (lane == src) sl[w].m = Mw, sl[w].oidx = omin, sl[w].x = bx, sl[w].y = by, sl[w].z = bz;
+            }
+            __syncthreads();
+            {
+                const int l = min(lane, NW - 1);
+                const float mw = sl[l].m;
+                const unsigned ow = sl[l].oidx;
+                const float M = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(mw)));
+                const unsigned cand = (mw == M) ? ow : 0xffffffffu;
+                const unsigned omin = __reduce_min_sync(0xffffffffu, cand);
+                const int src = min(__ffs(__ballot_sync(0xffffffffu, cand == omin && mw == M)) - 1, NW - 1);
+                cx = sl[src].x, cy = sl[src].y, cz = sl[src].z;
+                if (tid == 0) out[(size_t)cloud * npoint + s + 1] = (int32_t)omin;
+            }
+        }
+        return;
+    }
     for (int s = 0; s + 1 < npoint; s++) {
         FSTAMP(0);
         // (1) update the buckets whose box is closer to the new sample than their current maximum
@@ -322,12 +419,17 @@ extern "C" int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32
     fps_bucket_geometry(n, &nb, &KB, &s_md, &s_nomd);
     cudaStream_t st = (cudaStream_t)stream;
     if (s_md <= 227 * 1024) {
-        if (int rc = pf_smem_optin(fps_bucket_kernel<true>, s_md)) return rc;
-        fps_bucket_kernel<true><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB);
+        if (KB <= 32 * BPL) {    // bucket metadata in registers (BPL buckets per lane)
+            if (int rc = pf_smem_optin(fps_bucket_kernel<true, true>, s_md)) return rc;
+            fps_bucket_kernel<true, true><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB);
+        } else {
+            if (int rc = pf_smem_optin(fps_bucket_kernel<true, false>, s_md)) return rc;
+            fps_bucket_kernel<true, false><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB);
+        }
     } else {
         PF_CHECK_ARG(s_nomd <= 227 * 1024, "pf_fps_bucketed: n=%d too large (bucket metadata exceeds shared memory)", n);
-        if (int rc = pf_smem_optin(fps_bucket_kernel<false>, s_nomd)) return rc;
-        fps_bucket_kernel<false><<<B, FT, s_nomd, st>>>(xyz, n, npoint, idx, work, nb, KB);
+        if (int rc = pf_smem_optin(fps_bucket_kernel<false, false>, s_nomd)) return rc;
+        fps_bucket_kernel<false, false><<<B, FT, s_nomd, st>>>(xyz, n, npoint, idx, work, nb, KB);
     }
     return pf_launch_status("fps_bucket_kernel");
 }
