@@ -385,8 +385,12 @@ class PointInterpFlow(nn.Module):
         # for small batches the ~100 launches of a call, not the kernels, bound the latency)
         if os.environ.get("PUFLOW_CUDA_GRAPH") == "1" and not torch.is_grad_enabled():
             return eng.forward_graphed(xyz, upratio)
-        # PUFLOW_ONE_CALL=1: the whole network through the single C-ABI entry point pf_upsample_patches
-        if os.environ.get("PUFLOW_ONE_CALL") == "1" and eng.flow_tc:
+        # The whole network through the single C-ABI entry point pf_upsample_patches (same kernels, same results bit for
+        # bit, no per-kernel Python); the kernel-by-kernel path is kept for per-launch timing (bench.py's breakdown),
+        # for the FFMA A/B switches and with PUFLOW_ONE_CALL=0.
+        if eng.flow_tc and os.environ.get("PUFLOW_ONE_CALL", "1") != "0" and not ops.per_launch_events_wanted() \
+                and os.environ.get("PUFLOW_EDGECONV_SMALL") != "ffma" and os.environ.get("PUFLOW_PRESPLIT", "1") != "0" \
+                and 16 <= xyz.shape[1] <= 65535 and 1 <= upratio <= 32:
             return eng.forward_c(xyz, upratio)
         return eng.forward(xyz, upratio)
 

@@ -38,6 +38,12 @@ def set_launch_log(log):
     return prev
 
 
+def per_launch_events_wanted() -> bool:
+    """True while a LaunchLog with per-launch CUDA events is installed (bench.py's breakdown / roofline pass): callers then
+    go kernel by kernel through the wrappers below instead of through the one-call C entry point."""
+    return _log is not None and _log.events
+
+
 def count_launches(n: int):
     """Account for `n` kernels launched outside the wrappers below (a CUDA-graph replay)."""
     if _log is not None:
