@@ -17,6 +17,7 @@
 //   3..8  h_l = lrelu([geo|h_<l].Wh_l)  (N=16, K=16+16l)
 //   9  t0^T[128 ch x 128 edges] = M12g . X^T  (K=208; M12g = mlp.0 o (mlp.6 | conv_out) composed on the host, resident
 //      in TMEM as the A operand); thread = channel; t0 is written back as an M-major (edge-contiguous) operand
+//      -- its 13 K-steps are issued as their X columns become final, behind the MMAs of stages 3..8, so only h6 / h7 remain
 //  10  t1 = lrelu(t0.W3 + b3)  (A = t0 M-major, N=64, K=128)      11  logits = t1.W6 + b6  (N=32, K=64)
 //  then softmax over the 8 neighbours (8 consecutive lanes) and the weighted sum of the neighbours' latents.
 // Per-stage clock64() totals (tools/dev_interp_prof.py, -DPF_INTERP_PROF) showed the MMA-issuing thread, not the tensor
@@ -141,6 +142,16 @@ __global__ void __launch_bounds__(NT, 1)
                 tc::fence_after_sync();
                 PROF_TICK(0)
             };
+            // One K-step (16 columns of X) of t0^T = M12g . X^T, A from tensor memory (8 columns per K-step): the cross terms go
+            // to the d-branch's accumulator (dead after stage 2), the hi . hi term to d_a; the epilogue adds the two.  The 13
+            // K-steps are issued as their X columns become final, BEHIND the dense chain's own MMAs of each stage, so that
+            // the tensor pipe works on them while the epilogue warps turn the chain around; only h6 / h7 are left for stage 9.
+            const uint32_t mh = tmem_base + TM_M12_HI, ml = tmem_base + TM_M12_LO;
+            auto t0_step = [&](int s, bool first) {
+                tc::mma_f16_ts(d_b, ml + 8u * s, xh + 16u * s, i128, first ? 0u : 1u);
+                tc::mma_f16_ts(d_b, mh + 8u * s, xl + 16u * s, i128, 1);
+                tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, first ? 0u : 1u);
+            };
             for (; t < total_tiles; t += stride) {
                 // 1: d1, h0 from the geo slice
                 wait_ready();
@@ -158,18 +169,15 @@ __global__ void __launch_bounds__(NT, 1)
                     wait_ready();
                     issue2(d_c, xh, xl, 16, wdesc(wh_off(l), 16 + 16 * l), 16, l + 1, i32, i16, 16);
                     tc::commit(mbar);
+                    // t0 K-steps whose columns are final: 0 = geo, 1 + j = h_j (published before stage j + 2), 9..12 = d2
+                    // (published before this loop; d_b is free from here on)
+                    if (l == 2) t0_step(0, true), t0_step(1, false);
+                    else if (l < 7) t0_step(l - 1, false), t0_step(l + 6, false);
+                    else t0_step(6, false);
                 }
-                // 9: t0^T = M12g . X^T, A from tensor memory (8 columns per K-step)
+                // 9: the rest of t0^T: h6, h7
                 wait_ready();
-                {
-                    const uint32_t mh = tmem_base + TM_M12_HI, ml = tmem_base + TM_M12_LO;
-#pragma unroll
-                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, ml + 8u * s, xh + 16u * s, i128, s > 0);
-#pragma unroll
-                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xl + 16u * s, i128, 1);
-#pragma unroll
-                    for (int s = 0; s < 13; s++) tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, 1);
-                }
+                t0_step(7, false), t0_step(8, false);
                 tc::commit(mbar);
                 // 10: t1 = t0 . W3^T, A = t0 M-major (8-edge groups 128 B apart, 8-channel groups 2048 B apart)
                 wait_ready();
@@ -317,10 +325,10 @@ __global__ void __launch_bounds__(NT, 1)
                 uint8_t* th = smem + T0_OFF + (uint32_t)(e >> 3) * 2048 + (uint32_t)(e & 7) * 16;
 #pragma unroll 1
                 for (int c = 2 * half; c < 2 * half + 2; c++) {
-                    float a[32];
-                    tc::ld32(d_a + 32 * c, a);
+                    float a[32], b[32];                                  // hi . hi part, cross terms (t0_step)
+                    tc::ld32(d_a + 32 * c, a), tc::ld32(d_b + 32 * c, b);
 #pragma unroll
-                    for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] * tc::WINV, S_DEF);
+                    for (int u = 0; u < 32; u++) a[u] = lrelu((a[u] + b[u]) * tc::WINV, S_DEF);
 #pragma unroll
                     for (int g = 0; g < 4; g++) {
                         uint32_t hi[4], lo[4];
