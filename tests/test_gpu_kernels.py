@@ -603,7 +603,9 @@ def test_fps_lattice_ties(ops, dev):
 
 @pytest.mark.parametrize("B,n,npoint,kind", [(3, 2048, 32, "uniform"), (2, 5000, 600, "surface"), (2, 40960, 1500, "surface"),
                                              (1, 12345, 700, "uniform"), (4, 100, 100, "uniform"), (2, 1000, 400, "lattice"),
-                                             (1, 99840, 400, "surface"), (2, 3000, 3000, "dup")])
+                                             (1, 99840, 400, "surface"), (2, 3000, 3000, "dup"),
+                                             (1, 41000, 300, "uniform"), (1, 40929, 300, "uniform")])   # either side of the
+                                             # register-resident / shared-memory metadata switch (64 buckets per warp)
 def test_fps_bucketed_bit_exact(ops, dev, B, n, npoint, kind):
     """The spatially pruned FPS (pf_fps_bucketed) returns exactly the indices of the brute-force definition
     (oracle C restatement of modules/utils/fps.py:40-73), including exact ties (lattice, duplicated points) and
