@@ -74,13 +74,18 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
-        self.gpu, self.proc, self.lines = gpu_index, None, []
+    def __init__(self, gpu_index, enabled=True):
+        # One sampler per JOB (rank 0, all GPUs of the node in one nvidia-smi process): eight per-rank nvidia-smi loops at
+        # 10 Hz measurably stalled kernel launches in every process (gaps of 3.4 ms per step at N = 8 against 1.7 ms at
+        # N = 1, same kernels), i.e. the measurement disturbed the run.
+        self.gpu, self.proc, self.lines, self.enabled = gpu_index, None, [], enabled
 
     def start(self):
+        if not self.enabled:
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -92,6 +97,8 @@ class ClockSampler:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if not self.enabled:
+            return None
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -270,10 +277,14 @@ def run_ours(args):
     # ---- timed region: exactly K steps, device-timed, per-launch events on ---------------------------------
     log = ops.LaunchLog(events=not args.no_breakdown)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(",".join(str(i) for i in range(world)), enabled=(rank == 0))   # this job's GPUs (local ranks)
     sampler.start()
     barrier()
+    # per-launch CUDA events: the network's come from inside the one C call (pf_profile_*), the caller-side kernels'
+    # (FPS, patch kNN, Chamfer) from the Python wrappers -- the kernel-by-kernel Python path cost 0.6 ms per step of host
+    # time at N = 1 and 3 ms at N = 8 (eight ranks on 16 host cores), which the timed region would have charged to the GPU
     prev = ops.set_launch_log(log)
+    ops.c_profile(not args.no_breakdown)
     for e0, e1 in ev:
         flush.zero_()
         e0.record()
@@ -281,6 +292,8 @@ def run_ours(args):
         e1.record()
     ops.set_launch_log(prev)
     barrier()
+    c_times = ops.c_profile_read() if not args.no_breakdown else {}
+    ops.c_profile(False)
     clocks = sampler.stop()
     t_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
     tt = torch.tensor([t_ms], dtype=torch.float64, device=dev)
@@ -294,7 +307,11 @@ def run_ours(args):
     breakdown, roofline = None, None
     if not args.no_breakdown:
         peaks = load_peaks()
-        per = {k: (sum(v) / args.steps, len(v) // args.steps) for k, v in log.times_ms().items()}
+        times = log.times_ms()
+        for k, v in c_times.items():
+            if k != "logp":                                   # two tiny reduction kernels, counted with the plumbing
+                times.setdefault(k, []).extend(v)
+        per = {k: (sum(v) / args.steps, len(v) // args.steps) for k, v in times.items()}
         tot = sum(v[0] for v in per.values())
         step_ms = t_ms / args.steps
         breakdown = {k: {"ms_per_step": round(v[0], 4), "launches_per_step": v[1], "share": round(v[0] / step_ms, 4)}

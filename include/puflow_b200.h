@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 4
+#define PF_ABI_VERSION 5
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -213,6 +213,16 @@ PF_API int pf_model_entry(int i, char* name32, int64_t* offset, int64_t* bytes);
 PF_API int64_t pf_upsample_workspace_bytes(int Bp, int N, int R);
 PF_API int pf_upsample_patches(const void* model, const float* xyz, int Bp, int N, int R, void* workspace,
                         int64_t workspace_bytes, float* x, float* logp, void* stream);
+
+/* Optional per-launch timing of pf_upsample_patches (what bench.py's breakdown and roofline read): while enabled, the call
+ * records CUDA events on its stream around each of its pf_profile_slots() launches (fixed order, pf_profile_slot_name(i):
+ * knn | 6 x (projection, EdgeConv, conditioning chain) | flow_fwd | logp | interp | flow_inv).  pf_profile_read waits for
+ * the recorded calls, writes ms[call][slot] for up to max_calls calls, returns how many it wrote (-1 on error) and clears
+ * the record.  One profiling host thread; off by default; do not enable during CUDA-graph capture. */
+PF_API int pf_profile_enable(int on);
+PF_API int pf_profile_slots(void);
+PF_API const char* pf_profile_slot_name(int i);
+PF_API int pf_profile_read(float* ms, int max_calls);
 
 /* ---- on-disk format (host code, no CUDA) ------------------------------------------
  * The reference reads clouds with np.loadtxt(path, dtype=np.float32) (/root/reference/modules/discrete/upsample.py:42)

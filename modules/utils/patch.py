@@ -167,9 +167,14 @@ class PatchHelper(object):
         idx_dist1 = torch.argsort(dist1, dim=-1, descending=True, stable=True)
         idx_outliers = idx_dist1[:, :num_outliers]
         idxb = torch.arange(B, device=device).view(-1, 1)
-        inv = torch.ones((B, N), dtype=torch.int32, device=device)
-        inv[idxb, idx_outliers] = 0
-        inv = torch.nonzero(inv, as_tuple=False)[:, 1]
-        idx_inverse = inv.view(B, N - num_outliers)
-        return sr[idxb, idx_inverse]
+        keep = torch.ones((B, N), dtype=torch.bool, device=device)
+        keep[idxb, idx_outliers] = False
+        # The reference compacts with torch.nonzero (patch.py:211), which waits for the device; every row keeps exactly
+        # N - num_outliers points, so the same index list comes from a prefix sum and a scatter with no host round trip
+        # (dropped points go to a spare last column).
+        n_keep = N - num_outliers
+        dest = torch.where(keep, torch.cumsum(keep, dim=1) - 1, n_keep)
+        idx_inverse = torch.empty((B, n_keep + 1), dtype=torch.int64, device=device)
+        idx_inverse.scatter_(1, dest, torch.arange(N, device=device).expand(B, N))
+        return sr[idxb, idx_inverse[:, :n_keep]]
 # -----------------------------------------------------------------------------------------

@@ -38,10 +38,36 @@ def set_launch_log(log):
     return prev
 
 
+_c_profile = False
+
+
+def c_profile(on: bool):
+    """Switch the library's own per-launch event timing of pf_upsample_patches on / off (pf_profile_enable): with it on,
+    per-launch times of the network come from inside the one C call, and nothing has to go kernel by kernel in Python."""
+    global _c_profile
+    _c_profile = bool(on)
+    N.check(lib.pf_profile_enable(1 if on else 0), "pf_profile_enable")
+
+
+def c_profile_read(max_calls: int = 512):
+    """{tag: [ms, ...]} of the pf_upsample_patches calls recorded since c_profile(True) / the last read (waits for them)."""
+    import ctypes
+    slots = lib.pf_profile_slots()
+    buf = (ctypes.c_float * (slots * max_calls))()
+    n = lib.pf_profile_read(buf, max_calls)
+    if n < 0:
+        raise N.PuflowError(f"pf_profile_read failed: {lib.pf_last_error().decode(errors='replace')}")
+    out = {}
+    for c in range(n):
+        for i in range(slots):
+            out.setdefault(lib.pf_profile_slot_name(i).decode(), []).append(float(buf[c * slots + i]))
+    return out
+
+
 def per_launch_events_wanted() -> bool:
-    """True while a LaunchLog with per-launch CUDA events is installed (bench.py's breakdown / roofline pass): callers then
-    go kernel by kernel through the wrappers below instead of through the one-call C entry point."""
-    return _log is not None and _log.events
+    """True while a LaunchLog with per-launch CUDA events is installed and the library's own timing (c_profile) is off:
+    callers then go kernel by kernel through the wrappers below instead of through the one-call C entry point."""
+    return _log is not None and _log.events and not _c_profile
 
 
 def count_launches(n: int):
