@@ -188,12 +188,26 @@ __device__ __forceinline__ void ld8(uint32_t taddr, float (&v)[8]) {
     for (int i = 0; i < 8; i++) v[i] = __uint_as_float(r[i]);
 }
 
-// bounded mbarrier wait: a protocol bug traps instead of hanging the GPU
+// Bounded mbarrier wait: a protocol bug must not hang the GPU.  The bound is wall time (%globaltimer, 20 s), not a poll
+// count: under compute-sanitizer, a debugger or time-slicing a healthy kernel can poll for a long time.  The clock is
+// only read every 2^16 failed polls, so the fast path is the bare try_wait loop.
 __device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
     uint32_t spins = 0;
+    uint64_t t0 = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 26)) __trap();
+        if ((++spins & 0xffffu) == 0) {
+            uint64_t now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 20000000000ull) __trap();
+        }
     }
+}
+
+// arrive on `bar` once all cp.async of this thread issued so far have landed (.noinc: the arrival is one of the barrier's
+// expected count, i.e. the barrier is initialised with the number of threads that execute this per phase)
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
@@ -207,10 +221,21 @@ __device__ __forceinline__ uint32_t cvt_f16x2_sat(float a, float b) {
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
     return r;
 }
+// The residual a - hi is one mixed-precision FMA per value (fma.rn.f32.f16: hi * -1 + a, exact; SASS FHFMA reads the
+// .H0 / .H1 half of the packed register directly), so a pair costs 2 F2FP + 2 FHFMA instead of 2 F2FP + 2 HADD2.F32 + 2 FADD.
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
     hi = cvt_f16x2_sat(a, b);
-    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hi));
-    lo = cvt_f16x2_sat(a - hf.x, b - hf.y);
+    float la, lb;
+    asm("{\n"
+        "  .reg .f16 h0, h1, m1;\n"
+        "  mov.b32 {h0, h1}, %2;\n"
+        "  mov.b16 m1, 0xBC00;\n"
+        "  fma.rn.f32.f16 %0, h0, m1, %3;\n"
+        "  fma.rn.f32.f16 %1, h1, m1, %4;\n"
+        "}\n"
+        : "=f"(la), "=f"(lb)
+        : "r"(hi), "f"(a), "f"(b));
+    lo = cvt_f16x2_sat(la, lb);
 }
 
 }  // namespace tc

@@ -193,6 +193,31 @@ def test_edgeconv_other_k(ops, dev, packed, K):
     out = ops.edgeconv(pq.to(dev), idx.to(dev), f["wd"].to(dev), f["wo"].to(dev), Bp, N, g, Co).cpu()
     ok, err = parity.close_norm(out.view(Bp, N, Co).numpy(), ref.view(Bp, N, Co).numpy(), 1e-5)
     assert ok, err
+    tc = ops.edgeconv_tc(pq.to(dev), idx.to(dev), f["wtc"].to(dev), Bp, N, g, Co).cpu()      # tcgen05 kernel, same K
+    ok, err = parity.close_norm(tc.view(Bp, N, Co).numpy(), ref.view(Bp, N, Co).numpy(), 2e-5)
+    assert ok, err
+
+
+@pytest.mark.parametrize("K,blk,Bp,N", [(8, 3, 5, 250), (32, 3, 3, 130), (8, 0, 3, 256), (32, 1, 2, 256), (8, 1, 40, 64)])
+def test_edgeconv_tensor_core_other_k(ops, dev, packed, K, blk, Bp, N):
+    """pf_edgeconv_tc for K = 8 / 32 (tile = 16 / 4 points), ragged N, all three (G, C_out) shapes; 2e-5 normwise against
+    the float64-accumulated emulation like the K = 16 test below."""
+    from puflow_b200.packing import FEAT_CFG
+    C, g, Co = FEAT_CFG[blk]
+    gen = torch.Generator().manual_seed(K * 10 + blk)
+    x = torch.randn(Bp * N, C, generator=gen)
+    p = synth.make_patches(Bp, N, seed=K + blk, shape="uniform")
+    idx = torch.from_numpy(po.knn(p, p, K)[1]).int()
+    f = packed["feat"][blk]
+    pq = emulate.linear(x, f["wpq"], f["bpq"])
+    nref = min(Bp, 3)
+    ref = emulate.edgeconv(pq[:nref * N], idx[:nref], f["wd"], f["wo"], N, g, Co)
+    out = ops.edgeconv_tc(pq.to(dev), idx.to(dev), f["wtc"].to(dev), Bp, N, g, Co).cpu()
+    ok, err = parity.close_norm(out[:nref * N].view(nref, N, Co).numpy(), ref.view(nref, N, Co).numpy(), 2e-5)
+    assert ok, err
+    ffma = ops.edgeconv(pq.to(dev), idx.to(dev), f["wd"].to(dev), f["wo"].to(dev), Bp, N, g, Co).cpu()
+    ok, err = parity.close_norm(out.view(Bp, N, Co).numpy(), ffma.view(Bp, N, Co).numpy(), 2e-5)
+    assert ok, err
 
 
 @pytest.mark.parametrize("blk,Bp,N", [(2, 3, 256), (3, 2, 256), (5, 1, 250), (4, 37, 64), (3, 600, 256),
@@ -228,9 +253,9 @@ def test_edgeconv_tensor_core(ops, dev, packed, blk, Bp, N):
 def test_edgeconv_tensor_core_rejects_other_shapes(ops, dev, packed):
     f = packed["feat"][3]
     pq = torch.zeros(256, 512, device=dev)
-    idx8 = torch.zeros(1, 256, 8, dtype=torch.int32, device=dev)
-    with pytest.raises(Exception):
-        ops.edgeconv_tc(pq, idx8, f["wtc"].to(dev), 1, 256, 32, 128)
+    idx4 = torch.zeros(1, 256, 4, dtype=torch.int32, device=dev)
+    with pytest.raises(Exception):       # K outside {8, 16, 32}
+        ops.edgeconv_tc(pq, idx4, f["wtc"].to(dev), 1, 256, 32, 128)
     idx16 = torch.zeros(1, 256, 16, dtype=torch.int32, device=dev)
     with pytest.raises(Exception):       # blob of another block shape
         ops.edgeconv_tc(pq, idx16, packed["feat"][0]["wtc"].to(dev), 1, 256, 32, 128)

@@ -19,8 +19,8 @@ lib = _native.lib
 lib.pf_debug_edgeconv_prof.argtypes = [ctypes.c_void_p]
 assert lib.pf_debug_edgeconv_prof(buf) == 0
 v = list(buf)
-names = ["layer0 compute", "layer0 cp.wait+bar", "l1-3 pre (stage_q, read_q, add_p)", "l1-3 wait MMA", "l1-3 ld+lrelu+store",
-         "l1-3 cp.wait+bar", "out pre (Q gathers)", "out wait MMA", "out epilogue", "tile end cp.wait+bar"]
+names = ["l0 wait ring", "l0 read+lrelu+split+store+release", "l1-3 wait ring", "l1-3 read P+Q", "l1-3 wait MMA",
+         "l1-3 ld+lrelu+split+store+release", "out wait ring", "out wait MMA", "out ld+fma+max+store", "-"]
 tiles = -(-Bp * N * 16 // 128) // (148 * 2) + 1
 tot = sum(v[:10])
 print(f"epilogue thread 0 of CTA 0 (warpgroup 0): {tot} cycles, ~{tiles} tiles -> {tot / tiles:.0f} cycles per tile")
