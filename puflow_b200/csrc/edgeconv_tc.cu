@@ -20,8 +20,14 @@
 // operands ready (epilogue -> MMA), MMA done (tcgen05.commit).  The warpgroups run independent tiles, so one tile's MMAs
 // and TMEM round trips hide behind the other's CUDA-core work.  Per tile (9 ring stages for (32, 128)):
 //   layer 0      h0 = lrelu(P0_i + Q0_j)                                  (gather only)
-//   layers 1..3  D[128 edges x 32]  = H[128 x 32l] . W_l^T   (M=128, N=32, K=32l)   -> TMEM -> +P+Q, lrelu
-//                -> fp16 hi/lo -> next K-slice of H in shared memory (UMMA K-major layout, tc.cuh)
+//   layers 1..3  every new 32-channel slice h_m (fp16 hi/lo) goes to tensor memory as the A operand of ONE wide MMA
+//                group that adds its contribution to ALL later layers at once:
+//                    D[128 edges x 32 (3 - m)] += h_m . [W_{m+1,m}; ..; W_{3,m}]^T      (M=128, N=96/64/32, K=32)
+//                so layer l's accumulator is complete right after h_{l-1}'s group (K = 32 on the critical path, not
+//                32 l) and no dense-layer MMA reads its A operand from shared memory: ncu showed the kernel bound by
+//                the L1TEX data pipe -- 2,200 tensor-core + 2,800 LSU shared-memory wavefronts per tile against 7,000
+//                cycles -- and the re-read hi/lo activations were half of the tensor-core share.
+//                -> TMEM -> +P+Q, lrelu -> fp16 hi/lo -> TMEM slice (dense) and K-slice of H in shared memory (conv_out)
 //   conv_out     D^T[128 ch x 128 edges] = Wo[128 x 128] . H^T  (M=128, N=128, K=128): transposed so that a
 //                thread owns one output channel and the max over the K neighbours is a register max; the neighbour
 //                term is read from the ring (rows = edges, lanes = channels: conflict-free) and the output store is
@@ -76,14 +82,17 @@ struct Cfg {
     static constexpr int NBAR = 1 + 6 * NWG;                             // weights | per wg: mma, ready, full[2], empty[2]
     static constexpr uint32_t SMEM_BYTES = BAR_OFF + 8 * NBAR + 16;
     static constexpr uint32_t A_SBO = KT * 16;
-    // ---- tensor memory map (columns): per warpgroup 128 (conv_out accumulator; the dense accumulator aliases its
-    // first GP columns -- the two are never live together), then Wo hi / lo as the A operand of conv_out ----
-    static constexpr uint32_t TM_WG = 128, TM_WO_HI = NWG * 128, TM_WO_LO = TM_WO_HI + KT / 2, TM_COLS = 512;
+    // ---- tensor memory map (columns): per warpgroup 128 (conv_out accumulator; the dense accumulators of layers 1..3
+    // alias its first 3 GP columns -- never live together) + GP (the current activation slice, fp16 pairs: hi | lo, the
+    // A operand of the dense MMAs), then Wo hi / lo as the A operand of conv_out ----
+    static constexpr uint32_t TM_SLICE = 128, TM_WG = 128 + GP, TM_WO_HI = NWG * TM_WG, TM_WO_LO = TM_WO_HI + KT / 2,
+                              TM_COLS = 512;
     static_assert(TM_WO_LO + KT / 2 <= 512, "tensor memory budget");
     static_assert(SMEM_BYTES <= 232448, "shared memory budget");
     static_assert(KN == 8 || KN == 16 || KN == 32, "K in {8, 16, 32}");
-    __host__ __device__ static constexpr uint32_t wd_part(int l) { return 2u * GP * GP * l; }
-    __host__ __device__ static constexpr uint32_t wd_off(int l) { return 4u * GP * GP * (l * (l - 1) / 2); }
+    // dense weights by K-slice m = 0..2: rows = the GP (3 - m) output channels of layers m+1..3, K = GP; [hi | lo]
+    __host__ __device__ static constexpr uint32_t wd_part(int m) { return 2u * GP * GP * (3 - m); }
+    __host__ __device__ static constexpr uint32_t wd_off(int m) { return 4u * GP * GP * (3 * m - m * (m - 1) / 2); }
 };
 
 template <int G, int CO, int NWG, int KN>
@@ -168,21 +177,22 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
     if (role == 1) {
         // ================= MMA-issuing warp of warpgroup wg: one elected thread (elect_one, not lane == 0: tc.cuh) waits
         // for "operands ready", issues, commits =================
-        const uint32_t idesc_d = tc::idesc_f16(128, GP), idesc_o = tc::idesc_f16(128, 128);
+        const uint32_t idesc_o = tc::idesc_f16(128, 128);
         const uint64_t da_hi = tc::smem_desc(a_hi, C::A_SBO), da_lo = tc::smem_desc(a_lo, C::A_SBO);
-        // D[128 edges x GP] = H[:, 0:GP l] . W_l^T   (3 split products, the two small cross terms first: the accumulator
-        // adder truncates, so the additions at full magnitude -- the hi . hi pass -- come last and are as few as possible;
-        // K-step s is 256 B = 16 descriptor units further)
-        auto issue_dense = [&](int l) {
-            const uint32_t wl = sbase + C::wd_off(l);
-            const uint64_t db_hi = tc::smem_desc(wl, 16u * GP * l), db_lo = tc::smem_desc(wl + C::wd_part(l), 16u * GP * l);
-            const int ks = GP * l / 16;
+        // D[128 edges x GP (3 - m)] (+)= h_m . [W_{m+1,m}; ..; W_{3,m}]^T, h_m from tensor memory (8 columns per K-step).
+        // 3 split products, the two small cross terms first: the accumulator adder truncates, so the hi . hi pass -- the
+        // additions at full magnitude -- comes last.
+        auto issue_group = [&](int m) {
+            const uint32_t wl = sbase + C::wd_off(m);
+            const uint64_t db_hi = tc::smem_desc(wl, 16u * GP), db_lo = tc::smem_desc(wl + C::wd_part(m), 16u * GP);
+            const uint32_t idesc = tc::idesc_f16(128, GP * (3 - m));
+            const uint32_t d = d_dense + GP * m, h_hi = d_out + C::TM_SLICE, h_lo = h_hi + GP / 2;
 #pragma unroll
-            for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_lo + 16u * s, db_hi + 16u * s, idesc_d, s > 0);
+            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_lo + 8u * s, db_hi + 16u * s, idesc, m > 0 || s > 0);
 #pragma unroll
-            for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_lo + 16u * s, idesc_d, 1);
+            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_lo + 16u * s, idesc, 1);
 #pragma unroll
-            for (int s = 0; s < ks; s++) tc::mma_f16(d_dense, da_hi + 16u * s, db_hi + 16u * s, idesc_d, 1);
+            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_hi + 16u * s, idesc, 1);
         };
         // D^T[128 rows x 128 edges] = Wo . H^T, Wo from TMEM (8 columns per K-step)
         auto issue_out = [&]() {
@@ -200,13 +210,13 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
             PROF_DECL
             for (; t < total_tiles; t += stride) {
 #pragma unroll
-                for (int l = 1; l < 4; l++) {
+                for (int m = 0; m < 3; m++) {
                     PROF_TICK(1)
                     tc::mbar_wait_bounded(ready, rphase);
                     rphase ^= 1;
                     tc::fence_after_sync();
                     PROF_TICK(0)
-                    issue_dense(l);
+                    issue_group(m);
                     tc::commit(mbar);
                 }
                 PROF_TICK(1)
@@ -319,16 +329,28 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
         const uint32_t op_off = C::QPART + (uint32_t)(32 * grp / KN) * (4 * CO) + ch * 4;
         uint32_t phase = 0, st = 0;
 
-        // h[G] (fp32) -> fp16 hi/lo into K-slice l (GP wide) of this thread's row of the activation operand
+        // h[G] (fp32) -> fp16 hi/lo: K-slice l (GP wide) of this thread's row of H in shared memory (conv_out's B operand)
+        // and, for l < 3, this thread's lane of the tensor-memory slice (the A operand of the dense group l)
         auto store_slice = [&](int l, const float (&h)[G]) {
+            uint32_t hi[GP / 2], lo[GP / 2];
+#pragma unroll
+            for (int u = 0; u < G / 2; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
+#pragma unroll
+            for (int u = G / 2; u < GP / 2; u++) hi[u] = lo[u] = 0;
 #pragma unroll
             for (int c = 0; c < G / 8; c++) {
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) tc::split2(h[8 * c + 2 * u], h[8 * c + 2 * u + 1], hi[u], lo[u]);
                 const uint32_t off = a_row + (uint32_t)(l * (GP / 8) + c) * 128;
-                *reinterpret_cast<uint4*>(a_hi_p + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                *reinterpret_cast<uint4*>(a_hi_p + off) = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
+                *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
+            }
+            if (l < 3) {
+                const uint32_t ts = d_out + lane_sel + C::TM_SLICE;
+                if constexpr (GP == 32) {
+                    tc::st16_nowait(ts, hi), tc::st16_nowait(ts + 16, lo);
+                } else {
+                    tc::st8_nowait(ts, hi), tc::st8_nowait(ts + 8, lo);
+                }
+                tc::tmem_st_wait();
             }
         };
         // q[G] = Q_j + P_i of the dense stage in ring slot `slot`
@@ -387,13 +409,14 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 tc::fence_after_sync();
                 PROF_TICK(4)
                 float acc[G];
+                const uint32_t dl = d_dense + lane_sel + (uint32_t)(GP * (l - 1));   // layer l: columns [GP (l-1), GP l)
                 if constexpr (G == 32) {
-                    tc::ld32(d_dense + lane_sel, acc);
+                    tc::ld32(dl, acc);
                 } else if constexpr (G == 16) {
-                    tc::ld16(d_dense + lane_sel, acc);
+                    tc::ld16(dl, acc);
                 } else {
                     float a16[16];
-                    tc::ld16(d_dense + lane_sel, a16);
+                    tc::ld16(dl, a16);
 #pragma unroll
                     for (int c = 0; c < G; c++) acc[c] = a16[c];
                 }

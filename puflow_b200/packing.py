@@ -110,10 +110,11 @@ def edgeconv_tc_blob_bytes(g: int) -> int:
 
 def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
     """(wd, wo) of pack_edgeconv -> uint8[edgeconv_tc_blob_bytes(g)] for pf_edgeconv_tc, (g, C_out) in
-    {(8, 32), (16, 64), (32, 128)}:  [W1 hi | W1 lo | W2 hi | W2 lo | W3 hi | W3 lo | Wo hi | Wo lo].
+    {(8, 32), (16, 64), (32, 128)}:  [S0 hi | S0 lo | S1 hi | S1 lo | S2 hi | S2 lo | Wo hi | Wo lo], S_m = the columns of
+    K-slice m (layer m's hidden channels) of the weights of layers m+1..3 stacked along the rows ([gp (3 - m) out][gp in]):
+    the kernel multiplies every new activation slice against all later layers at once.
     gp = max(g, 16) is the width of one layer's K slice in the activation operand; for g = 8 hidden channel k of layer j
-    sits at K index j*gp + k and the rest of the slice is zero.  W_l: [gp out][gp*l in] in the shared-memory operand
-    layout; Wo: plain row-major fp16 [128][layers*gp] whose row r is conv_out channel r % C_out (it is copied to tensor
+    sits at K index j*gp + k and the rest of the slice is zero.  S_m in the shared-memory operand layout; Wo: plain row-major fp16 [128][layers*gp] whose row r is conv_out channel r % C_out (it is copied to tensor
     memory, one row per lane; the kernel reads channel r % C_out for edge group r // C_out from lane r)."""
     assert (g, C_out) in ((8, 32), (16, 64), (32, 128)) and layers == 4
     gp = max(g, 16)
@@ -124,13 +125,16 @@ def pack_edgeconv_tc(wd, wo, g: int = 32, C_out: int = 128, layers: int = 4):
             out[:, j * gp:j * gp + g] = W[:, j * g:(j + 1) * g]
         return out
 
-    parts, off = [], 0
+    Ws, off = {}, 0
     for l in range(1, layers):
         Wl = wd[off:off + g * l * g].reshape(g * l, g).t().double()   # [g out, g*l in]
         off += g * l * g
         Wp = torch.zeros(gp, l * gp, dtype=torch.float64)
         Wp[:g] = pad_k(Wl, l)
-        parts.extend(umma_kmajor_fp16(Wp))
+        Ws[l] = Wp
+    parts = []
+    for m in range(layers - 1):      # K-slice m (hidden channels of layer m) against every later layer, stacked along the rows
+        parts.extend(umma_kmajor_fp16(torch.cat([Ws[l][:, m * gp:(m + 1) * gp] for l in range(m + 1, layers)], 0)))
     wo_rows = pad_k(wo.t().double(), layers)                          # [C_out, layers*gp]
     wo32 = wo_rows.repeat(128 // C_out, 1).contiguous().to(torch.float32)   # row r = channel r % C_out
     wo_hi, wo_lo = split_weight(wo32)

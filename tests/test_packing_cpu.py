@@ -106,15 +106,19 @@ def test_tensor_core_blobs_decode_to_the_weights(state_dict):
         f = w["feat"][i]
         gp = max(g, 16)
         assert f["wtc"].numel() == packing.edgeconv_tc_blob_bytes(g)
-        off, woff = 0, 0
+        Wl, woff = {}, 0
         for l in range(1, 4):
-            part = 2 * gp * gp * l
-            dec = _umma_decode(f["wtc"][off:off + part], gp, gp * l) + _umma_decode(f["wtc"][off + part:off + 2 * part], gp, gp * l)
-            Wl = f["wd"][woff:woff + g * l * g].view(g * l, g).t()
+            Wl[l] = f["wd"][woff:woff + g * l * g].view(g * l, g).t()   # [g out, g*l in]
             woff += g * l * g
-            for j in range(l):
-                assert (dec[:g, j * gp:j * gp + g] - Wl[:, j * g:(j + 1) * g]).abs().max() <= 2.0 ** -21 * Wl.abs().max()
-                assert (dec[:g, j * gp + g:(j + 1) * gp] == 0).all() and (dec[g:] == 0).all()
+        off = 0
+        for m in range(3):                                             # K-slice m against layers m+1..3, rows stacked
+            rows = gp * (3 - m)
+            part = 2 * rows * gp
+            dec = _umma_decode(f["wtc"][off:off + part], rows, gp) + _umma_decode(f["wtc"][off + part:off + 2 * part], rows, gp)
+            for n, l in enumerate(range(m + 1, 4)):
+                blk = dec[n * gp:(n + 1) * gp]
+                assert (blk[:g, :g] - Wl[l][:, m * g:(m + 1) * g]).abs().max() <= 2.0 ** -21 * Wl[l].abs().max()
+                assert (blk[:g, g:] == 0).all() and (blk[g:] == 0).all()
             off += 2 * part
         KT = 4 * gp
         hi = f["wtc"][off:off + 128 * KT * 2].view(torch.float16).view(128, KT).float() / packing.TC_WSCALE
