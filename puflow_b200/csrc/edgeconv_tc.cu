@@ -79,7 +79,7 @@ struct Cfg {
     static constexpr uint32_t QPART = 16384, PPART = 16384 / KN, SLOT = QPART + PPART;
     static constexpr uint32_t QS_OFF = A_OFF + 2 * NWG * A_PART;
     static constexpr uint32_t BAR_OFF = QS_OFF + 2 * NWG * SLOT;
-    static constexpr int NBAR = 1 + 6 * NWG;                             // weights | per wg: mma, ready, full[2], empty[2]
+    static constexpr int NBAR = 1 + 10 * NWG;                            // weights | per wg: mma, ready, full[2], empty[2], conv[4]
     static constexpr uint32_t SMEM_BYTES = BAR_OFF + 8 * NBAR + 16;
     static constexpr uint32_t A_SBO = KT * 16;
     // ---- tensor memory map (columns): per warpgroup 128 (conv_out accumulator; the dense accumulators of layers 1..3
@@ -112,17 +112,21 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
     const int wg = role == 0 ? warp >> 2 : (role == 1 ? warp - 4 * NWG : warp - 5 * NWG);
     const int wq = warp & 3;                                              // TMEM lane quadrant (epilogue warps)
     const int e = tid & 127;                                              // tile row (edge) / conv_out row of this thread
-    uint64_t* mbar = wbar + 1 + 6 * wg;                                   // MMA done
+    uint64_t* mbar = wbar + 1 + 10 * wg;                                  // dense MMA group done
     uint64_t* ready = mbar + 1;                                           // operands ready (one arrival per epilogue warp)
     uint64_t* qfull = mbar + 2;                                           // [2] ring slot filled (32 cp.async arrivals)
     uint64_t* qempty = mbar + 4;                                          // [2] ring slot consumed (one arrival per warp)
+    uint64_t* cbar = mbar + 6;                                            // [4] conv_out step c done (one barrier per step: all
+                                                                          // steps are committed back to back, a waiter must
+                                                                          // never fall two phases behind one barrier)
 
     if (tid == 0) {
         mbar_init(wbar, 1);
         for (int i = 0; i < NWG; i++) {
-            uint64_t* b = wbar + 1 + 6 * i;
+            uint64_t* b = wbar + 1 + 10 * i;
             mbar_init(b, 1), mbar_init(b + 1, 4);
             mbar_init(b + 2, 32), mbar_init(b + 3, 32), mbar_init(b + 4, 4), mbar_init(b + 5, 4);
+            for (int c = 0; c < 4; c++) mbar_init(b + 6 + c, 1);
         }
         mbar_fence_init();
     }
@@ -177,7 +181,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
     if (role == 1) {
         // ================= MMA-issuing warp of warpgroup wg: one elected thread (elect_one, not lane == 0: tc.cuh) waits
         // for "operands ready", issues, commits =================
-        const uint32_t idesc_o = tc::idesc_f16(128, 128);
+        const uint32_t idesc_o = tc::idesc_f16(128, 32);
         const uint64_t da_hi = tc::smem_desc(a_hi, C::A_SBO), da_lo = tc::smem_desc(a_lo, C::A_SBO);
         // D[128 edges x GP (3 - m)] (+)= h_m . [W_{m+1,m}; ..; W_{3,m}]^T, h_m from tensor memory (8 columns per K-step).
         // 3 split products, the two small cross terms first: the accumulator adder truncates, so the hi . hi pass -- the
@@ -194,15 +198,24 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
 #pragma unroll
             for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_hi + 16u * s, idesc, 1);
         };
-        // D^T[128 rows x 128 edges] = Wo . H^T, Wo from TMEM (8 columns per K-step)
-        auto issue_out = [&]() {
+        // conv_out step c: D^T[128 rows x 32 edges] = Wo . H^T for the 128 / CO column blocks (32 edges each) that the
+        // epilogue threads read in step c (block g NCH + c for edge group g); Wo from TMEM (8 columns per K-step), H^T rows
+        // 32 cb .. 32 cb + 32 of the shared-memory operand (4 row groups = 4 SBO further per block).  One commit per step:
+        // the epilogue of step c runs while the tensor pipe computes step c + 1 (one N = 128 MMA chain kept the epilogue
+        // waiting for all 24 instructions, 1,500 cycles per tile).
+        auto issue_out = [&](int c) {
             const uint32_t wo_hi = tmem_base + C::TM_WO_HI, wo_lo = tmem_base + C::TM_WO_LO;
 #pragma unroll
-            for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_lo + 8u * s, da_hi + 16u * s, idesc_o, s > 0);
+            for (int g = 0; g < 128 / CO; g++) {
+                const uint32_t cb = (uint32_t)(g * NCH + c), d = d_out + 32u * cb;
+                const uint64_t bh = da_hi + (uint64_t)(4u * cb * (C::A_SBO >> 4)), bl = da_lo + (uint64_t)(4u * cb * (C::A_SBO >> 4));
 #pragma unroll
-            for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_lo + 16u * s, idesc_o, 1);
+                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_lo + 8u * s, bh + 16u * s, idesc_o, s > 0);
 #pragma unroll
-            for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d_out, wo_hi + 8u * s, da_hi + 16u * s, idesc_o, 1);
+                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bl + 16u * s, idesc_o, 1);
+#pragma unroll
+                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bh + 16u * s, idesc_o, 1);
+            }
         };
         tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
         if (tc::elect_one()) {
@@ -224,8 +237,11 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 rphase ^= 1;
                 tc::fence_after_sync();
                 PROF_TICK(0)
-                issue_out();
-                tc::commit(mbar);
+#pragma unroll
+                for (int c = 0; c < NCH; c++) {
+                    issue_out(c);
+                    tc::commit(cbar + c);
+                }
             }
             PROF_TICK(1)
             if (wg == 0) { PROF_DUMP(16, 2) }
@@ -327,22 +343,26 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
         for (int v = 0; v < 4; v++)
             o_off[v] = (uint32_t)(32 * grp) * (4 * CO) + ((((uint32_t)ch >> 2) ^ ((uint32_t)v << LCPR)) << 4) + (ch & 3) * 4;
         const uint32_t op_off = C::QPART + (uint32_t)(32 * grp / KN) * (4 * CO) + ch * 4;
-        uint32_t phase = 0, st = 0;
+        uint32_t phase = 0, cphase = 0, st = 0;
+        // pre-split output through a register transpose when a thread owns 8 points of a tile (the (32, 128), K = 16 blocks)
+        constexpr bool SPLIT_T = CO == 128 && KN == 16;
+        uint32_t sp[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
-        // h[G] (fp32) -> fp16 hi/lo: K-slice l (GP wide) of this thread's row of H in shared memory (conv_out's B operand)
-        // and, for l < 3, this thread's lane of the tensor-memory slice (the A operand of the dense group l)
+        // h[G] (fp32) of layer l -> fp16 hi/lo.  l < 3: this thread's lane of the tensor-memory slice (the A operand of dense
+        // group l) is written and published FIRST; the copy into K-slice l of H in shared memory (conv_out's B operand)
+        // follows off the critical path.  l == 3: the shared-memory copy completes H: generic -> async proxy fence (it
+        // covers the earlier slices' stores of this thread as well), then publish.
         auto store_slice = [&](int l, const float (&h)[G]) {
             uint32_t hi[GP / 2], lo[GP / 2];
 #pragma unroll
             for (int u = 0; u < G / 2; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
 #pragma unroll
             for (int u = G / 2; u < GP / 2; u++) hi[u] = lo[u] = 0;
-#pragma unroll
-            for (int c = 0; c < G / 8; c++) {
-                const uint32_t off = a_row + (uint32_t)(l * (GP / 8) + c) * 128;
-                *reinterpret_cast<uint4*>(a_hi_p + off) = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
-                *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
-            }
+            auto publish = [&]() {
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(ready);
+            };
             if (l < 3) {
                 const uint32_t ts = d_out + lane_sel + C::TM_SLICE;
                 if constexpr (GP == 32) {
@@ -351,6 +371,17 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                     tc::st8_nowait(ts, hi), tc::st8_nowait(ts + 8, lo);
                 }
                 tc::tmem_st_wait();
+                publish();
+            }
+#pragma unroll
+            for (int c = 0; c < G / 8; c++) {
+                const uint32_t off = a_row + (uint32_t)(l * (GP / 8) + c) * 128;
+                *reinterpret_cast<uint4*>(a_hi_p + off) = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
+                *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
+            }
+            if (l == 3) {
+                tc::fence_async_smem();
+                publish();
             }
         };
         // q[G] = Q_j + P_i of the dense stage in ring slot `slot`
@@ -362,17 +393,12 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 q[4 * c] = v.x + p.x, q[4 * c + 1] = v.y + p.y, q[4 * c + 2] = v.z + p.z, q[4 * c + 3] = v.w + p.w;
             }
         };
-        // this warp is done with ring slot b / has published its rows of the operand
-        auto release = [&](uint32_t b, bool publish) {
-            if (publish) {
-                tc::fence_async_smem();
-                tc::fence_before_sync();
-            }
+        // this warp has read what it needs from ring slot b (the values are in registers): the producer may refill it.
+        // Dense stages release right after the read, a whole stage before their results are published -- with a 2-slot ring
+        // that is what lets the producer run a stage ahead.
+        auto release = [&](uint32_t b) {
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(qempty + b);
-                if (publish) mbar_arrive(ready);
-            }
+            if (lane == 0) mbar_arrive(qempty + b);
         };
         tc::mbar_wait_bounded(wbar, 0);   // (ordering only: nothing below reads the weights)
 
@@ -388,10 +414,10 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 PROF_TICK(0)
                 float q[G];
                 read_pq(ring_p + b * C::SLOT, q);
+                release(b);
 #pragma unroll
                 for (int c = 0; c < G; c++) q[c] = lrelu(q[c], slope);
                 store_slice(0, q);
-                release(b, true);
                 PROF_TICK(1)
             }
             // ---- layers 1..3 ----
@@ -403,6 +429,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 PROF_TICK(2)
                 float q[G];
                 read_pq(ring_p + b * C::SLOT, q);
+                release(b);
                 PROF_TICK(3)
                 tc::mbar_wait_bounded(mbar, phase);
                 phase ^= 1;
@@ -423,7 +450,6 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
 #pragma unroll
                 for (int c = 0; c < G; c++) acc[c] = lrelu(fmaf(acc[c], tc::WINV, q[c]), slope);
                 store_slice(l, acc);
-                release(b, true);
                 PROF_TICK(5)
             }
             // ---- conv_out (transposed) + max over the KN neighbours ----
@@ -433,12 +459,9 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 tc::mbar_wait_bounded(qfull + b, (st >> 1) & 1);
                 st++;
                 PROF_TICK(6)
-                if (c == 0) {
-                    tc::mbar_wait_bounded(mbar, phase);
-                    phase ^= 1;
-                    tc::fence_after_sync();
-                    PROF_TICK(7)
-                }
+                tc::mbar_wait_bounded(cbar + c, cphase);
+                tc::fence_after_sync();
+                PROF_TICK(7)
                 const uint8_t* slot = ring_p + b * C::SLOT;
                 float acc[32];
                 tc::ld32(d_out + lane_sel + 32 * (grp * NCH + c), acc);
@@ -448,20 +471,21 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 float pv[32 / KN];
 #pragma unroll
                 for (int h = 0; h < 32 / KN; h++) pv[h] = *reinterpret_cast<const float*>(slot + op_off + h * (4 * CO));
-                release(b, false);
+                release(b);
+                float val[32 / KN];
 #pragma unroll
                 for (int h = 0; h < 32 / KN; h++) {
                     float m = acc[KN * h];
 #pragma unroll
                     for (int u = 1; u < KN; u++) m = fmaxf(m, acc[KN * h + u]);
+                    val[h] = m + pv[h];
                     const int pp = p0 + (CO * grp + 32 * c) / KN + h;
                     if (pp < N) {
-                        const float val = m + pv[h];
                         const size_t grow = (size_t)patch * N + pp;
-                        if (out) out[grow * CO + ch] = val;
-                        if (out_split) {   // fp16 hi/lo in the tile-blocked operand layout of linear_split.cu (K = CO)
+                        if (out) out[grow * CO + ch] = val[h];
+                        if (!SPLIT_T && out_split) {   // fp16 hi/lo in the tile-blocked operand layout of linear_split.cu (K = CO)
                             uint32_t hi, lo;
-                            tc::split2(val, 0.f, hi, lo);
+                            tc::split2(val[h], 0.f, hi, lo);
                             uint8_t* tile = out_split + (grow >> 7) * (size_t)(CO * 512) + (size_t)(ch >> 3) * 2048 +
                                             (grow & 127) * 16 + (ch & 7) * 2;
                             *reinterpret_cast<uint16_t*>(tile) = (uint16_t)(hi & 0xffffu);
@@ -469,7 +493,41 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                         }
                     }
                 }
+                if constexpr (SPLIT_T) {   // this step's two points -> (hi | lo << 16) of this thread's channel
+                    uint32_t hi, lo;
+                    tc::split2(val[0], val[1], hi, lo);
+                    sp[2 * c] = __byte_perm(hi, lo, 0x5410), sp[2 * c + 1] = __byte_perm(hi, lo, 0x7632);
+                }
                 PROF_TICK(8)
+            }
+            cphase ^= 1;
+            if constexpr (SPLIT_T) {
+                if (out_split) {
+                    // sp[q] = this channel's value for point q of the tile.  8 x 8 transpose inside each group of 8 lanes
+                    // (= 8 consecutive channels): lane r ends up with the 8 channels of point r, i.e. one aligned 16-byte
+                    // piece of the operand tile per half -- 2 STG.128 per thread and tile instead of 16 two-byte stores
+                    // (ncu: 21 of 32 bytes per sector used, +0.2 ms per launch).
+#pragma unroll
+                    for (int m = 1; m < 8; m <<= 1) {
+                        const bool up = (lane & m) != 0;
+#pragma unroll
+                        for (int i = 0; i < 8; i++)
+                            if (!(i & m)) {
+                                const uint32_t recv = __shfl_xor_sync(0xffffffffu, up ? sp[i] : sp[i + m], m);
+                                if (up) sp[i] = recv; else sp[i + m] = recv;
+                            }
+                    }
+                    const int pp = p0 + (lane & 7);
+                    if (pp < N) {
+                        const size_t grow = (size_t)patch * N + pp;
+                        uint8_t* tile = out_split + (grow >> 7) * (size_t)(CO * 512) + (size_t)(ch >> 3) * 2048 + (grow & 127) * 16;
+                        *reinterpret_cast<uint4*>(tile) = make_uint4(__byte_perm(sp[0], sp[1], 0x5410), __byte_perm(sp[2], sp[3], 0x5410),
+                                                                     __byte_perm(sp[4], sp[5], 0x5410), __byte_perm(sp[6], sp[7], 0x5410));
+                        *reinterpret_cast<uint4*>(tile + CO * 256) =
+                            make_uint4(__byte_perm(sp[0], sp[1], 0x7632), __byte_perm(sp[2], sp[3], 0x7632),
+                                       __byte_perm(sp[4], sp[5], 0x7632), __byte_perm(sp[6], sp[7], 0x7632));
+                    }
+                }
             }
             // The next tile's layer 0 overwrites H and (layer 1) the accumulator: both are free -- this thread's conv_out
             // tcgen05.ld have completed, and its next `ready` arrival (after fence::before_thread_sync) orders them
