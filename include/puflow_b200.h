@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 5
+#define PF_ABI_VERSION 6
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -195,6 +195,27 @@ PF_API long long pf_fps_work_floats(int B, int n);
 PF_API int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
 
+/* ---- caller glue as kernels ------------------------------------------------------
+ * pf_normalize_pc     PatchHelper.normalize_pc (/root/reference/modules/utils/patch.py:168-178): pc[B][n][3] ->
+ *                     out[B][n][3] = (pc - centroid) / max radius, centroid[B][3], radius[B] (either may be NULL).
+ * pf_gather_normalize the patch gather of extract_knn_patch (patch.py:112-125) fused with the per-patch normalize_pc of
+ *                     __upsampling_patches (patch.py:85): item (b, p) takes the points pc[b][idx[b][p][0..k)] of cloud b
+ *                     (n points); out[B*items][k][3], centroid[B*items][3], radius[B*items].
+ * pf_gather_points    index_points / gather_operation (patch.py:106,157): out[b][i] = pc[b][idx[b][i]], i < m, optionally
+ *                     * scale[b] + shift[b][0..3) (the de-normalisation of patch.py:76; scale and shift both or neither).
+ * pf_denorm_concat    torch.cat([generated, patch], 1) * radius + centroid (patch.py:90-91): out[items][nx + np][3].
+ * pf_remove_outliers  patch.py:198-214 given dist1 = the squared distance of every point of sr to its nearest input point
+ *                     (pf_chamfer_nn): drops the num_outliers largest (ties: the lowest index goes first, i.e. a stable
+ *                     descending argsort), survivors keep their order; sr[B][n][3], dist1[B][n] -> out[B][n - num_outliers][3]. */
+PF_API int pf_normalize_pc(const float* pc, int B, int n, float* out, float* centroid, float* radius, void* stream);
+PF_API int pf_gather_normalize(const float* pc, const int32_t* idx, int B, int n, int items, int k, float* out, float* centroid,
+                        float* radius, void* stream);
+PF_API int pf_gather_points(const float* pc, const int32_t* idx, int B, int n, int m, const float* scale, const float* shift,
+                     float* out, void* stream);
+PF_API int pf_denorm_concat(const float* x, const float* patches, const float* centroid, const float* radius, int items, int nx,
+                     int np, float* out, void* stream);
+PF_API int pf_remove_outliers(const float* sr, const float* dist1, int B, int n, int num_outliers, float* out, void* stream);
+
 /* ---- whole network in one call --------------------------------------------------------------------------------
  * pf_upsample_patches replaces PointInterpFlow.forward (/root/reference/modules/discrete/interpflow.py:327-337:
  * knn_points -> feat_extract -> log_prob -> interp -> g) for a batch of patches:
@@ -214,15 +235,32 @@ PF_API int64_t pf_upsample_workspace_bytes(int Bp, int N, int R);
 PF_API int pf_upsample_patches(const void* model, const float* xyz, int Bp, int N, int R, void* workspace,
                         int64_t workspace_bytes, float* x, float* logp, void* stream);
 
-/* Optional per-launch timing of pf_upsample_patches (what bench.py's breakdown and roofline read): while enabled, the call
- * records CUDA events on its stream around each of its pf_profile_slots() launches (fixed order, pf_profile_slot_name(i):
- * knn | 6 x (projection, EdgeConv, conditioning chain) | flow_fwd | logp | interp | flow_inv).  pf_profile_read waits for
- * the recorded calls, writes ms[call][slot] for up to max_calls calls, returns how many it wrote (-1 on error) and clears
- * the record.  One profiling host thread; off by default; do not enable during CUDA-graph capture. */
+/* pf_upsample_clouds replaces the body of the reference's per-file loop (/root/reference/modules/discrete/upsample.py:46-54:
+ * PatchHelper.upsample(jitter=False) + remove_outliers) for a batch of clouds:
+ *   clouds[B][N][3] -> out[B][npoint - num_outliers][3]:  normalise -> n_patch seeds by FPS -> patch kNN (patch_points per
+ *   patch) -> per-patch normalise -> pf_upsample_patches -> de-normalise + append the input patch -> merge FPS to npoint
+ *   points (the reference: N*R + num_outliers) -> back to the input frame -> Chamfer pass against the input -> drop the
+ *   num_outliers farthest points.
+ * n_patch is the caller's int(N / patch_points * expand_ratio) (patch.py:101).  Every launch goes to `stream`; nothing is
+ * allocated and nothing synchronises (CUDA-graph capturable).  workspace: pf_upsample_clouds_workspace_bytes(...) bytes,
+ * 256-byte aligned.  num_outliers = 0 skips the Chamfer pass and writes the npoint merged points directly
+ * (= PatchHelper.upsample alone). */
+PF_API int64_t pf_upsample_clouds_workspace_bytes(int B, int N, int R, int npoint, int patch_points, int n_patch);
+PF_API int pf_upsample_clouds(const void* model, const float* clouds, int B, int N, int R, int npoint, int num_outliers,
+                       int patch_points, int n_patch, void* workspace, int64_t workspace_bytes, float* out, void* stream);
+
+/* Optional per-launch timing of the one-call entry points (what bench.py's breakdown and roofline read): while enabled,
+ * pf_upsample_patches / pf_upsample_clouds record a CUDA event on their stream after each of their launches; every interval
+ * carries the launch's name ("knn_topk_k16", "linear_split_k128_n512", "edgeconv_tc_g32_c128_k16", "cond_chain_tc_c128",
+ * "flow_fwd_tc", "logp", "interp_tc", "flow_inv_tc"; "normalize_pc", "fps_n<candidates>", "gather_points", "knn_patch",
+ * "gather_normalize", "denorm_concat", "chamfer_nn", "remove_outliers").  pf_profile_intervals: how many were recorded
+ * since pf_profile_enable(1) / pf_profile_clear; pf_profile_interval(i, name40, ms) waits for interval i and returns its
+ * name and duration.  The record is per HOST THREAD (thread_local): threads driving different streams do not interfere.
+ * Off by default; do not enable during CUDA-graph capture. */
 PF_API int pf_profile_enable(int on);
-PF_API int pf_profile_slots(void);
-PF_API const char* pf_profile_slot_name(int i);
-PF_API int pf_profile_read(float* ms, int max_calls);
+PF_API int pf_profile_intervals(void);
+PF_API int pf_profile_interval(int i, char* name40, float* ms);
+PF_API int pf_profile_clear(void);
 
 /* ---- on-disk format (host code, no CUDA) ------------------------------------------
  * The reference reads clouds with np.loadtxt(path, dtype=np.float32) (/root/reference/modules/discrete/upsample.py:42)

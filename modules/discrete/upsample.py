@@ -19,6 +19,7 @@ from pathlib import Path
 sys.path.append(os.getcwd())
 
 from modules.utils.patch import PatchHelper
+from puflow_b200 import ops
 from puflow_b200.xyzio import load_xyz, save_xyz
 from modules.discrete.interpflow import PointInterpFlow
 
@@ -26,7 +27,7 @@ from modules.discrete.interpflow import PointInterpFlow
 # -----------------------------------------------------------------------------------------
 @torch.no_grad()
 def upsampling(data_paths: List[str], target_path: str, checkpoint_path: str, up_ratio: int, num_outlier: int,
-               num_patch: int, num_upsampling: int = None, seed=None, device=None):
+               num_patch: int, num_upsampling: int = None, seed=None, device=None, batch_clouds: int = 128):
 
     if seed is not None:
         np.random.seed(seed)
@@ -48,34 +49,55 @@ def upsampling(data_paths: List[str], target_path: str, checkpoint_path: str, up
     network.eval()
     patch_helper = PatchHelper(num_patch, patch_expand_ratio=4)
 
-    for path in sorted(data_paths)[rank::world] if world > 1 else data_paths:
-        _, file_name = os.path.split(path)
-
+    paths = sorted(data_paths)[rank::world] if world > 1 else list(data_paths)
+    # Files are read (and permuted: one torch.randperm per file, in list order, like the reference's loop) first, then
+    # clouds of the same size go through the GPU together: a 2,048-point cloud alone is 32 patches and an 8,216-round FPS
+    # on one SM, a batch of them fills the device.  Outputs are the reference's: same file names, '%.6f' rows.
+    clouds = []
+    for path in paths:
         pt_input = load_xyz(path)                       # np.loadtxt(path, dtype=np.float32), upsample.py:42
-        pt_input = pt_input[torch.randperm(pt_input.shape[0]).numpy()]
-        pred = upsample_array(network, patch_helper, pt_input[None], up_ratio, num_outlier, num_upsampling, device)
-        save_xyz(Path(target_path) / file_name, pred[0])  # np.savetxt(..., fmt='%.6f'), upsample.py:57
+        clouds.append(pt_input[torch.randperm(pt_input.shape[0]).numpy()])
+    by_size = {}
+    for i, c in enumerate(clouds):
+        by_size.setdefault(c.shape[0], []).append(i)
+    for n, members in by_size.items():
+        for j in range(0, len(members), batch_clouds):
+            chunk = members[j:j + batch_clouds]
+            pred = upsample_array(network, patch_helper, np.stack([clouds[i] for i in chunk], 0), up_ratio, num_outlier,
+                                  num_upsampling, device)
+            for i, p in zip(chunk, pred):
+                save_xyz(Path(target_path) / os.path.split(paths[i])[1], p)  # np.savetxt(..., fmt='%.6f'), upsample.py:57
 
 
 # -----------------------------------------------------------------------------------------
 @torch.no_grad()
 def upsample_array(network, patch_helper, clouds, up_ratio: int = 4, num_outlier: int = 24,
-                   num_upsampling: int = None, device=None, out: torch.Tensor = None):
+                   num_upsampling: int = None, device=None, out: torch.Tensor = None, graph: bool = True):
     """Host-buffer form of the per-file body of the reference's loop (upsample.py:42-56): clouds[B,N,3] fp32 in HOST
     memory (numpy array or CPU tensor, pinned or not) -> upsampled clouds [B, N*up_ratio (or num_upsampling), 3] in
     host memory (numpy; or written into the pinned CPU tensor `out`).  The host->device copy, the whole
     PatchHelper.upsample + remove_outliers pipeline and the device->host copy run on the current stream; the call
-    returns after the result has landed in host memory."""
+    returns after the result has landed in host memory.  With the drop-in PointInterpFlow the device part is ONE C call
+    (pf_upsample_clouds) replayed from a CUDA graph captured per cloud shape (graph=False launches it directly)."""
     device = torch.device(device) if device is not None else next(network.parameters()).device
     src = torch.from_numpy(clouds) if isinstance(clouds, np.ndarray) else clouds
     if src.dim() != 3 or src.shape[2] != 3 or src.dtype != torch.float32:
         raise ValueError(f"upsample_array: expected fp32 clouds[B,N,3], got {tuple(src.shape)} {src.dtype}")
     pt_input = src.to(device, non_blocking=True).contiguous()
 
-    n_out = (pt_input.shape[1] * up_ratio if num_upsampling is None else num_upsampling) + (num_outlier or 0)
-    pred = patch_helper.upsample(network, pt_input, npoint=n_out, upratio=up_ratio, jitter=False)
-    if num_outlier is not None and num_outlier > 0:
-        pred = PatchHelper.remove_outliers(pred, pt_input, num_outlier)
+    n_pts = pt_input.shape[1] * up_ratio if num_upsampling is None else num_upsampling
+    n_drop = num_outlier or 0
+    eng = network.engine(device) if hasattr(network, "engine") else None
+    k = patch_helper.npoint_patch
+    n_patch = int(pt_input.shape[1] / k * patch_helper.patch_expand_ratio)
+    if eng is not None and eng.flow_tc and pt_input.shape[1] >= k >= 16 and 1 <= n_patch <= pt_input.shape[1] \
+            and not ops.per_launch_events_wanted():
+        # the whole per-file body of the reference's loop in one C call, replayed from a CUDA graph per shape
+        pred = eng.upsample_clouds(pt_input, up_ratio, n_pts + n_drop, n_drop, k, n_patch, graph=graph)
+    else:
+        pred = patch_helper.upsample(network, pt_input, npoint=n_pts + n_drop, upratio=up_ratio, jitter=False)
+        if n_drop > 0:
+            pred = PatchHelper.remove_outliers(pred, pt_input, n_drop)
 
     if out is not None:
         out.copy_(pred, non_blocking=True)
@@ -98,6 +120,7 @@ if __name__ == "__main__":
     parser.add_argument('--num_patch', type=int, help='number of point in each patch', default=256)  # 192
     parser.add_argument('--num_out', type=int, default=None, help='number of point of output point cloud')
     parser.add_argument('--device', type=str, default=None, help='CUDA device (default cuda:LOCAL_RANK)')
+    parser.add_argument('--batch_clouds', type=int, default=128, help='same-sized clouds per GPU batch')
 
     args = parser.parse_args()
 
@@ -108,4 +131,5 @@ if __name__ == "__main__":
         data_paths.extend([os.path.join(root, f) for f in files if '.xyz' in f])
 
     upsampling(data_paths, args.target, args.checkpoint, up_ratio=args.up_ratio,
-        num_outlier=24, num_patch=args.num_patch, num_upsampling=args.num_out, seed=args.seed, device=args.device)
+        num_outlier=24, num_patch=args.num_patch, num_upsampling=args.num_out, seed=args.seed, device=args.device,
+        batch_clouds=args.batch_clouds)

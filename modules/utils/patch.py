@@ -1,8 +1,8 @@
 """PatchHelper -- same class / method names / argument meaning as the reference's
 modules/utils/patch.py:17-215, with knn_cuda.KNN, pointnet2_ops.furthest_point_sample/gather_operation and
-the chamfer_3D extension replaced by puflow_b200 kernels (pf_knn_patch, pf_fps, pf_chamfer_nn).
-Everything stays on the GPU; the only PyTorch ops left are index gathers and the normalisation
-reductions (plumbing)."""
+the chamfer_3D extension replaced by puflow_b200 kernels (pf_knn_patch, pf_fps, pf_chamfer_nn) and the tensor
+glue in between (normalise, patch gather, de-normalise + concat, merge gather, outlier selection) by the kernels of
+csrc/caller.cu.  `upsample` with a PointInterpFlow and jitter=False is ONE C call (pf_upsample_clouds)."""
 import torch
 import torch.nn as nn
 from torch import Tensor
@@ -51,10 +51,26 @@ class PatchHelper(object):
             self.__extract_func_name__ = 'extract_knn_patch'
             self.knn = KNN(k=self.__npoint_patch, transpose_mode=False)
 
+    @property
+    def npoint_patch(self):
+        return self.__npoint_patch
+
+    @property
+    def patch_expand_ratio(self):
+        return self.__patch_expand_ratio
+
     def upsample(self, upsampler: nn.Module, pc: Tensor, npoint: int, upratio=None, jitter=False, **kwargs):
         """pc[B,N,3] -> [B,npoint,3]; reference patch.py:35-79."""
         B, N, C = pc.shape
         extract_func = getattr(self, self.__extract_func_name__)
+        # the whole method as one C call (pf_upsample_clouds: same kernels in the same order, no Python in between) when
+        # the upsampler is the drop-in PointInterpFlow and nothing below needs a Python hook
+        eng = upsampler.engine(pc.device) if hasattr(upsampler, "engine") and pc.is_cuda else None
+        if eng is not None and eng.flow_tc and not jitter and not kwargs and C == 3 and not ops.per_launch_events_wanted() \
+                and N >= self.__npoint_patch >= 16:
+            n_patch = int(N / self.__npoint_patch * self.__patch_expand_ratio)
+            if 1 <= n_patch <= N:
+                return eng.upsample_clouds(pc, upratio or 4, npoint, 0, self.__npoint_patch, n_patch)
 
         pc, g_centroid, g_furthest_distance = PatchHelper.normalize_pc(pc)
         if jitter:
@@ -84,8 +100,11 @@ class PatchHelper(object):
             predict_patches = patch_sharded(lambda p: upsampler.sample(p, upratio=(upratio or 4), **kwargs), patches)
         else:
             predict_patches = upsampler.sample(patches, upratio=(upratio or 4), **kwargs)  # [B * n_patch, k2, C]
-        predict_patches = torch.cat([predict_patches, patches], dim=1)
-        predict_patches = predict_patches * furthest_distance + centroids
+        if predict_patches.is_cuda and C == 3:          # cat + scale + shift in one kernel (pf_denorm_concat)
+            predict_patches = ops.denorm_concat(predict_patches.contiguous().float(), patches, centroids, furthest_distance)
+        else:
+            predict_patches = torch.cat([predict_patches, patches], dim=1)
+            predict_patches = predict_patches * furthest_distance + centroids
         return predict_patches.reshape(B, n_patch, -1, C)
 
     @staticmethod
@@ -98,9 +117,9 @@ class PatchHelper(object):
         else:
             _, n_patch = seed_centroids_idx.shape
             patch_centroids_idx = seed_centroids_idx
-        B = pc.shape[0]
-        seeds = pc[torch.arange(B, device=pc.device).view(-1, 1), patch_centroids_idx.long()].contiguous()
-        idx = ops.knn_patch(seeds.float(), pc.contiguous().float(), npoint_patch)          # [B, n_patch, k]
+        pc32 = pc.contiguous().float()
+        seeds = ops.gather_points(pc32, patch_centroids_idx.int().contiguous())
+        idx = ops.knn_patch(seeds, pc32, npoint_patch)                                     # [B, n_patch, k]
         return idx.long(), n_patch
 
     @staticmethod
@@ -110,7 +129,10 @@ class PatchHelper(object):
         idx_b = torch.arange(B, device=pc.device).view(-1, 1)
         idx_patches, n_patch = PatchHelper._extract_idx_patches(pc, knn_searcher, npoint_patch, expand_ratio,
                                                                 seed_centroids_idx)
-        patches = pc[idx_b, idx_patches.flatten(start_dim=1)]  # [B, n_patch * k, C]
+        if pc.is_cuda and C == 3 and pc.dtype == torch.float32:
+            patches = ops.gather_points(pc.contiguous(), idx_patches.flatten(start_dim=1).int().contiguous())
+        else:
+            patches = pc[idx_b, idx_patches.flatten(start_dim=1)]  # [B, n_patch * k, C]
         return patches.reshape(B, n_patch, npoint_patch, C)
 
     @staticmethod
@@ -127,9 +149,10 @@ class PatchHelper(object):
             patches = patches.reshape(B, -1, C).contiguous()
         else:
             patches = torch.cat([patches.reshape(B, -1, C), origins], dim=1).contiguous()
-        patches_T = patches.transpose(1, 2).contiguous()
         idx_predict_pc = furthest_point_sample(patches, npoint)
-        return gather_operation(patches_T, idx_predict_pc)  # [B, 3, npoint]
+        if patches.is_cuda and C == 3 and patches.dtype == torch.float32:
+            return ops.gather_points(patches, idx_predict_pc).transpose(1, 2)  # [B, 3, npoint]
+        return gather_operation(patches.transpose(1, 2).contiguous(), idx_predict_pc)  # [B, 3, npoint]
 
     @staticmethod
     def merge_pc(pc1: Tensor, pc2: Tensor, npoint: int):
@@ -139,7 +162,11 @@ class PatchHelper(object):
 
     @staticmethod
     def normalize_pc(pc: Tensor):
-        """centroid / max-radius normalisation; reference patch.py:168-178."""
+        """centroid / max-radius normalisation; reference patch.py:168-178.  [B,n,3] fp32 CUDA tensors go through
+        pf_normalize_pc (one kernel); anything else (other widths, CPU tensors of host-side tools) through the torch
+        expressions of the reference."""
+        if pc.is_cuda and pc.dim() == 3 and pc.shape[2] == 3 and pc.dtype == torch.float32:
+            return ops.normalize_pc(pc.contiguous())
         centroid = torch.mean(pc, dim=1, keepdim=True)
         pc = pc - centroid
         dist_square = torch.sum(pc ** 2, dim=-1, keepdim=True).sqrt()
@@ -161,20 +188,10 @@ class PatchHelper(object):
     @staticmethod
     def remove_outliers(sr: Tensor, lr: Tensor, num_outliers: int) -> Tensor:
         """Drop the num_outliers generated points farthest from the input, keeping the survivors' order;
-        reference patch.py:198-214 with chamfer_3DDist -> pf_chamfer_nn."""
-        (B, N, _), device = sr.shape, sr.device
-        dist1, _, _, _ = ops.chamfer_nn(sr.contiguous().float(), lr.contiguous().float(), both=False)
-        idx_dist1 = torch.argsort(dist1, dim=-1, descending=True, stable=True)
-        idx_outliers = idx_dist1[:, :num_outliers]
-        idxb = torch.arange(B, device=device).view(-1, 1)
-        keep = torch.ones((B, N), dtype=torch.bool, device=device)
-        keep[idxb, idx_outliers] = False
-        # The reference compacts with torch.nonzero (patch.py:211), which waits for the device; every row keeps exactly
-        # N - num_outliers points, so the same index list comes from a prefix sum and a scatter with no host round trip
-        # (dropped points go to a spare last column).
-        n_keep = N - num_outliers
-        dest = torch.where(keep, torch.cumsum(keep, dim=1) - 1, n_keep)
-        idx_inverse = torch.empty((B, n_keep + 1), dtype=torch.int64, device=device)
-        idx_inverse.scatter_(1, dest, torch.arange(N, device=device).expand(B, N))
-        return sr[idxb, idx_inverse[:, :n_keep]]
+        reference patch.py:198-214 with chamfer_3DDist -> pf_chamfer_nn (only the sr -> lr direction is read) and
+        argsort + nonzero -> pf_remove_outliers (a top-k select on the distances and an ordered compaction: the points
+        dropped are the first num_outliers of a stable descending argsort; no sort, no host round trip)."""
+        sr = sr.contiguous().float()
+        dist1, _, _, _ = ops.chamfer_nn(sr, lr.contiguous().float(), both=False)
+        return ops.remove_outliers(sr, dist1, num_outliers)
 # -----------------------------------------------------------------------------------------

@@ -48,9 +48,16 @@ SIGNATURES = {
     "pf_xyz_write": [ctypes.c_char_p, _vp, _i64, _i],
     "pf_model_entry": [_i, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)],
     "pf_upsample_patches": [_vp, _vp, _i, _i, _i, _vp, _i64, _vp, _vp, _vp],
+    "pf_normalize_pc": [_vp, _i, _i, _vp, _vp, _vp, _vp],
+    "pf_gather_normalize": [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "pf_gather_points": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp],
+    "pf_denorm_concat": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp],
+    "pf_remove_outliers": [_vp, _vp, _i, _i, _i, _vp, _vp],
+    "pf_upsample_clouds": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i64, _vp, _vp],
     "pf_profile_enable": [_i],
-    "pf_profile_slots": [],
-    "pf_profile_read": [_vp, _i],
+    "pf_profile_intervals": [],
+    "pf_profile_interval": [_i, ctypes.c_char_p, ctypes.POINTER(ctypes.c_float)],
+    "pf_profile_clear": [],
 }
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)
@@ -62,12 +69,12 @@ lib.pf_model_bytes.argtypes = []
 lib.pf_model_bytes.restype = ctypes.c_int64
 lib.pf_upsample_workspace_bytes.argtypes = [_i, _i, _i]
 lib.pf_upsample_workspace_bytes.restype = ctypes.c_int64
-lib.pf_profile_slot_name.argtypes = [_i]
-lib.pf_profile_slot_name.restype = ctypes.c_char_p
+lib.pf_upsample_clouds_workspace_bytes.argtypes = [_i, _i, _i, _i, _i, _i]
+lib.pf_upsample_clouds_workspace_bytes.restype = ctypes.c_int64
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 5
+PF_ABI_VERSION = 6
 PF_MODEL_ENTRIES = 27
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "prof.h"
 #include "puflow_b200.h"
 
 namespace {
@@ -127,81 +128,34 @@ __global__ void logp_mean_kernel(const double* __restrict__ pv, int Bp, float* _
     if (threadIdx.x == 0) logp[0] = (float)(-sh[0] / Bp);
 }
 
-// ---- optional per-launch timing of pf_upsample_patches (bench.py's breakdown / roofline) --------------------------------
-// CUDA events recorded on the caller's stream around every launch of the call; one slot per launch, fixed order.
-// Not thread-safe (one profiling host thread), off by default, costs nothing when off.
-constexpr int PROF_SLOTS = 3 * NB + 5;          // knn | 6 x (projection, EdgeConv, chain) | flow_fwd | logp | interp | flow_inv
-struct Profile {
-    bool on = false;
-    int calls = 0;
-    std::vector<cudaEvent_t> ev;                // (PROF_SLOTS + 1) boundaries per recorded call
-    char names[PROF_SLOTS][40];
-};
-Profile& prof() {
-    static Profile p = [] {
-        Profile q;
-        int n = 0;
-        snprintf(q.names[n++], 40, "knn_topk_k%d", KNN);
-        for (int i = 0; i < NB; i++) {
-            if (i == 0) snprintf(q.names[n++], 40, "linear_k3_n%d", r2_of(0));
-            else snprintf(q.names[n++], 40, "linear_split_k%d_n%d", CFG[i].c_in, r2_of(i));
-            snprintf(q.names[n++], 40, "edgeconv_tc_g%d_c%d_k%d", CFG[i].g, CFG[i].c_out, KNN);
-            snprintf(q.names[n++], 40, "cond_chain_tc_c%d", CFG[i].c_out);
-        }
-        snprintf(q.names[n++], 40, "flow_fwd_tc");
-        snprintf(q.names[n++], 40, "logp");
-        snprintf(q.names[n++], 40, "interp_tc");
-        snprintf(q.names[n++], 40, "flow_inv_tc");
-        return q;
-    }();
-    return p;
-}
-// boundary k of the current call (k = 0 before the first launch, k = i + 1 after launch i)
-struct Marker {
-    Profile& p;
-    cudaStream_t st;
-    size_t base;
-    bool on;
-    Marker(cudaStream_t s) : p(prof()), st(s), base(0), on(prof().on) {
-        if (!on) return;
-        base = (size_t)p.calls * (PROF_SLOTS + 1);
-        while (p.ev.size() < base + PROF_SLOTS + 1) {
-            cudaEvent_t e;
-            if (cudaEventCreate(&e) != cudaSuccess) { on = false; return; }
-            p.ev.push_back(e);
-        }
-        p.calls++;
-    }
-    void mark(int k) { if (on) cudaEventRecord(p.ev[base + k], st); }
-};
-
 }  // namespace
 
+pf::Recorder& pf::recorder() {
+    thread_local Recorder r;
+    return r;
+}
+
 extern "C" int pf_profile_enable(int on) {
-    Profile& p = prof();
-    p.on = on != 0;
-    p.calls = 0;
+    pf::Recorder& r = pf::recorder();
+    r.on = on != 0;
+    r.reset();
     return 0;
 }
-extern "C" int pf_profile_slots(void) { return PROF_SLOTS; }
-extern "C" const char* pf_profile_slot_name(int i) { return i >= 0 && i < PROF_SLOTS ? prof().names[i] : ""; }
-extern "C" int pf_profile_read(float* ms, int max_calls) {
-    Profile& p = prof();
-    const int n = p.calls < max_calls ? p.calls : max_calls;
-    for (int c = 0; c < n; c++) {
-        const size_t base = (size_t)c * (PROF_SLOTS + 1);
-        if (cudaEventSynchronize(p.ev[base + PROF_SLOTS]) != cudaSuccess) {
-            pf_set_error("pf_profile_read: %s", cudaGetErrorString(cudaGetLastError()));
-            return -1;
-        }
-        for (int i = 0; i < PROF_SLOTS; i++) {
-            float t = 0.f;
-            cudaEventElapsedTime(&t, p.ev[base + i], p.ev[base + i + 1]);
-            ms[(size_t)c * PROF_SLOTS + i] = t;
-        }
-    }
-    p.calls = 0;
-    return n;
+extern "C" int pf_profile_intervals(void) { return (int)pf::recorder().iv.size(); }
+extern "C" int pf_profile_interval(int i, char* name40, float* ms) {
+    pf::Recorder& r = pf::recorder();
+    PF_CHECK_ARG(i >= 0 && (size_t)i < r.iv.size() && name40 && ms, "pf_profile_interval: index %d outside [0, %d)", i,
+                 (int)r.iv.size());
+    const pf::Recorder::Interval& v = r.iv[i];
+    PF_CUDA(cudaEventSynchronize(r.ev[v.e1]));
+    PF_CUDA(cudaEventElapsedTime(ms, r.ev[v.e0], r.ev[v.e1]));
+    strncpy(name40, v.name.c_str(), 39);
+    name40[39] = 0;
+    return 0;
+}
+extern "C" int pf_profile_clear(void) {
+    pf::recorder().reset();
+    return 0;
 }
 
 extern "C" int64_t pf_model_bytes(void) { return layout().total; }
@@ -250,9 +204,8 @@ extern "C" int pf_upsample_patches(const void* model, const float* xyz, int Bp, 
     double* pv = reinterpret_cast<double*>(ws + w.pv);
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
-    Marker mk(st);
-    int slot = 0;
-    mk.mark(slot++);
+    pf::ProfScope mk(st);
+    char tag[40];
 
     // a1: kNN-16 inside each patch (grid.y limit: 65,535 patches per launch)
     for (int b0 = 0; b0 < Bp; b0 += 65535) {
@@ -260,7 +213,8 @@ extern "C" int pf_upsample_patches(const void* model, const float* xyz, int Bp, 
         const float* q = xyz + (size_t)b0 * N * 3;
         if ((rc = pf_knn_topk(q, q, nb, N, N, KNN, idx + (size_t)b0 * N * KNN, nullptr, stream))) return rc;
     }
-    mk.mark(slot++);
+    snprintf(tag, sizeof(tag), "knn_topk_k%d", KNN);
+    mk.mark(tag);
     // a2-a4 + first layers of the conditioning nets: six EdgeConv blocks, each followed by its fused conditioning chain
     for (int i = 0; i < NB; i++) {
         const int r2 = r2_of(i);
@@ -270,28 +224,32 @@ extern "C" int pf_upsample_patches(const void* model, const float* xyz, int Bp, 
         else
             rc = pf_linear_tc_split(split, m(l.feat_wpq_tc[i]), bpq, pq, r2, M, CFG[i].c_in, r2, PF_ACT_NONE, 0.f, stream);
         if (rc) return rc;
-        mk.mark(slot++);
+        if (i == 0) snprintf(tag, sizeof(tag), "linear_k3_n%d", r2);
+        else snprintf(tag, sizeof(tag), "linear_split_k%d_n%d", CFG[i].c_in, r2);
+        mk.mark(tag);
         if ((rc = pf_edgeconv_tc_split(pq, idx, m(l.feat_wtc[i]), c, i + 1 < NB ? split : nullptr, Bp, N, KNN, CFG[i].g,
                                        CFG[i].c_out, 0.05f, stream)))
             return rc;
-        mk.mark(slot++);
+        snprintf(tag, sizeof(tag), "edgeconv_tc_g%d_c%d_k%d", CFG[i].g, CFG[i].c_out, KNN);
+        mk.mark(tag);
         if ((rc = pf_cond_chain_tc(c, CFG[i].c_out, m(l.chain[i]), raw1 + (size_t)i * M * 64, sb + (size_t)i * M * 8, M, stream)))
             return rc;
-        mk.mark(slot++);
+        snprintf(tag, sizeof(tag), "cond_chain_tc_c%d", CFG[i].c_out);
+        mk.mark(tag);
     }
     // a5-a11: flow forward -> z, log-likelihood
     if ((rc = pf_flow_fwd_tc(xyz, raw1, 64, sb, m(l.flow), z, ssum, M, NB, stream))) return rc;
-    mk.mark(slot++);
+    mk.mark("flow_fwd_tc");
     if (logp) {
         logp_patch_kernel<<<Bp, 256, 0, st>>>(z, ssum, reinterpret_cast<const float*>(m(l.logdet)), N, pv);
         logp_mean_kernel<<<1, 256, 0, st>>>(pv, Bp, logp);
         if ((rc = pf_launch_status("logp kernels"))) return rc;
+        mk.mark("logp");
     }
-    mk.mark(slot++);
     // a12-a15: latent interpolation (the k = 8 list is the head of the sorted K = 16 list), a10: flow inverse
     if ((rc = pf_interp_tc(xyz, z, idx, KNN, m(l.interp), zup, Bp, N, R, stream))) return rc;
-    mk.mark(slot++);
+    mk.mark("interp_tc");
     rc = pf_flow_inv_tc(zup, raw1, 64, sb, m(l.flow), x, M, R, NB, stream);
-    mk.mark(slot++);
+    mk.mark("flow_inv_tc");
     return rc;
 }

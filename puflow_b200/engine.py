@@ -180,13 +180,63 @@ class PUFlowEngine:
         in x; logp_x reduced in float64 on the device.  What a non-Python host would call."""
         if xyz.dim() != 3 or xyz.shape[2] != 3:
             raise ValueError(f"expected xyz[B,N,3], got {tuple(xyz.shape)}")
-        if self._model_blob is None:
-            from .packing import pack_model_blob
-            self._model_blob = pack_model_blob(self.w).to(self.device)
-        return ops.upsample_patches(self._model_blob, xyz.contiguous().float(), upratio)
+        return ops.upsample_patches(self.model_blob(), xyz.contiguous().float(), upratio)
 
     def sample(self, xyz: torch.Tensor, upratio: int = 4):
         return self.forward(xyz, upratio)[0]
+
+    def model_blob(self):
+        if self._model_blob is None:
+            from .packing import pack_model_blob
+            self._model_blob = pack_model_blob(self.w).to(self.device)
+        return self._model_blob
+
+    @torch.no_grad()
+    def upsample_clouds(self, clouds: torch.Tensor, upratio: int, npoint: int, num_outliers: int, patch_points: int,
+                        n_patch: int, out: torch.Tensor = None, graph: bool = False):
+        """PatchHelper.upsample(jitter=False) [+ remove_outliers] for clouds[B,N,3] in ONE C call (pf_upsample_clouds):
+        normalise -> seeds -> patches -> network -> merge FPS -> (Chamfer + outlier removal), every launch on the current
+        stream.  graph=True replays the launch sequence from a CUDA graph captured per shape (static input / output /
+        workspace buffers owned by the engine; the result is copied out)."""
+        clouds = clouds.contiguous().float()
+        if not graph:
+            return ops.upsample_clouds(self.model_blob(), clouds, upratio, npoint, num_outliers, patch_points, n_patch, out=out)
+        key = ("clouds", tuple(clouds.shape), int(upratio), int(npoint), int(num_outliers), int(patch_points), int(n_patch))
+        ent = self._graphs.pop(key, None)
+        if ent is None:
+            B, N, _ = clouds.shape
+            static_in = clouds.clone()
+            static_out = torch.empty((B, npoint - num_outliers, 3), dtype=torch.float32, device=self.device)
+            ws = torch.empty((ops.upsample_clouds_workspace_bytes(B, N, upratio, npoint, patch_points, n_patch),),
+                             dtype=torch.uint8, device=self.device)
+            blob = self.model_blob()
+            run = lambda: ops.upsample_clouds(blob, static_in, upratio, npoint, num_outliers, patch_points, n_patch,
+                                              out=static_out, workspace=ws)
+            cur = torch.cuda.current_stream(self.device)
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(cur)
+            prev = ops.set_launch_log(None)
+            try:
+                with torch.cuda.stream(side):
+                    run()                                # lazy initialisation (smem opt-ins) before capture
+                cur.wait_stream(side)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    run()
+            finally:
+                ops.set_launch_log(prev)
+            ent = (g, static_in, static_out, ws, ops.cloud_launches(B * n_patch, num_outliers))
+            while len(self._graphs) >= self.MAX_GRAPHS:
+                self._graphs.pop(next(iter(self._graphs)))
+        self._graphs[key] = ent
+        g, static_in, static_out, _, n_launch = ent
+        static_in.copy_(clouds)
+        g.replay()
+        ops.count_launches(n_launch)
+        if out is not None:
+            out.copy_(static_out)
+            return out
+        return static_out.clone()
 
     # ---- CUDA-graph replay of the whole path (SURVEY.md section 8f rank 3) ---------------------------------------
     @torch.no_grad()

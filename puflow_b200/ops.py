@@ -42,25 +42,24 @@ _c_profile = False
 
 
 def c_profile(on: bool):
-    """Switch the library's own per-launch event timing of pf_upsample_patches on / off (pf_profile_enable): with it on,
-    per-launch times of the network come from inside the one C call, and nothing has to go kernel by kernel in Python."""
+    """Switch the library's own per-launch event timing of pf_upsample_patches / pf_upsample_clouds on / off
+    (pf_profile_enable, per host thread): per-launch times then come from inside the one C call, and nothing has to go
+    kernel by kernel in Python."""
     global _c_profile
     _c_profile = bool(on)
     N.check(lib.pf_profile_enable(1 if on else 0), "pf_profile_enable")
 
 
-def c_profile_read(max_calls: int = 512):
-    """{tag: [ms, ...]} of the pf_upsample_patches calls recorded since c_profile(True) / the last read (waits for them)."""
+def c_profile_read():
+    """{tag: [ms, ...]} of the launches of the one-call entry points recorded on THIS host thread since c_profile(True) /
+    the last read (waits for them)."""
     import ctypes
-    slots = lib.pf_profile_slots()
-    buf = (ctypes.c_float * (slots * max_calls))()
-    n = lib.pf_profile_read(buf, max_calls)
-    if n < 0:
-        raise N.PuflowError(f"pf_profile_read failed: {lib.pf_last_error().decode(errors='replace')}")
     out = {}
-    for c in range(n):
-        for i in range(slots):
-            out.setdefault(lib.pf_profile_slot_name(i).decode(), []).append(float(buf[c * slots + i]))
+    name, ms = ctypes.create_string_buffer(40), ctypes.c_float()
+    for i in range(lib.pf_profile_intervals()):
+        N.check(lib.pf_profile_interval(i, name, ctypes.byref(ms)), "pf_profile_interval")
+        out.setdefault(name.value.decode(), []).append(float(ms.value))
+    lib.pf_profile_clear()
     return out
 
 
@@ -374,14 +373,33 @@ def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.
 
 
 # ---- whole network in one C call ---------------------------------------------------------------------
-_workspaces = {}
+class _Workspaces:
+    """Scratch buffers of the one-call entry points, one per (device, stream, size): two streams (or two host threads on
+    two streams) never share a buffer, a handful are kept (LRU) so that alternating shapes do not re-allocate GBs."""
+    KEEP = 3
+
+    def __init__(self):
+        self.buf = {}
+
+    def get(self, device, nbytes: int):
+        key = (device.index if device.index is not None else torch.cuda.current_device(), _stream(), int(nbytes))
+        ws = self.buf.pop(key, None)
+        if ws is None:
+            while len(self.buf) >= self.KEEP:
+                self.buf.pop(next(iter(self.buf)))
+            ws = torch.empty((max(int(nbytes), 1),), dtype=torch.uint8, device=device)
+        self.buf[key] = ws                       # most recently used last
+        return ws
 
 
-def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_logp: bool = True):
+_workspaces = _Workspaces()
+
+
+def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_logp: bool = True, workspace=None):
     """pf_upsample_patches: xyz[Bp,N,3] -> (x[Bp, N*R, 3], logp scalar tensor or None) with the whole of
     PointInterpFlow.forward (interpflow.py:327-337) launched from C on the current stream.  model_blob: uint8 CUDA tensor
-    from packing.pack_model_blob.  The scratch buffer is kept per (device, size) and re-used by later calls on the same
-    stream order; 24 kernel launches (22 without logp)."""
+    from packing.pack_model_blob.  The scratch buffer is kept per (device, stream, size) unless `workspace` is given;
+    24 kernel launches (22 without logp)."""
     _chk(model_blob, "model_blob", torch.uint8), _chk(xyz, "xyz")
     if xyz.dim() != 3 or xyz.shape[2] != 3:
         raise ValueError(f"upsample_patches: expected xyz[Bp,N,3], got {tuple(xyz.shape)}")
@@ -391,22 +409,60 @@ def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_l
     need = lib.pf_upsample_workspace_bytes(Bp, Npts, R)
     if need < 0:
         raise ValueError(f"upsample_patches: bad sizes Bp={Bp} N={Npts} R={R}")
-    key = (xyz.device, need)
-    ws = _workspaces.get(key)
-    if ws is None:
-        _workspaces.clear()                      # one live workspace: shapes rarely alternate, GBs do not pile up
-        ws = _workspaces[key] = torch.empty((max(need, 1),), dtype=torch.uint8, device=xyz.device)
     x = torch.empty((Bp, Npts * R, 3), dtype=torch.float32, device=xyz.device)
     logp = torch.empty((), dtype=torch.float32, device=xyz.device) if want_logp else None
     with _dev(xyz):
+        ws = workspace if workspace is not None else _workspaces.get(xyz.device, need)
         N.check(lib.pf_upsample_patches(model_blob.data_ptr(), xyz.data_ptr(), Bp, Npts, R, ws.data_ptr(), need,
                                         x.data_ptr(), logp.data_ptr() if want_logp else None, _stream()),
                 "pf_upsample_patches")
     if Bp:
-        count_launches(((Bp + 65534) // 65535) + 3 * 6 + 3 + (2 if want_logp else 0))
+        count_launches(network_launches(Bp, want_logp))
     elif want_logp:
         logp.fill_(float("nan"))
     return x, logp
+
+
+def network_launches(Bp: int, want_logp: bool) -> int:
+    return ((Bp + 65534) // 65535) + 3 * 6 + 3 + (2 if want_logp else 0)
+
+
+def upsample_clouds_workspace_bytes(B, Npts, R, npoint, patch_points, n_patch) -> int:
+    need = lib.pf_upsample_clouds_workspace_bytes(B, Npts, R, npoint, patch_points, n_patch)
+    if need < 0:
+        raise ValueError(f"upsample_clouds: bad sizes B={B} N={Npts} R={R} npoint={npoint}")
+    return need
+
+
+def upsample_clouds(model_blob: torch.Tensor, clouds: torch.Tensor, R: int, npoint: int, num_outliers: int,
+                    patch_points: int, n_patch: int, out: torch.Tensor = None, workspace=None):
+    """pf_upsample_clouds: clouds[B,N,3] -> [B, npoint - num_outliers, 3]: PatchHelper.upsample(jitter=False) (+
+    remove_outliers when num_outliers > 0) launched from C on the current stream (upsample.py:46-54)."""
+    _chk(model_blob, "model_blob", torch.uint8), _chk(clouds, "clouds")
+    if clouds.dim() != 3 or clouds.shape[2] != 3:
+        raise ValueError(f"upsample_clouds: expected clouds[B,N,3], got {tuple(clouds.shape)}")
+    B, Npts, _ = clouds.shape
+    need = upsample_clouds_workspace_bytes(B, Npts, R, npoint, patch_points, n_patch)
+    if out is None:
+        out = torch.empty((B, npoint - num_outliers, 3), dtype=torch.float32, device=clouds.device)
+    else:
+        _chk(out, "out")
+        if tuple(out.shape) != (B, npoint - num_outliers, 3):
+            raise ValueError("upsample_clouds: out has the wrong shape")
+    if B == 0:
+        return out
+    with _dev(clouds):
+        ws = workspace if workspace is not None else _workspaces.get(clouds.device, need)
+        N.check(lib.pf_upsample_clouds(model_blob.data_ptr(), clouds.data_ptr(), B, Npts, R, npoint, num_outliers,
+                                       patch_points, n_patch, ws.data_ptr(), need, out.data_ptr(), _stream()),
+                "pf_upsample_clouds")
+    count_launches(cloud_launches(B * n_patch, num_outliers))
+    return out
+
+
+def cloud_launches(Bp: int, num_outliers: int) -> int:
+    """kernels of one pf_upsample_clouds call: 5 before the network, the network, 3 after, + Chamfer and the outlier pass."""
+    return 5 + network_launches(Bp, False) + 3 + (2 if num_outliers else 0)
 
 
 # ---- caller side ---------------------------------------------------------------------------------
@@ -439,3 +495,74 @@ def knn_patch(q: torch.Tensor, p: torch.Tensor, k: int):
         N.check(lib.pf_knn_patch(q.data_ptr(), p.data_ptr(), B, nq, p.shape[1], k, idx.data_ptr(), _stream()),
                 "pf_knn_patch")
     return idx
+
+
+# ---- caller glue as kernels (csrc/caller.cu) ------------------------------------------------------------------
+def normalize_pc(pc: torch.Tensor):
+    """pc[B,n,3] -> (normalised [B,n,3], centroid [B,1,3], radius [B,1,1]); PatchHelper.normalize_pc (patch.py:168-178)."""
+    _chk(pc, "pc")
+    if pc.dim() != 3 or pc.shape[2] != 3:
+        raise ValueError(f"normalize_pc: expected pc[B,n,3], got {tuple(pc.shape)}")
+    B, n, _ = pc.shape
+    out = torch.empty_like(pc)
+    cen = torch.empty((B, 1, 3), dtype=torch.float32, device=pc.device)
+    rad = torch.empty((B, 1, 1), dtype=torch.float32, device=pc.device)
+    with _dev(pc), _launch("normalize_pc"):
+        N.check(lib.pf_normalize_pc(pc.data_ptr(), B, n, out.data_ptr(), cen.data_ptr(), rad.data_ptr(), _stream()),
+                "pf_normalize_pc")
+    return out, cen, rad
+
+
+def gather_normalize(pc: torch.Tensor, idx: torch.Tensor):
+    """pc[B,n,3], idx[B,items,k] int32 -> (patches [B*items,k,3] normalised, centroid [B*items,1,3], radius [B*items,1,1])."""
+    _chk(pc, "pc"), _chk(idx, "idx", torch.int32)
+    B, n, _ = pc.shape
+    _, items, k = idx.shape
+    out = torch.empty((B * items, k, 3), dtype=torch.float32, device=pc.device)
+    cen = torch.empty((B * items, 1, 3), dtype=torch.float32, device=pc.device)
+    rad = torch.empty((B * items, 1, 1), dtype=torch.float32, device=pc.device)
+    with _dev(pc), _launch("gather_normalize"):
+        N.check(lib.pf_gather_normalize(pc.data_ptr(), idx.data_ptr(), B, n, items, k, out.data_ptr(), cen.data_ptr(),
+                                        rad.data_ptr(), _stream()), "pf_gather_normalize")
+    return out, cen, rad
+
+
+def gather_points(pc: torch.Tensor, idx: torch.Tensor, scale=None, shift=None):
+    """out[b,i] = pc[b, idx[b,i]] (* scale[b] + shift[b]); pc[B,n,3], idx[B,m] int32."""
+    _chk(pc, "pc"), _chk(idx, "idx", torch.int32)
+    B, n, _ = pc.shape
+    m = idx.shape[1]
+    out = torch.empty((B, m, 3), dtype=torch.float32, device=pc.device)
+    if scale is not None:
+        _chk(scale, "scale"), _chk(shift, "shift")
+    with _dev(pc), _launch("gather_points"):
+        N.check(lib.pf_gather_points(pc.data_ptr(), idx.data_ptr(), B, n, m, scale.data_ptr() if scale is not None else None,
+                                     shift.data_ptr() if shift is not None else None, out.data_ptr(), _stream()),
+                "pf_gather_points")
+    return out
+
+
+def denorm_concat(x: torch.Tensor, patches: torch.Tensor, cen: torch.Tensor, rad: torch.Tensor):
+    """cat([x, patches], 1) * rad + cen; x[I,nx,3], patches[I,np,3] -> [I, nx+np, 3] (patch.py:90-91)."""
+    _chk(x, "x"), _chk(patches, "patches"), _chk(cen, "cen"), _chk(rad, "rad")
+    I, nx, _ = x.shape
+    np_ = patches.shape[1]
+    out = torch.empty((I, nx + np_, 3), dtype=torch.float32, device=x.device)
+    with _dev(x), _launch("denorm_concat"):
+        N.check(lib.pf_denorm_concat(x.data_ptr(), patches.data_ptr(), cen.data_ptr(), rad.data_ptr(), I, nx, np_,
+                                     out.data_ptr(), _stream()), "pf_denorm_concat")
+    return out
+
+
+def remove_outliers(sr: torch.Tensor, dist1: torch.Tensor, num_outliers: int):
+    """sr[B,n,3], dist1[B,n] -> [B, n - num_outliers, 3]: the num_outliers largest dist1 dropped (ties: lowest index first),
+    order kept (patch.py:205-214)."""
+    _chk(sr, "sr"), _chk(dist1, "dist1")
+    B, n, _ = sr.shape
+    if num_outliers <= 0:
+        return sr.clone()
+    out = torch.empty((B, n - num_outliers, 3), dtype=torch.float32, device=sr.device)
+    with _dev(sr), _launch("remove_outliers"):
+        N.check(lib.pf_remove_outliers(sr.data_ptr(), dist1.data_ptr(), B, n, num_outliers, out.data_ptr(), _stream()),
+                "pf_remove_outliers")
+    return out
