@@ -16,7 +16,15 @@ normalise -> seed FPS -> patch kNN-256 -> [kNN-16 -> 6x EdgeConv+merge -> flow f
           of the clouds and device -> pinned host copy of the 128 x 8,192 x 3 result inside the timed region.
   network_only : the five north_star subsystems alone (PointInterpFlow.sample on pre-extracted patches).
   roofline : the kernel with the largest share of the step, algorithmic work / its average launch duration
-             measured live with CUDA events on the launching stream (see DESIGN.md for the per-kernel figures).
+             measured live with CUDA events on the launching stream (see DESIGN.md for the per-kernel figures);
+  roofline_all : the same figure for every kernel of the step (kNN, the EdgeConv shapes, projections, conditioning
+             chain, flow fwd / inv, interpolation, FPS, Chamfer, the caller-side glue kernels).
+  parity   : one cloud of the timed batch against the CPU oracle, outside the timed region: kNN index mismatches,
+             normwise error of the network output on that cloud's patches, Chamfer distance of the final clouds.
+  latency_one_cloud_ms : BASELINE.json configs[0] on the GPU (one 2,048-pt cloud through upsample_array, host buffers).
+  --config 3 : BASELINE.json configs[2], 5,000-pt clouds -> 20,000 points: (a) `--clouds` clouds per rank (cloud-sharded,
+             weak scaling), (b) ONE cloud with its 78 patches split over the ranks (all_gather of the generated points
+             timed separately; the merge FPS is sequential per cloud and replicated: Amdahl).
   cpu_baseline : the CPU restatement of the reference (oracle/, kind "port"; the reference's Python cannot travel
              to the GPU box) timed on this box's host cores on a bounded sample of the same workload.
 
@@ -53,11 +61,22 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-breakdown", action="store_true")
     ap.add_argument("--ref-clouds", type=int, default=1, help="clouds per step of the CPU reference arm")
-    return ap.parse_args()
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3],
+                    help="BASELINE.json config: 2 = 128 x 2,048-pt clouds per GPU (default, the metric's config); "
+                         "3 = 5,000-pt clouds (8 per GPU unless --clouds is given) + one cloud patch-sharded")
+    a = ap.parse_args()
+    if a.config == 3:
+        a.npts = 5000 if a.npts == N_PTS else a.npts
+        a.clouds = 8 if a.clouds == 128 else a.clouds
+    return a
+
+
+DTYPE = "f32 (3xfp16-split tcgen05, fp32 accumulate)"
 
 
 def workload_name(clouds, npts):
-    return f"PU1K-shape batch: {clouds} synthetic {npts}-pt clouds -> {npts * UP} pts, x4, per B200"
+    shape = "PU1K-shape" if npts == N_PTS else ("PU-GAN-shape" if npts == 5000 else "synthetic")
+    return f"{shape} batch: {clouds} synthetic {npts}-pt clouds -> {npts * UP} pts, x4, per B200"
 
 
 def make_clouds(clouds, npts, rank):
@@ -124,7 +143,7 @@ class ClockSampler:
 
 
 # ---- the reference's CPU path (oracle port), timed on the host cores ----------------------------------------------
-def cpu_reference_run(steps, warmup, clouds_per_step, npts):
+def cpu_reference_run(steps, warmup, clouds_per_step, npts, want_outputs=False):
     """Times oracle.puflow_oracle (the CPU restatement of the reference's Python: torch CPU ops + plain C for
     kNN / FPS / Chamfer) on `clouds_per_step` clouds of the bench workload per step.  Returns (points/s, ms/step,
     cores)."""
@@ -155,7 +174,33 @@ def cpu_reference_run(steps, warmup, clouds_per_step, npts):
         dt = time.perf_counter() - t0
     assert tuple(out[0].shape[-2:]) == (npts * UP, 3), out[0].shape
     pts = steps * clouds_per_step * npts * UP
+    if want_outputs:
+        return pts / dt, dt / steps * 1e3, cores, orc, out
     return pts / dt, dt / steps * 1e3, cores
+
+
+def parity_block(orc, oracle_out, gpu_out0, gpu_patches0, gpu_knn0, gpu_x0):
+    """Cloud 0 of the timed batch, GPU path against the CPU oracle (checker), outside the timed region.
+    kNN: index mismatches on the cloud's normalised patches (bit-exact bar); x: normwise relative error of the network
+    output per patch (bar 1e-4); cd: Chamfer distance of the final clouds, mean(d1) + mean(d2) of squared distances on
+    coordinates normalised like evaluate.py:230-235 (bar 1e-5).  The final clouds need not line up row by row: the merge
+    FPS is chaotic under 1e-7 perturbations of near-duplicate candidates."""
+    import numpy as np
+    import torch
+    from oracle import puflow_oracle as po
+    with torch.no_grad():
+        ref = orc.forward(torch.from_numpy(gpu_patches0), UP, return_all=True)
+    knn_bad = int((ref["knn_idx"].numpy() != gpu_knn0).sum())
+    xr = ref["x"].numpy()
+    err = np.abs(gpu_x0 - xr).reshape(xr.shape[0], -1).max(1) / np.abs(xr).reshape(xr.shape[0], -1).max(1)
+    a, b = gpu_out0.astype(np.float32), oracle_out.astype(np.float32)
+    c = b.mean(0, keepdims=True)
+    r = np.sqrt(((b - c) ** 2).sum(-1)).max()
+    d1, d2, _, _ = po.chamfer_nn(((a - c) / r)[None], ((b - c) / r)[None])
+    return {"cloud": 0, "patches": int(xr.shape[0]), "knn_index_mismatches": knn_bad, "knn_indices": int(gpu_knn0.size),
+            "x_normwise_rel_err_max": float(err.max()), "x_tolerance": 1e-4,
+            "chamfer_to_oracle": float(d1.mean() + d2.mean()), "chamfer_tolerance": 1e-5,
+            "ok": bool(knn_bad == 0 and err.max() <= 1e-4 and d1.mean() + d2.mean() <= 1e-5)}
 
 
 def run_reference(args):
@@ -212,7 +257,46 @@ def algorithmic_work(tag, Bc, npts):
         return "hbm", Bc * (npts * 12.0 + n_patch * (12 + 4 * PATCH)), "B"
     if tag == "chamfer_nn":
         return "hbm", Bc * ((npts * UP + N_OUTLIER) * 20.0 + npts * 12.0), "B"       # a -> b direction only
+    n_out, ncand = npts * UP + N_OUTLIER, n_patch * PATCH * (UP + 1)
+    if tag == "normalize_pc":
+        return "hbm", Bc * npts * 24.0, "B"
+    if tag == "gather_normalize":
+        return "hbm", Bc * (npts * 12.0 + n_patch * PATCH * 16.0), "B"
+    if tag == "denorm_concat":
+        return "hbm", Bc * (n_patch * PATCH * 12.0 + 2 * ncand * 12.0 - n_patch * PATCH * 12.0), "B"
+    if tag == "gather_points":      # two launches per step: the 32 seeds (negligible) and the merged cloud
+        return "hbm", Bc * (n_out * 16.0 + n_out * 12.0) / 2, "B"
+    if tag == "remove_outliers":
+        return "hbm", Bc * (n_out * 16.0 + (n_out - N_OUTLIER) * 12.0), "B"
     return "hbm", 0.0, "B"
+
+
+def pairs_per_launch(tag, Bc, npts):
+    """Pair-distance count of the brute-force neighbour kernels (their binding resource is the ALU)."""
+    n_patch = int(npts / PATCH * 4)
+    if tag.startswith("knn_topk_k"):
+        return float(Bc * n_patch * PATCH * PATCH)
+    if tag == "chamfer_nn":
+        return float(Bc * (npts * UP + N_OUTLIER) * npts)
+    if tag == "knn_patch":
+        return float(Bc * n_patch * npts)
+    return None
+
+
+def roofline_entry(tag, avg_ms, Bc, npts, peaks, traffic):
+    bound, amount, unit = algorithmic_work(tag, Bc, npts)
+    dur_s = avg_ms * 1e-3
+    if bound == "hbm":
+        ach, peak, u = amount / dur_s / 1e9, peaks["hbm_gbs"], "GB/s"
+    else:
+        ach, peak, u = amount / dur_s / 1e12, peaks["tensor_tflops"], "TFLOP/s"
+    e = {"kernel": tag, "bound": bound, "achieved": ach, "peak": peak, "unit": u, "frac": ach / peak,
+         "traffic": traffic.get(tag), "avg_launch_ms": avg_ms, "algorithmic_per_launch": amount, "algorithmic_unit": unit}
+    pr = pairs_per_launch(tag, Bc, npts)
+    if pr:
+        e["pair_distances_per_launch"] = pr
+        e["tera_pairs_per_s"] = pr / dur_s / 1e12
+    return e
 
 
 def load_peaks():
@@ -251,9 +335,11 @@ def run_ours(args):
     net.set_to_initialized_state()
     net = net.to(dev).eval()
     helper = PatchHelper(PATCH, patch_expand_ratio=4)
+    eng = net.engine(dev)
 
     Bc, npts = args.clouds, args.npts
     n_out = npts * UP + N_OUTLIER
+    n_patch = int(npts / PATCH * 4)
     host_in = torch.from_numpy(make_clouds(Bc, npts, rank)).pin_memory()
     host_out = torch.empty((Bc, npts * UP, 3), dtype=torch.float32).pin_memory()
     clouds = host_in.to(dev)
@@ -266,23 +352,20 @@ def run_ours(args):
 
     @torch.no_grad()
     def step():
-        pred = helper.upsample(net, clouds, npoint=n_out, upratio=UP, jitter=False)
-        return PatchHelper.remove_outliers(pred, clouds, N_OUTLIER)
+        # PatchHelper.upsample + remove_outliers (upsample.py:46-54) as the product path runs them: ONE C call
+        return eng.upsample_clouds(clouds, UP, n_out, N_OUTLIER, PATCH, n_patch)
 
     for _ in range(max(args.warmup, 3)):
         out = step()
     torch.cuda.synchronize(dev)
     assert tuple(out.shape) == (Bc, npts * UP, 3) and bool(torch.isfinite(out).all()), "bad output"
 
-    # ---- timed region: exactly K steps, device-timed, per-launch events on ---------------------------------
-    log = ops.LaunchLog(events=not args.no_breakdown)
+    # ---- timed region: exactly K steps, device-timed, per-launch events recorded inside the C call ----------------
+    log = ops.LaunchLog(events=False)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     sampler = ClockSampler(",".join(str(i) for i in range(world)), enabled=(rank == 0))   # this job's GPUs (local ranks)
     sampler.start()
     barrier()
-    # per-launch CUDA events: the network's come from inside the one C call (pf_profile_*), the caller-side kernels'
-    # (FPS, patch kNN, Chamfer) from the Python wrappers -- the kernel-by-kernel Python path cost 0.6 ms per step of host
-    # time at N = 1 and 3 ms at N = 8 (eight ranks on 16 host cores), which the timed region would have charged to the GPU
     prev = ops.set_launch_log(log)
     ops.c_profile(not args.no_breakdown)
     for e0, e1 in ev:
@@ -303,40 +386,31 @@ def run_ours(args):
     pts_per_step = world * Bc * npts * UP
     value = pts_per_step * args.steps / (t_ms * 1e-3)
 
-    # ---- per-kernel breakdown + roofline of the dominant kernel ----------------------------------------------
-    breakdown, roofline = None, None
+    # ---- per-kernel breakdown, roofline of every kernel and of the dominant one ------------------------------------
+    breakdown, roofline, roofline_all = None, None, None
     if not args.no_breakdown:
         peaks = load_peaks()
-        times = log.times_ms()
-        for k, v in c_times.items():
-            if k != "logp":                                   # two tiny reduction kernels, counted with the plumbing
-                times.setdefault(k, []).extend(v)
-        per = {k: (sum(v) / args.steps, len(v) // args.steps) for k, v in times.items()}
+        traffic = {}
+        rp = os.path.join(ROOT, "profiles", "traffic.json")          # dram bytes per launch from ncu (tools/ncu_traffic.py)
+        if os.path.exists(rp):
+            try:
+                traffic = json.load(open(rp))
+            except ValueError:
+                pass
+        per = {k: (sum(v) / args.steps, len(v) // args.steps) for k, v in c_times.items() if k != "logp"}
         tot = sum(v[0] for v in per.values())
         step_ms = t_ms / args.steps
         breakdown = {k: {"ms_per_step": round(v[0], 4), "launches_per_step": v[1], "share": round(v[0] / step_ms, 4)}
                      for k, v in sorted(per.items(), key=lambda kv: -kv[1][0])}
-        breakdown["(torch plumbing + gaps)"] = {"ms_per_step": round(step_ms - tot, 4), "launches_per_step": None,
-                                                "share": round((step_ms - tot) / step_ms, 4)}
-        top = max(per, key=lambda k: per[k][0])
-        bound, amount, unit = algorithmic_work(top, Bc, npts)
-        dur_s = per[top][0] / per[top][1] * 1e-3
-        if bound == "hbm":
-            ach, peak, u = amount / dur_s / 1e9, peaks["hbm_gbs"], "GB/s"
-        else:
-            ach, peak, u = amount / dur_s / 1e12, peaks["tensor_tflops"], "TFLOP/s"
-        roofline = {"kernel": top, "bound": bound, "achieved": ach, "peak": peak, "unit": u, "frac": ach / peak,
-                    "traffic": None, "avg_launch_ms": dur_s * 1e3, "algorithmic_per_launch": amount,
-                    "algorithmic_unit": unit, "peak_source": peaks["source"]}
-        if bound == "tensor":
+        breakdown["(launch gaps + logp)"] = {"ms_per_step": round(step_ms - tot, 4), "launches_per_step": None,
+                                             "share": round((step_ms - tot) / step_ms, 4)}
+        roofline_all = [roofline_entry(k, v[0] / v[1], Bc, npts, peaks, traffic)
+                        for k, v in sorted(per.items(), key=lambda kv: -kv[1][0])]
+        roofline = dict(roofline_all[0])
+        roofline["peak_source"] = peaks["source"]
+        if roofline["bound"] == "tensor":
             roofline["fp32_ffma_peak_tflops"] = 74.4
-            roofline["fp32_ffma_frac"] = ach / 74.4
-        rp = os.path.join(ROOT, "profiles", "traffic.json")          # dram bytes per launch from the ncu --set full capture
-        if os.path.exists(rp):
-            try:
-                roofline["traffic"] = json.load(open(rp)).get(top)
-            except ValueError:
-                pass
+            roofline["fp32_ffma_frac"] = roofline["achieved"] / 74.4
     gpu_launches = log.count
 
     # ---- network only (the five north_star subsystems on pre-extracted patches) ------------------------------
@@ -360,18 +434,8 @@ def run_ours(args):
     net_ms = float(tn.item())
     network_only = {"value": world * patches.shape[0] * PATCH * UP / (net_ms * 1e-3), "unit": "generated points/s",
                     "ms_per_step": net_ms, "patches_per_gpu": int(patches.shape[0])}
-    # the same network through the single C-ABI entry point (pf_upsample_patches), rank-local figure
-    with torch.no_grad():
-        eng = net.engine(dev)
-        eng.forward_c(patches, UP)
-        e0.record()
-        for _ in range(nrep):
-            eng.forward_c(patches, UP)
-        e1.record()
-        torch.cuda.synchronize()
-    network_only["c_abi_one_call_ms"] = e0.elapsed_time(e1) / nrep
 
-    # ---- e2e: host buffers in and out through the public API ----------------------------------------------------
+    # ---- e2e: host buffers in and out through the public API (one C call replayed from a CUDA graph) -------------------
     for _ in range(2):
         upsample_array(net, helper, host_in, UP, N_OUTLIER, None, dev, out=host_out)
     barrier()
@@ -388,26 +452,109 @@ def run_ours(args):
            "ms_per_step": float(te.item()) / args.steps * 1e3}
     assert bool(torch.isfinite(host_out).all())
 
-    # ---- CPU baseline on rank 0 at N=1 (bounded sample) ----------------------------------------------------------
-    cpu = None
+    # ---- one cloud alone (configs[0] on the GPU): latency through the public API, host buffers --------------------------
+    latency = None
+    if rank == 0:
+        one_in, one_out = host_in[:1].clone().pin_memory(), torch.empty((1, npts * UP, 3)).pin_memory()
+        latency = {}
+        for name, g in (("eager", False), ("graph", True)):
+            for _ in range(3):
+                upsample_array(net, helper, one_in, UP, N_OUTLIER, None, dev, out=one_out, graph=g)
+            ts = []
+            for _ in range(15):
+                t0 = time.perf_counter()
+                upsample_array(net, helper, one_in, UP, N_OUTLIER, None, dev, out=one_out, graph=g)
+                ts.append((time.perf_counter() - t0) * 1e3)
+            latency[name] = statistics.median(ts)
+        latency["note"] = f"one {npts}-pt cloud -> {npts * UP} pts, pinned host in / out, median of 15"
+
+    # ---- config 3 (b): ONE cloud, its patches split over the ranks ----------------------------------------------------
+    patch_sharded = None
+    if args.config == 3:
+        one = clouds[:1].contiguous() if rank == 0 else torch.empty((1, npts, 3), device=dev)
+        if world > 1:
+            dist.broadcast(one, 0)                     # every rank holds the same cloud (as when every rank reads the file)
+
+        @torch.no_grad()
+        def sharded():
+            pred = helper.upsample(net, one, npoint=n_out, upratio=UP, jitter=False, shard_patches=True)
+            return PatchHelper.remove_outliers(pred, one, N_OUTLIER)
+
+        for _ in range(3):
+            ref = sharded()
+        full = eng.upsample_clouds(one, UP, n_out, N_OUTLIER, PATCH, n_patch)
+        same = bool(torch.equal(ref, full))
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            sharded()
+        e1.record()
+        barrier()
+        tp = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+        # the exchange alone: all_gather of ceil(n_patch / world) x 1024 x 3 floats per rank
+        ag_ms = 0.0
+        if world > 1:
+            per = -(-n_patch // world)
+            buf = torch.zeros((per, PATCH * UP, 3), device=dev)
+            parts = [torch.empty_like(buf) for _ in range(world)]
+            for _ in range(3):
+                dist.all_gather(parts, buf)
+            barrier()
+            e0.record()
+            for _ in range(20):
+                dist.all_gather(parts, buf)
+            e1.record()
+            barrier()
+            ag_ms = e0.elapsed_time(e1) / 20
+        # the part that does not shard: merge FPS of one cloud (+ Chamfer / outlier pass), from the one-call path's timers
+        ops.c_profile(True)
+        eng.upsample_clouds(one, UP, n_out, N_OUTLIER, PATCH, n_patch)
+        ct = ops.c_profile_read()
+        ops.c_profile(False)
+        serial = sum(v[0] for k, v in ct.items() if k.startswith("fps_n") or k in ("chamfer_nn", "remove_outliers", "normalize_pc",
+                                                                                 "knn_patch", "gather_points", "gather_normalize",
+                                                                                 "denorm_concat"))
+        total1 = sum(v[0] for v in ct.values())
+        patch_sharded = {"ms_per_cloud": float(tp.item()), "points_per_s": npts * UP / (float(tp.item()) * 1e-3),
+                         "all_gather_ms": ag_ms, "patches": n_patch, "patches_per_rank": -(-n_patch // world),
+                         "bit_identical_to_unsharded": same,
+                         "one_call_unsharded_ms": total1, "replicated_ms": serial,
+                         "amdahl_serial_fraction": serial / total1,
+                         "note": "seed FPS, patch kNN and the merge FPS (sequential per cloud) run on every rank; only the "
+                                 "network shards"}
+
+    # ---- CPU baseline + parity on rank 0 at N=1 (bounded sample) ---------------------------------------------------
+    cpu, par = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, ms, cores = cpu_reference_run(steps=3, warmup=1, clouds_per_step=1, npts=npts)
+        v, ms, cores, orc, oracle_out = cpu_reference_run(steps=3, warmup=1, clouds_per_step=1, npts=npts, want_outputs=True)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "ms_per_cloud": ms,
                "sample": "1 cloud of the batch per run (full pipeline), 1 warm-up + 3 timed runs"}
+        with torch.no_grad():
+            p0 = patches[:n_patch].contiguous()
+            r0 = eng.forward(p0, UP, return_all=True)
+        par = parity_block(orc, np.asarray(oracle_out[0]).reshape(-1, 3), out[0].cpu().numpy(), p0.cpu().numpy(),
+                           r0["knn_idx"].cpu().numpy().astype(np.int64), r0["x"].cpu().numpy())
 
     if rank == 0:
-        print(json.dumps({
+        line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": t_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
             "config": {"workload": workload_name(Bc, npts), "clouds_per_gpu": Bc, "points_per_cloud": npts,
                        "patches_per_gpu": int(patches.shape[0]), "up_ratio": UP, "num_outlier": N_OUTLIER,
                        "weights": "pretrain/puflow-x4-pu1k.pt (408-key layout)",
                        "l2": "256 MiB flush between steps; per-step working set is several GB (>> 126 MB L2)",
                        "sharding": f"{world} rank(s), clouds sharded, no collective on the data path"},
             "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu, "network_only": network_only, "breakdown": breakdown,
-        }), flush=True)
+            "cpu_baseline": cpu, "parity": par, "latency_one_cloud_ms": latency, "network_only": network_only,
+            "breakdown": breakdown, "roofline_all": roofline_all,
+        }
+        if patch_sharded is not None:
+            line["patch_sharded_one_cloud"] = patch_sharded
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
