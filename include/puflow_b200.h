@@ -193,6 +193,13 @@ PF_API int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, floa
  * pf_fps dispatches here when work != NULL and n >= 4096. */
 PF_API long long pf_fps_work_floats(int B, int n);
 PF_API int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
+/* Same result again, for FEW LARGE clouds: the cloud's buckets are spread over a thread-block cluster of 2..16 CTAs (sorted
+ * coordinates and running minima in the cluster's shared memory, one DSMEM candidate exchange + remote mbarrier arrive per
+ * round) whenever B * cluster <= SM count; otherwise (a batch of many clouds) it is pf_fps_bucketed.  Config 3's merge FPS
+ * (20,024 of 99,840 candidates) and a single 2,048-pt cloud's (8,216 of 40,960) are the cases it is for.
+ * work: pf_fps_clustered_work_floats(B, n) floats. */
+PF_API long long pf_fps_clustered_work_floats(int B, int n);
+PF_API int pf_fps_clustered(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
 
 /* ---- caller glue as kernels ------------------------------------------------------

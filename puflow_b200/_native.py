@@ -42,6 +42,7 @@ SIGNATURES = {
     "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_bucketed": [_vp, _i, _i, _i, _vp, _vp, _vp],
+    "pf_fps_clustered": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_knn_patch": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
     "pf_xyz_count": [ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int)],
     "pf_xyz_read": [ctypes.c_char_p, _vp, _i64, _i],
@@ -65,6 +66,8 @@ for _name, _args in SIGNATURES.items():
     _fn.restype = ctypes.c_int
 lib.pf_fps_work_floats.argtypes = [_i, _i]
 lib.pf_fps_work_floats.restype = ctypes.c_longlong
+lib.pf_fps_clustered_work_floats.argtypes = [_i, _i]
+lib.pf_fps_clustered_work_floats.restype = ctypes.c_longlong
 lib.pf_model_bytes.argtypes = []
 lib.pf_model_bytes.restype = ctypes.c_int64
 lib.pf_upsample_workspace_bytes.argtypes = [_i, _i, _i]

@@ -222,7 +222,7 @@ CloudWork cloud_layout(int64_t B, int64_t N, int64_t R, int64_t npoint, int64_t 
     w.patches = take(Bp * k * 12), w.pcen = take(Bp * 12), w.prad = take(Bp * 4);
     w.net = take(pf_upsample_workspace_bytes((int)Bp, (int)k, (int)R));
     w.x = take(Bp * k * R * 12), w.cand = take(B * ncand * 12);
-    const int64_t fa = pf_fps_work_floats((int)B, (int)N), fb = pf_fps_work_floats((int)B, (int)ncand);
+    const int64_t fa = pf_fps_clustered_work_floats((int)B, (int)N), fb = pf_fps_clustered_work_floats((int)B, (int)ncand);
     w.fps = take((fa > fb ? fa : fb) * 4);
     w.sel = take(B * npoint * 4), w.pred = take(B * npoint * 12), w.d1 = take(B * npoint * 4), w.i1 = take(B * npoint * 4);
     w.total = o;
@@ -311,7 +311,9 @@ extern "C" int pf_upsample_clouds(const void* model, const float* clouds, int B,
     // normalise the clouds, pick the patch seeds, cut the patches (patch.py:59-64,96-125)
     if ((rc = pf_normalize_pc(clouds, B, N, F(w.pcn), F(w.gcen), F(w.grad), stream))) return rc;
     mk.mark("normalize_pc");
-    if ((rc = pf_fps(F(w.pcn), B, N, n_patch, I(w.seed_idx), N >= 4096 ? F(w.fps) : nullptr, stream))) return rc;
+    if ((rc = N >= 4096 ? pf_fps_clustered(F(w.pcn), B, N, n_patch, I(w.seed_idx), F(w.fps), stream)
+                        : pf_fps(F(w.pcn), B, N, n_patch, I(w.seed_idx), nullptr, stream)))
+        return rc;
     snprintf(tag, sizeof(tag), "fps_n%d", N);
     mk.mark(tag);
     if ((rc = pf_gather_points(F(w.pcn), I(w.seed_idx), B, N, n_patch, nullptr, nullptr, F(w.seeds), stream))) return rc;
@@ -327,7 +329,9 @@ extern "C" int pf_upsample_clouds(const void* model, const float* clouds, int B,
     if ((rc = pf_denorm_concat(F(w.x), F(w.patches), F(w.pcen), F(w.prad), Bp, k * R, k, F(w.cand), stream))) return rc;
     mk.mark("denorm_concat");
     // merge: farthest point sampling over all candidates of a cloud, back to the input frame (patch.py:67-70,142-158)
-    if ((rc = pf_fps(F(w.cand), B, ncand, npoint, I(w.sel), ncand >= 4096 ? F(w.fps) : nullptr, stream))) return rc;
+    if ((rc = ncand >= 4096 ? pf_fps_clustered(F(w.cand), B, ncand, npoint, I(w.sel), F(w.fps), stream)
+                            : pf_fps(F(w.cand), B, ncand, npoint, I(w.sel), nullptr, stream)))
+        return rc;
     snprintf(tag, sizeof(tag), "fps_n%d", ncand);
     mk.mark(tag);
     float* pred = num_outliers ? F(w.pred) : out;

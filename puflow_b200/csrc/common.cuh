@@ -14,6 +14,8 @@
 #define PF_ENOMEM 10002   // shared memory request over the 227 KB limit
 
 void pf_set_error(const char* fmt, ...);
+// fps_bucket.cu: pf_fps_bucketed with a device-side run condition (internal; pf_fps_clustered's fallback)
+int pf_fps_bucketed_if(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, const int* run_flag, void* stream);
 
 #define PF_CHECK_ARG(cond, ...)                     \
     do {                                            \

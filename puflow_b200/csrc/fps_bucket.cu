@@ -79,7 +79,8 @@ struct Slot {
 template <bool MD_SMEM, bool REGBOX>
 __global__ void __launch_bounds__(FT, 1)
     fps_bucket_kernel(const float* __restrict__ xyz, int n, int npoint, int32_t* __restrict__ out, float* work, int nb,
-                      int KB) {
+                      int KB, const int* __restrict__ run_flag) {
+    if (run_flag && *run_flag == 0) return;      // conditional launch (pf_fps_clustered's fallback): nothing to do
     extern __shared__ __align__(16) float sm[];
     const int npad = nb * 32;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -411,6 +412,11 @@ extern "C" long long pf_fps_work_floats(int B, int n) {
 }
 
 extern "C" int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream) {
+    return pf_fps_bucketed_if(xyz, B, n, npoint, idx, work, nullptr, stream);
+}
+
+// run_flag: NULL = always run; otherwise a device int, the kernel returns at once when it reads 0 (no host round trip)
+int pf_fps_bucketed_if(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, const int* run_flag, void* stream) {
     PF_CHECK_ARG(xyz && idx && work, "pf_fps_bucketed: null pointer (work must hold pf_fps_work_floats(B, n) floats)");
     PF_CHECK_ARG(B >= 0 && n > 0 && npoint > 0, "pf_fps_bucketed: bad sizes B=%d n=%d npoint=%d", B, n, npoint);
     if (B == 0) return 0;
@@ -421,15 +427,15 @@ extern "C" int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32
     if (s_md <= 227 * 1024) {
         if (KB <= 32 * BPL) {    // bucket metadata in registers (BPL buckets per lane)
             if (int rc = pf_smem_optin(fps_bucket_kernel<true, true>, s_md)) return rc;
-            fps_bucket_kernel<true, true><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB);
+            fps_bucket_kernel<true, true><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB, run_flag);
         } else {
             if (int rc = pf_smem_optin(fps_bucket_kernel<true, false>, s_md)) return rc;
-            fps_bucket_kernel<true, false><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB);
+            fps_bucket_kernel<true, false><<<B, FT, s_md, st>>>(xyz, n, npoint, idx, work, nb, KB, run_flag);
         }
     } else {
         PF_CHECK_ARG(s_nomd <= 227 * 1024, "pf_fps_bucketed: n=%d too large (bucket metadata exceeds shared memory)", n);
         if (int rc = pf_smem_optin(fps_bucket_kernel<false, false>, s_nomd)) return rc;
-        fps_bucket_kernel<false, false><<<B, FT, s_nomd, st>>>(xyz, n, npoint, idx, work, nb, KB);
+        fps_bucket_kernel<false, false><<<B, FT, s_nomd, st>>>(xyz, n, npoint, idx, work, nb, KB, run_flag);
     }
     return pf_launch_status("fps_bucket_kernel");
 }

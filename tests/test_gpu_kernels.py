@@ -653,6 +653,36 @@ def test_fps_bucketed_bit_exact(ops, dev, B, n, npoint, kind):
     assert np.array_equal(out, ref)
     if n <= 102400:
         assert np.array_equal(ops.fps(x, npoint, mode="brute").cpu().numpy(), ref)
+    assert np.array_equal(ops.fps(x, npoint, mode="cluster").cpu().numpy(), ref)      # buckets spread over a CTA cluster
+
+
+@pytest.mark.parametrize("B,n,npoint,kind", [(1, 99840, 2500, "surface"), (8, 99840, 300, "surface"), (1, 40960, 8216, "surface"),
+                                             (3, 20000, 900, "uniform"), (1, 131000, 300, "uniform"), (2, 9000, 9000, "dup"),
+                                             (2, 8000, 500, "lattice"), (1, 30000, 200, "blob"), (1, 6000, 100, "same")])
+def test_fps_clustered_bit_exact(ops, dev, B, n, npoint, kind):
+    """pf_fps_clustered (one thread-block cluster per cloud: DSMEM candidate exchange, remote mbarrier arrives) against the
+    brute-force definition: the config-3 merge size, 8 clouds at once, a full 8,216-round run, ties (lattice, triplicated
+    points), and degenerate clouds whose cells overflow a CTA's capacity ("blob": 90 % of the points in one grid cell,
+    "same": all points identical) -- these take the in-stream fallback to the single-CTA kernel."""
+    rng = np.random.default_rng(n + npoint)
+    if kind == "uniform":
+        p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    elif kind == "surface":
+        p = np.stack([synth.make_cloud(n, 21 + b, synth.SHAPES[b % 3]) for b in range(B)])
+    elif kind == "lattice":
+        p = np.stack([synth.make_cloud(n, 5 + b, "lattice") for b in range(B)])
+    elif kind == "dup":
+        base = rng.uniform(-1, 1, (B, n // 3, 3)).astype(np.float32)
+        p = np.concatenate([base, base, base], 1)[:, rng.permutation(n // 3 * 3)]
+        npoint = min(npoint, p.shape[1])
+    elif kind == "blob":
+        p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+        p[:, : n * 9 // 10] = p[:, : n * 9 // 10] * 1e-3 + 0.5
+    else:
+        p = np.full((B, n, 3), 0.25, np.float32)
+    ref = po.fps(p, npoint)
+    x = torch.from_numpy(np.ascontiguousarray(p)).to(dev)
+    assert np.array_equal(ops.fps(x, npoint, mode="cluster").cpu().numpy(), ref)
 
 
 @pytest.mark.parametrize("B,nq,np_,k", [(2, 32, 2048, 256), (1, 78, 5000, 256), (2, 5, 300, 256), (1, 3, 1000, 1000)])

@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
     from puflow_b200 import _native
-    assert set(_native.SIGNATURES) | {"pf_last_error", "pf_fps_work_floats", "pf_model_bytes", "pf_upsample_clouds_workspace_bytes",
+    assert set(_native.SIGNATURES) | {"pf_last_error", "pf_fps_work_floats", "pf_fps_clustered_work_floats", "pf_model_bytes", "pf_upsample_clouds_workspace_bytes",
                                       "pf_upsample_workspace_bytes"} == declared
     assert lib.pf_abi_version() == _native.PF_ABI_VERSION
 
