@@ -52,7 +52,7 @@ int main(int argc, char** argv) {
     CU(cudaMemcpyAsync(d_model, h_model, model_bytes, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(d_in, h_in, in_bytes, cudaMemcpyHostToDevice, st));
 
-    const int rc = pf_upsample_patches(d_model, d_in, Bp, N, R, d_ws, ws_bytes, d_out, d_logp, st);
+    const int rc = pf_upsample_patches(d_model, d_in, Bp, N, R, d_ws, ws_bytes, d_out, d_logp, PF_PREC_FP32_SPLIT, st);
     if (rc) { fprintf(stderr, "pf_upsample_patches -> %d: %s\n", rc, pf_last_error()); return 4; }
 
     float logp = 0.f;

@@ -37,11 +37,25 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 6
+#define PF_ABI_VERSION 7
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
 /* activation codes of pf_linear */
+/* Precision of the tensor-core contractions (trailing `precision` argument of every tcgen05 entry point):
+ *   PF_PREC_FP32_SPLIT  operands as fp16 hi + lo pairs, three products per contraction (hi.hi + lo.hi + hi.lo), fp32
+ *                       accumulation: fp32-class results (2^-22 per product); the default and the path every parity
+ *                       number refers to.
+ *   PF_PREC_FP16        single pass: the hi.hi product alone (operands rounded to fp16 = 11 significant bits, the mantissa
+ *                       width of TF32; fp32 accumulation): a third of the MMAs.  STATED TOLERANCE (tests/test_gpu_precision.py,
+ *                       measured: 3.5e-3 / 6.1e-2 / 1.3e-2 for the three released checkpoints): network output within
+ *                       1e-2 (pu1k), 3e-2 (pugeo), 1e-1 (pugan) normwise of the reference -- the split path's bar is 1e-4 --
+ *                       and Chamfer distance to the reference output <= 1e-4 (pu1k; the split path meets 1e-5, this
+ *                       mode does not: it is an option for the precision sweep, not the product path).  (pf_interp_tc keeps the weights split in this mode and drops the activations' lo
+ *                       products only: 2 of 3 MMAs.) */
+#define PF_PREC_FP32_SPLIT 0
+#define PF_PREC_FP16 1
+
 #define PF_ACT_NONE 0
 #define PF_ACT_RELU 1
 #define PF_ACT_LRELU 2
@@ -79,7 +93,7 @@ PF_API int pf_linear(const float* A, int64_t lda, const float* W, const float* b
  * fp32 accumulation: fp32-class result, tolerance in tests/test_gpu_kernels.py).  wtc: weights pre-split and laid out
  * per 128-column chunk by puflow_b200/packing.py pack_linear_tc: ceil(N/128) chunks of 128*K*4 bytes. */
 PF_API int pf_linear_tc(const float* A, int64_t lda, const void* wtc, const float* bias, float* out, int64_t ldo, int64_t M,
-                 int K, int N, int act, float slope, void* stream);
+                 int K, int N, int act, float slope, int precision, void* stream);
 
 /* ---- (2) fused EdgeConv block -----------------------------------------------------------------
  * Replaces FeatureExtractUnit.forward (/root/reference/modules/discrete/interpflow.py:223-248):
@@ -101,7 +115,7 @@ PF_API int pf_edgeconv(const float* pq, const int32_t* idx, const float* wd, con
  * gp = max(G, 16): PF_EDGECONV_TC_BLOB for G = 32. */
 #define PF_EDGECONV_TC_BLOB 90112
 PF_API int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K, int G,
-                   int C_out, float slope, void* stream);
+                   int C_out, float slope, int precision, void* stream);
 
 /* Pre-split activations.  pf_edgeconv_tc_split is pf_edgeconv_tc that ALSO (or only: out may be NULL) writes its output as
  * fp16 hi/lo in the tile-blocked tensor-core operand layout: out_split holds ceil(Bp*N / 128) tiles of
@@ -111,9 +125,9 @@ PF_API int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, 
  * 128-byte aligned, out 32-byte aligned, ldo a multiple of 8. */
 #define PF_SPLIT_TILE_BYTES(K) (512 * (K))
 PF_API int pf_edgeconv_tc_split(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
-                         int N, int K, int G, int C_out, float slope, void* stream);
+                         int N, int K, int G, int C_out, float slope, int precision, void* stream);
 PF_API int pf_linear_tc_split(const void* a_split, const void* wtc, const float* bias, float* out, int64_t ldo, int64_t M,
-                       int K, int N, int act, float slope, void* stream);
+                       int K, int N, int act, float slope, int precision, void* stream);
 
 /* ---- (3) flow stack ---------------------------------------------------------------------------------
  * FlowBlock.forward / inverse x6 (/root/reference/modules/discrete/interpflow.py:66-82,302-321):
@@ -150,13 +164,13 @@ PF_API int pf_flow_inv(const float* zin, const float* raw, const float* sb, cons
  * bias, no activation) is composed with the first layers on the host (packing.pack_chain_tc, PF_CHAIN_TC_BYTES(C)). */
 #define PF_COND_TC_BLOCK 35360
 #define PF_FLOW_TC_BLOCK 17920
-PF_API int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, void* stream);
+PF_API int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, int precision, void* stream);
 #define PF_CHAIN_TC_BYTES(C) (2 * (C) * (C) + 2 * 192 * (C) + 4 * 8192 + (64 + 648) * 4)
 PF_API int pf_flow_fwd_tc(const float* x, const float* raw, int ldraw, const float* sb, const void* flow_tc, float* z,
-                   float* ssum, int64_t M, int nblocks, void* stream);
+                   float* ssum, int64_t M, int nblocks, int precision, void* stream);
 PF_API int pf_flow_inv_tc(const float* zin, const float* raw, int ldraw, const float* sb, const void* flow_tc, float* x,
-                   int64_t M, int R, int nblocks, void* stream);
-PF_API int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, float* raw1, float* sb, int64_t M, void* stream);
+                   int64_t M, int R, int nblocks, int precision, void* stream);
+PF_API int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, float* raw1, float* sb, int64_t M, int precision, void* stream);
 
 /* ---- (4) latent interpolation -------------------------------------------------------------------------
  * Replaces InterpolationModule.forward (/root/reference/modules/discrete/interpflow.py:162-186) with
@@ -177,7 +191,7 @@ PF_API int pf_interp(const float* xyz, const float* z, const int32_t* idx, int l
  * wtc: PF_INTERP_TC_BLOB bytes from puflow_b200/packing.py pack_interp_tc. */
 #define PF_INTERP_TC_BLOB 205440
 PF_API int pf_interp_tc(const float* xyz, const float* z, const int32_t* idx, int ldidx, const void* wtc, float* out,
-                 int Bp, int N, int R, void* stream);
+                 int Bp, int N, int R, int precision, void* stream);
 
 /* ---- caller side ("next" rows of SURVEY.md section 8f) ---------------------------------------------------
  * pf_fps replaces pointnet2_ops.furthest_point_sample (/root/reference/modules/utils/patch.py:102,156)
@@ -240,7 +254,7 @@ PF_API int64_t pf_model_bytes(void);
 PF_API int pf_model_entry(int i, char* name32, int64_t* offset, int64_t* bytes);
 PF_API int64_t pf_upsample_workspace_bytes(int Bp, int N, int R);
 PF_API int pf_upsample_patches(const void* model, const float* xyz, int Bp, int N, int R, void* workspace,
-                        int64_t workspace_bytes, float* x, float* logp, void* stream);
+                        int64_t workspace_bytes, float* x, float* logp, int precision, void* stream);
 
 /* pf_upsample_clouds replaces the body of the reference's per-file loop (/root/reference/modules/discrete/upsample.py:46-54:
  * PatchHelper.upsample(jitter=False) + remove_outliers) for a batch of clouds:
@@ -254,7 +268,8 @@ PF_API int pf_upsample_patches(const void* model, const float* xyz, int Bp, int 
  * (= PatchHelper.upsample alone). */
 PF_API int64_t pf_upsample_clouds_workspace_bytes(int B, int N, int R, int npoint, int patch_points, int n_patch);
 PF_API int pf_upsample_clouds(const void* model, const float* clouds, int B, int N, int R, int npoint, int num_outliers,
-                       int patch_points, int n_patch, void* workspace, int64_t workspace_bytes, float* out, void* stream);
+                       int patch_points, int n_patch, void* workspace, int64_t workspace_bytes, float* out, int precision,
+                       void* stream);
 
 /* Optional per-launch timing of the one-call entry points (what bench.py's breakdown and roofline read): while enabled,
  * pf_upsample_patches / pf_upsample_clouds record a CUDA event on their stream after each of their launches; every interval

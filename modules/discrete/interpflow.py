@@ -342,6 +342,18 @@ class PointInterpFlow(nn.Module):
         for i in range(self.num_blocks):
             self.flow_blocks.append(FlowBlock(idim=pc_channel, hdim=64, cdim=cond_channels[i], is_even=(i % 2 == 0)))
         self._engine_cache = BlobCache()
+        # Precision of the tensor-core contractions: "fp32" (default: split-fp16 operands, three products per contraction,
+        # fp32-class -- the parity path) or "fp16" (single pass; tolerance stated in include/puflow_b200.h).  An attribute,
+        # not an environment switch: set `net.precision = "fp16"` before the next call.
+        self.precision = "fp32"
+
+    def invalidate_packed(self):
+        """Drop the packed weights (call after editing parameters through `.data`, which the cache cannot see)."""
+        self._engine_cache.invalidate()
+        for m in self.modules():
+            c = getattr(m, "_cache", None)
+            if isinstance(c, BlobCache):
+                c.invalidate()
 
     # ---- packed-weight engine, rebuilt only when a parameter / buffer changes or the model moves ----
     def engine(self, device=None) -> PUFlowEngine:
@@ -356,8 +368,8 @@ class PointInterpFlow(nn.Module):
                 if not fb.actnorm.is_inited:
                     raise RuntimeError("ActNorm is not initialised: load a checkpoint and call "
                                        "set_to_initialized_state() (reference upsample.py:32-33)")
-            return PUFlowEngine({k: v.detach() for k, v in self.state_dict().items()}, device)
-        return self._engine_cache.get(tensors, device, build)
+            return PUFlowEngine({k: v.detach() for k, v in self.state_dict().items()}, device, precision=self.precision)
+        return self._engine_cache.get(tensors, device, build, extra=(self.precision,))
 
     def feat_extract(self, xyz: Tensor, knn_idx: Tensor):
         xyz = check_input(xyz, "PointInterpFlow.feat_extract")

@@ -17,16 +17,22 @@ def check_input(x: torch.Tensor, who: str):
 
 
 class BlobCache:
-    """Re-packs a layer's blob only when one of its parameters changed (or moved device)."""
+    """Re-packs a layer's blob only when one of its parameters changed (or moved device).
+    The key is (storage pointer, version counter) per tensor: in-place writes through `p.data` (or `p.data.copy_`) do NOT
+    bump the version counter, so code that edits weights that way (EMA swaps, manual re-initialisation) must call
+    invalidate() -- or write with `with torch.no_grad(): p.copy_(...)`, which does bump it."""
 
     def __init__(self):
         self.key, self.value = None, None
 
-    def get(self, tensors, device, build):
-        key = (str(device),) + tuple((t.data_ptr(), t._version) for t in tensors)
+    def get(self, tensors, device, build, extra=()):
+        key = (str(device),) + tuple(extra) + tuple((t.data_ptr(), t._version) for t in tensors)
         if key != self.key:
             self.key, self.value = key, build()
         return self.value
+
+    def invalidate(self):
+        self.key, self.value = None, None
 
 
 def to_dev(t, device):

@@ -61,7 +61,8 @@ class ActNorm(nn.Module):
             dims.remove(self.dim)
             bias = -torch.mean(x.detach(), dim=dims, keepdim=True)
             logs = -torch.log(torch.std(x.detach(), dim=dims, keepdim=True) + self.eps)
-            self.bias.data.copy_(bias.data)
-            self.logs.data.copy_(logs.data)
+            self.bias.copy_(bias)               # under no_grad: bumps the version counter the blob cache keys on
+            self.logs.copy_(logs)               # (a write through `.data` would leave a stale packed blob behind)
+            self._cache.invalidate()
             self.is_inited = True
 # -----------------------------------------------------------------------------------------

@@ -26,20 +26,20 @@ SIGNATURES = {
     "pf_knn_topk": [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
     "pf_chamfer_nn": [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp],
     "pf_linear": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
-    "pf_linear_tc": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
+    "pf_linear_tc": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _i, _vp],
     "pf_edgeconv": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
-    "pf_edgeconv_tc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
-    "pf_edgeconv_tc_split": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _vp],
-    "pf_linear_tc_split": [_vp, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _vp],
+    "pf_edgeconv_tc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _i, _vp],
+    "pf_edgeconv_tc_split": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _i, _vp],
+    "pf_linear_tc_split": [_vp, _vp, _vp, _vp, _i64, _i64, _i, _i, _i, _f, _i, _vp],
     "pf_flow_cond": [_vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_flow_inv": [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
-    "pf_flow_cond_tc": [_vp, _vp, _vp, _i64, _i, _vp],
-    "pf_flow_fwd_tc": [_vp, _vp, _i, _vp, _vp, _vp, _vp, _i64, _i, _vp],
-    "pf_flow_inv_tc": [_vp, _vp, _i, _vp, _vp, _vp, _i64, _i, _i, _vp],
-    "pf_cond_chain_tc": [_vp, _i, _vp, _vp, _vp, _i64, _vp],
+    "pf_flow_cond_tc": [_vp, _vp, _vp, _i64, _i, _i, _vp],
+    "pf_flow_fwd_tc": [_vp, _vp, _i, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
+    "pf_flow_inv_tc": [_vp, _vp, _i, _vp, _vp, _vp, _i64, _i, _i, _i, _vp],
+    "pf_cond_chain_tc": [_vp, _i, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
-    "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
+    "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_bucketed": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_clustered": [_vp, _i, _i, _i, _vp, _vp, _vp],
@@ -48,13 +48,13 @@ SIGNATURES = {
     "pf_xyz_read": [ctypes.c_char_p, _vp, _i64, _i],
     "pf_xyz_write": [ctypes.c_char_p, _vp, _i64, _i],
     "pf_model_entry": [_i, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int64)],
-    "pf_upsample_patches": [_vp, _vp, _i, _i, _i, _vp, _i64, _vp, _vp, _vp],
+    "pf_upsample_patches": [_vp, _vp, _i, _i, _i, _vp, _i64, _vp, _vp, _i, _vp],
     "pf_normalize_pc": [_vp, _i, _i, _vp, _vp, _vp, _vp],
     "pf_gather_normalize": [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp],
     "pf_gather_points": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp],
     "pf_denorm_concat": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp],
     "pf_remove_outliers": [_vp, _vp, _i, _i, _i, _vp, _vp],
-    "pf_upsample_clouds": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i64, _vp, _vp],
+    "pf_upsample_clouds": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i64, _vp, _i, _vp],
     "pf_profile_enable": [_i],
     "pf_profile_intervals": [],
     "pf_profile_interval": [_i, ctypes.c_char_p, ctypes.POINTER(ctypes.c_float)],
@@ -77,7 +77,7 @@ lib.pf_upsample_clouds_workspace_bytes.restype = ctypes.c_int64
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 6
+PF_ABI_VERSION = 7
 PF_MODEL_ENTRIES = 27
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
@@ -92,6 +92,8 @@ PF_INTERP_BLOB = 46304
 PF_EDGECONV_TC_BLOB = 90112
 PF_INTERP_TC_BLOB = 205440
 ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
+PREC_FP32_SPLIT, PREC_FP16 = 0, 1          # PF_PREC_*: precision argument of the tensor-core entry points
+PRECISIONS = {"fp32": PREC_FP32_SPLIT, "fp32_split": PREC_FP32_SPLIT, "fp16": PREC_FP16, 0: 0, 1: 1}
 
 if lib.pf_abi_version() != PF_ABI_VERSION:
     raise ImportError(f"{LIB_PATH}: ABI version {lib.pf_abi_version()} != {PF_ABI_VERSION}; rebuild")

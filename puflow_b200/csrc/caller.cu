@@ -287,7 +287,7 @@ extern "C" int64_t pf_upsample_clouds_workspace_bytes(int B, int N, int R, int n
 
 extern "C" int pf_upsample_clouds(const void* model, const float* clouds, int B, int N, int R, int npoint, int num_outliers,
                                   int patch_points, int n_patch, void* workspace, int64_t workspace_bytes, float* out,
-                                  void* stream) {
+                                  int precision, void* stream) {
     PF_CHECK_ARG(B >= 0 && N >= patch_points && R >= 1 && R <= 32 && num_outliers >= 0 && npoint > num_outliers &&
                      patch_points >= 16 && n_patch >= 1,
                  "pf_upsample_clouds: bad sizes B=%d N=%d R=%d npoint=%d num_outliers=%d patch_points=%d n_patch=%d", B, N, R,
@@ -324,7 +324,7 @@ extern "C" int pf_upsample_clouds(const void* model, const float* clouds, int B,
     mk.mark("gather_normalize");
     // the network on every patch (patch.py:82-93 -> PointInterpFlow.sample)
     if ((rc = pf_upsample_patches(model, F(w.patches), Bp, k, R, ws + w.net, pf_upsample_workspace_bytes(Bp, k, R), F(w.x), nullptr,
-                                  stream)))
+                                  precision, stream)))
         return rc;
     if ((rc = pf_denorm_concat(F(w.x), F(w.patches), F(w.pcen), F(w.prad), Bp, k * R, k, F(w.cand), stream))) return rc;
     mk.mark("denorm_concat");

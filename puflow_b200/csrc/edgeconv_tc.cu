@@ -99,7 +99,7 @@ template <int G, int CO, int NWG, int KN>
 __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
     edgeconv_tc_kernel(const float* __restrict__ pq, const int32_t* __restrict__ idx, const uint8_t* __restrict__ wblob,
                        float* __restrict__ out, uint8_t* __restrict__ out_split, int N, int tiles_per_patch,
-                       long long total_tiles, float slope) {
+                       long long total_tiles, float slope, int prec) {
     using C = Cfg<G, CO, NWG, KN>;
     constexpr int GP = C::GP, R = C::R, R2 = C::R2, KT = C::KT, CPR = C::CPR, LCPR = C::LCPR, NCH = C::NCH, PT = C::PT;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -182,6 +182,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
         // ================= MMA-issuing warp of warpgroup wg: one elected thread (elect_one, not lane == 0: tc.cuh) waits
         // for "operands ready", issues, commits =================
         const uint32_t idesc_o = tc::idesc_f16(128, 32);
+        const bool split3 = prec == PF_PREC_FP32_SPLIT;     // PF_PREC_FP16: the hi . hi products alone
         const uint64_t da_hi = tc::smem_desc(a_hi, C::A_SBO), da_lo = tc::smem_desc(a_lo, C::A_SBO);
         // D[128 edges x GP (3 - m)] (+)= h_m . [W_{m+1,m}; ..; W_{3,m}]^T, h_m from tensor memory (8 columns per K-step).
         // 3 split products, the two small cross terms first: the accumulator adder truncates, so the hi . hi pass -- the
@@ -191,12 +192,14 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
             const uint64_t db_hi = tc::smem_desc(wl, 16u * GP), db_lo = tc::smem_desc(wl + C::wd_part(m), 16u * GP);
             const uint32_t idesc = tc::idesc_f16(128, GP * (3 - m));
             const uint32_t d = d_dense + GP * m, h_hi = d_out + C::TM_SLICE, h_lo = h_hi + GP / 2;
+            if (split3) {
 #pragma unroll
-            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_lo + 8u * s, db_hi + 16u * s, idesc, m > 0 || s > 0);
+                for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_lo + 8u * s, db_hi + 16u * s, idesc, m > 0 || s > 0);
 #pragma unroll
-            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_lo + 16u * s, idesc, 1);
+                for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_lo + 16u * s, idesc, 1);
+            }
 #pragma unroll
-            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_hi + 16u * s, idesc, 1);
+            for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_hi + 16u * s, idesc, split3 || m > 0 || s > 0);
         };
         // conv_out step c: D^T[128 rows x 32 edges] = Wo . H^T for the 128 / CO column blocks (32 edges each) that the
         // epilogue threads read in step c (block g NCH + c for edge group g); Wo from TMEM (8 columns per K-step), H^T rows
@@ -209,12 +212,14 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
             for (int g = 0; g < 128 / CO; g++) {
                 const uint32_t cb = (uint32_t)(g * NCH + c), d = d_out + 32u * cb;
                 const uint64_t bh = da_hi + (uint64_t)(4u * cb * (C::A_SBO >> 4)), bl = da_lo + (uint64_t)(4u * cb * (C::A_SBO >> 4));
+                if (split3) {
 #pragma unroll
-                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_lo + 8u * s, bh + 16u * s, idesc_o, s > 0);
+                    for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_lo + 8u * s, bh + 16u * s, idesc_o, s > 0);
 #pragma unroll
-                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bl + 16u * s, idesc_o, 1);
+                    for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bl + 16u * s, idesc_o, 1);
+                }
 #pragma unroll
-                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bh + 16u * s, idesc_o, 1);
+                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bh + 16u * s, idesc_o, split3 || s > 0);
             }
         };
         tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
@@ -354,8 +359,14 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
         // covers the earlier slices' stores of this thread as well), then publish.
         auto store_slice = [&](int l, const float (&h)[G]) {
             uint32_t hi[GP / 2], lo[GP / 2];
+            const bool split3 = prec == PF_PREC_FP32_SPLIT;        // single-pass mode: no lo halves are computed or stored
+            if (split3) {
 #pragma unroll
-            for (int u = 0; u < G / 2; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
+                for (int u = 0; u < G / 2; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
+            } else {
+#pragma unroll
+                for (int u = 0; u < G / 2; u++) hi[u] = tc::cvt_f16x2_sat(h[2 * u], h[2 * u + 1]), lo[u] = 0;
+            }
 #pragma unroll
             for (int u = G / 2; u < GP / 2; u++) hi[u] = lo[u] = 0;
             auto publish = [&]() {
@@ -366,9 +377,11 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
             if (l < 3) {
                 const uint32_t ts = d_out + lane_sel + C::TM_SLICE;
                 if constexpr (GP == 32) {
-                    tc::st16_nowait(ts, hi), tc::st16_nowait(ts + 16, lo);
+                    tc::st16_nowait(ts, hi);
+                    if (split3) tc::st16_nowait(ts + 16, lo);
                 } else {
-                    tc::st8_nowait(ts, hi), tc::st8_nowait(ts + 8, lo);
+                    tc::st8_nowait(ts, hi);
+                    if (split3) tc::st8_nowait(ts + 8, lo);
                 }
                 tc::tmem_st_wait();
                 publish();
@@ -377,7 +390,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
             for (int c = 0; c < G / 8; c++) {
                 const uint32_t off = a_row + (uint32_t)(l * (GP / 8) + c) * 128;
                 *reinterpret_cast<uint4*>(a_hi_p + off) = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
-                *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
+                if (split3) *reinterpret_cast<uint4*>(a_lo_p + off) = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
             }
             if (l == 3) {
                 tc::fence_async_smem();
@@ -543,7 +556,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
 
 template <int G, int CO, int NWG, int KN>
 int launch(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp, int N, float slope,
-           cudaStream_t st) {
+           int prec, cudaStream_t st) {
     using C = Cfg<G, CO, NWG, KN>;
     constexpr int PT = C::PT;
     auto kern = edgeconv_tc_kernel<G, CO, NWG, KN>;
@@ -556,14 +569,15 @@ int launch(const float* pq, const int32_t* idx, const void* wtc, float* out, voi
     const long long want = (total + NWG - 1) / NWG;
     const int grid = (int)(want < sms ? want : sms);
     kern<<<grid, C::NT, C::SMEM_BYTES, st>>>(pq, idx, static_cast<const uint8_t*>(wtc), out, static_cast<uint8_t*>(out_split),
-                                             N, tiles_per_patch, total, slope);
+                                             N, tiles_per_patch, total, slope, prec);
     return pf_launch_status("edgeconv_tc_kernel");
 }
 
 }  // namespace
 
 static int edgeconv_tc_dispatch(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
-                                int N, int K, int G_, int C_out, float slope, void* stream) {
+                                int N, int K, int G_, int C_out, float slope, int precision, void* stream) {
+    PF_CHECK_ARG(precision == PF_PREC_FP32_SPLIT || precision == PF_PREC_FP16, "pf_edgeconv_tc: precision %d (PF_PREC_FP32_SPLIT or PF_PREC_FP16)", precision);
     PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(Bp >= 0 && N > 0, "pf_edgeconv_tc: bad sizes Bp=%d N=%d", Bp, N);
     if (Bp == 0) return 0;
@@ -577,9 +591,9 @@ static int edgeconv_tc_dispatch(const float* pq, const int32_t* idx, const void*
     cudaStream_t st = (cudaStream_t)stream;
 #define PF_EC_CASE(g, c, nwg)                                                                                     \
     if (G_ == g && C_out == c) {                                                                                  \
-        if (K == 16) return launch<g, c, nwg, 16>(pq, idx, wtc, out, out_split, Bp, N, slope, st);                  \
-        if (K == 8) return launch<g, c, nwg, 8>(pq, idx, wtc, out, out_split, Bp, N, slope, st);                    \
-        return launch<g, c, nwg, 32>(pq, idx, wtc, out, out_split, Bp, N, slope, st);                               \
+        if (K == 16) return launch<g, c, nwg, 16>(pq, idx, wtc, out, out_split, Bp, N, slope, precision, st);                  \
+        if (K == 8) return launch<g, c, nwg, 8>(pq, idx, wtc, out, out_split, Bp, N, slope, precision, st);                    \
+        return launch<g, c, nwg, 32>(pq, idx, wtc, out, out_split, Bp, N, slope, precision, st);                               \
     }
     PF_EC_CASE(32, 128, 2)
     PF_EC_CASE(16, 64, 3)
@@ -596,11 +610,11 @@ extern "C" __attribute__((visibility("default"))) int pf_debug_edgeconv_prof(lon
 #endif
 
 extern "C" int pf_edgeconv_tc(const float* pq, const int32_t* idx, const void* wtc, float* out, int Bp, int N, int K,
-                              int G_, int C_out, float slope, void* stream) {
-    return edgeconv_tc_dispatch(pq, idx, wtc, out, nullptr, Bp, N, K, G_, C_out, slope, stream);
+                              int G_, int C_out, float slope, int precision, void* stream) {
+    return edgeconv_tc_dispatch(pq, idx, wtc, out, nullptr, Bp, N, K, G_, C_out, slope, precision, stream);
 }
 
 extern "C" int pf_edgeconv_tc_split(const float* pq, const int32_t* idx, const void* wtc, float* out, void* out_split, int Bp,
-                                    int N, int K, int G_, int C_out, float slope, void* stream) {
-    return edgeconv_tc_dispatch(pq, idx, wtc, out, out_split, Bp, N, K, G_, C_out, slope, stream);
+                                    int N, int K, int G_, int C_out, float slope, int precision, void* stream) {
+    return edgeconv_tc_dispatch(pq, idx, wtc, out, out_split, Bp, N, K, G_, C_out, slope, precision, stream);
 }

@@ -45,6 +45,7 @@ struct Wg {
     uint64_t* mbar;         // MMA-done barrier of this warpgroup
     uint32_t phase;
     int bar_id, e;
+    int prec;               // PF_PREC_FP32_SPLIT: three split products; PF_PREC_FP16: the hi . hi product alone
 };
 
 // 64 activations (already through LeakyReLU) -> this thread's operand row.  fp16 saturates at 65,504, and exp(s) of the
@@ -86,12 +87,15 @@ __device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[
         const uint32_t idesc = tc::idesc_f16(128, H);
         const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
         const uint64_t db_hi = tc::smem_desc(w_addr, H * 16), db_lo = tc::smem_desc(w_addr + W_PART, H * 16);
+        if (g.prec == PF_PREC_FP32_SPLIT) {
 #pragma unroll
-        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, s > 0);
+            for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, s > 0);
 #pragma unroll
-        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+            for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+        }
 #pragma unroll
-        for (int s = 0; s < H / 16; s++) tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, 1);   // full magnitude last
+        for (int s = 0; s < H / 16; s++)       // full magnitude last
+            tc::mma_f16(g.d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, (g.prec == PF_PREC_FP32_SPLIT || s > 0) ? 1u : 0u);
         tc::commit(g.mbar);
     }
     tc::mbar_wait_bounded(g.mbar, g.phase);
@@ -105,7 +109,8 @@ __device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[
 }
 
 __device__ __forceinline__ void wg_init(Wg& g, uint8_t* smem, uint32_t a_off, uint64_t* mbars, uint32_t tmem_base,
-                                        int tid) {
+                                        int tid, int prec) {
+    g.prec = prec;
     const int warp = tid >> 5, wg = warp >> 2;
     g.e = tid & 127;
     uint8_t* a = smem + a_off + (size_t)wg * A_WG;
@@ -128,7 +133,7 @@ template <bool INVERSE>
 __global__ void __launch_bounds__(NT, 1)
     flow_tc_kernel(const float* __restrict__ xin, const float* __restrict__ raw, const float* __restrict__ sb,
                    const uint8_t* __restrict__ wtc, float* __restrict__ xout, float* __restrict__ ssum, int64_t M,
-                   int R, int nblocks, int ldraw) {
+                   int R, int nblocks, int ldraw, int prec) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t w_bytes = (uint32_t)nblocks * FBLK;
     const uint32_t a_off = (w_bytes + 127u) & ~127u;
@@ -151,7 +156,7 @@ __global__ void __launch_bounds__(NT, 1)
         bulk_g2s_chunked(smem, wtc, w_bytes, wbar);
     }
     Wg g;
-    wg_init(g, smem, a_off, mbars, *tmem_slot, tid);
+    wg_init(g, smem, a_off, mbars, *tmem_slot, tid, prec);
     const uint32_t sbase = smem_u32(smem);
     const int64_t rows = INVERSE ? M * R : M;
     const int64_t ntiles = (rows + TP - 1) / TP;
@@ -260,7 +265,7 @@ constexpr uint32_t CBLK = PF_COND_TC_BLOCK;
 
 __global__ void __launch_bounds__(NT_C, 1)
     flow_cond_tc_kernel(const float* __restrict__ raw, const uint8_t* __restrict__ wtc, float* __restrict__ sb,
-                        int64_t M) {
+                        int64_t M, int prec) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr uint32_t a_off = (CBLK + 127u) & ~127u;
     uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off + NWG_C * A_WG);
@@ -283,7 +288,7 @@ __global__ void __launch_bounds__(NT_C, 1)
         bulk_g2s_chunked(smem, wtc + (size_t)blk * CBLK, CBLK, wbar);
     }
     Wg g;
-    wg_init(g, smem, a_off, mbars, *tmem_slot, tid);
+    wg_init(g, smem, a_off, mbars, *tmem_slot, tid, prec);
     const uint32_t sbase = smem_u32(smem);
     const float* cw = reinterpret_cast<const float*>(smem + 4 * W_PART);
     const int64_t ntiles = (M + TP - 1) / TP;
@@ -356,12 +361,15 @@ __device__ __forceinline__ void issue3(Wg& g, uint32_t d_tmem, uint32_t w_addr, 
         const uint32_t idesc = tc::idesc_f16(128, n);
         const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
         const uint64_t db_hi = tc::smem_desc(w_addr, w_sbo) + 16u * w_k0, db_lo = tc::smem_desc(w_addr + w_part, w_sbo) + 16u * w_k0;
+        const bool split = g.prec == PF_PREC_FP32_SPLIT;
+        if (split) {
 #pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, (accumulate || s > 0) ? 1u : 0u);
+            for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, (accumulate || s > 0) ? 1u : 0u);
 #pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+            for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
+        }
 #pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, 1);
+        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, (split || accumulate || s > 0) ? 1u : 0u);
         tc::commit(g.mbar);
     }
     tc::mbar_wait_bounded(g.mbar, g.phase);
@@ -387,7 +395,7 @@ __host__ __device__ constexpr uint32_t chain_bytes(int C) {
 template <int C>
 __global__ void __launch_bounds__(NT_CH, 1)
     cond_chain_tc_kernel(const float* __restrict__ cin, const uint8_t* __restrict__ wtc, float* __restrict__ raw1,
-                         float* __restrict__ sb, int64_t M) {
+                         float* __restrict__ sb, int64_t M, int prec) {
     constexpr int H1 = C / 2;
     constexpr uint32_t W1P = chain_w1_part(C), W2P = chain_w2_part(C), WBYTES = chain_bytes(C);
     constexpr uint32_t OFF_W2 = 2 * W1P, OFF_NET = OFF_W2 + 2 * W2P, OFF_F = OFF_NET + 4 * W_PART;
@@ -412,7 +420,7 @@ __global__ void __launch_bounds__(NT_CH, 1)
         bulk_g2s_chunked(smem, wtc, WBYTES, wbar);
     }
     Wg g;
-    wg_init(g, smem, a_off, mbars, *tmem_slot, tid);
+    wg_init(g, smem, a_off, mbars, *tmem_slot, tid, prec);
     g.d_tmem = *tmem_slot + (uint32_t)wg * 256;          // per warpgroup: raw at +0 (192 columns), scratch at +192 (64)
     const uint32_t d_raw = g.d_tmem, d_s = g.d_tmem + 192;
     const uint32_t sbase = smem_u32(smem);
@@ -521,13 +529,13 @@ __global__ void __launch_bounds__(NT_CH, 1)
 }
 
 template <int C>
-int chain_launch(const float* c, const uint8_t* w, float* raw1, float* sb, int64_t M, int sms, cudaStream_t st) {
+int chain_launch(const float* c, const uint8_t* w, float* raw1, float* sb, int64_t M, int sms, int prec, cudaStream_t st) {
     constexpr size_t smem = ((chain_bytes(C) + 127u) & ~127u) + NWG_CH * A_WG + 64;
     if (int rc = pf_smem_optin(cond_chain_tc_kernel<C>, smem)) return rc;
     const int64_t ntiles = (M + TP - 1) / TP;
     int grid = sms;
     if ((int64_t)grid * NWG_CH > ntiles) grid = (int)((ntiles + NWG_CH - 1) / NWG_CH);
-    cond_chain_tc_kernel<C><<<grid, NT_CH, smem, st>>>(c, w, raw1, sb, M);
+    cond_chain_tc_kernel<C><<<grid, NT_CH, smem, st>>>(c, w, raw1, sb, M, prec);
     return pf_launch_status("cond_chain_tc_kernel");
 }
 
@@ -539,7 +547,12 @@ int sm_count() {
 
 }  // namespace
 
-extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, void* stream) {
+#define PF_CHECK_PREC(p, who) \
+    PF_CHECK_ARG((p) == PF_PREC_FP32_SPLIT || (p) == PF_PREC_FP16, who ": precision %d (PF_PREC_FP32_SPLIT or PF_PREC_FP16)", (p))
+
+extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb, int64_t M, int nblocks, int precision,
+                               void* stream) {
+    PF_CHECK_PREC(precision, "pf_flow_cond_tc");
     if (M == 0) return 0;
     PF_CHECK_ARG(raw && cond_tc && sb, "pf_flow_cond_tc: null pointer");
     PF_CHECK_ARG(M >= 0 && nblocks >= 1 && nblocks <= MAXB, "pf_flow_cond_tc: bad sizes M=%lld nblocks=%d", (long long)M,
@@ -554,12 +567,14 @@ extern "C" int pf_flow_cond_tc(const float* raw, const void* cond_tc, float* sb,
     if (workers < 1) workers = 1;
     if ((int64_t)workers * NWG_C > ntiles) workers = (int)((ntiles + NWG_C - 1) / NWG_C);
     dim3 grid((unsigned)workers, (unsigned)nblocks);
-    flow_cond_tc_kernel<<<grid, NT_C, smem, (cudaStream_t)stream>>>(raw, static_cast<const uint8_t*>(cond_tc), sb, M);
+    flow_cond_tc_kernel<<<grid, NT_C, smem, (cudaStream_t)stream>>>(raw, static_cast<const uint8_t*>(cond_tc), sb, M, precision);
     return pf_launch_status("flow_cond_tc_kernel");
 }
 
 static int flow_tc_launch(bool inverse, const float* xin, const float* raw, int ldraw, const float* sb,
-                          const void* flow_tc, float* xout, float* ssum, int64_t M, int R, int nblocks, void* stream) {
+                          const void* flow_tc, float* xout, float* ssum, int64_t M, int R, int nblocks, int precision,
+                          void* stream) {
+    PF_CHECK_PREC(precision, "pf_flow_tc");
     PF_CHECK_ARG(ldraw >= 64 && ldraw % 8 == 0, "pf_flow_tc: ldraw=%d must be a multiple of 8, >= 64", ldraw);
     if (M == 0) return 0;
     PF_CHECK_ARG(xin && raw && sb && flow_tc && xout, "pf_flow_tc: null pointer");
@@ -576,26 +591,27 @@ static int flow_tc_launch(bool inverse, const float* xin, const float* raw, int 
     const uint8_t* w = static_cast<const uint8_t*>(flow_tc);
     if (inverse) {
         if (int rc = pf_smem_optin(flow_tc_kernel<true>, smem)) return rc;
-        flow_tc_kernel<true><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, nullptr, M, R, nblocks, ldraw);
+        flow_tc_kernel<true><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, nullptr, M, R, nblocks, ldraw, precision);
     } else {
         if (int rc = pf_smem_optin(flow_tc_kernel<false>, smem)) return rc;
-        flow_tc_kernel<false><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, ssum, M, 1, nblocks, ldraw);
+        flow_tc_kernel<false><<<grid, NT, smem, (cudaStream_t)stream>>>(xin, raw, sb, w, xout, ssum, M, 1, nblocks, ldraw, precision);
     }
     return pf_launch_status("flow_tc_kernel");
 }
 
 extern "C" int pf_flow_fwd_tc(const float* x, const float* raw, int ldraw, const float* sb, const void* flow_tc, float* z,
-                              float* ssum, int64_t M, int nblocks, void* stream) {
-    return flow_tc_launch(false, x, raw, ldraw, sb, flow_tc, z, ssum, M, 1, nblocks, stream);
+                              float* ssum, int64_t M, int nblocks, int precision, void* stream) {
+    return flow_tc_launch(false, x, raw, ldraw, sb, flow_tc, z, ssum, M, 1, nblocks, precision, stream);
 }
 
 extern "C" int pf_flow_inv_tc(const float* zin, const float* raw, int ldraw, const float* sb, const void* flow_tc,
-                              float* x, int64_t M, int R, int nblocks, void* stream) {
-    return flow_tc_launch(true, zin, raw, ldraw, sb, flow_tc, x, nullptr, M, R, nblocks, stream);
+                              float* x, int64_t M, int R, int nblocks, int precision, void* stream) {
+    return flow_tc_launch(true, zin, raw, ldraw, sb, flow_tc, x, nullptr, M, R, nblocks, precision, stream);
 }
 
 extern "C" int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, float* raw1, float* sb, int64_t M,
-                                void* stream) {
+                                int precision, void* stream) {
+    PF_CHECK_PREC(precision, "pf_cond_chain_tc");
     if (M == 0) return 0;
     PF_CHECK_ARG(c && chain_tc && raw1 && sb, "pf_cond_chain_tc: null pointer");
     PF_CHECK_ARG(M >= 0, "pf_cond_chain_tc: bad size M=%lld", (long long)M);
@@ -608,8 +624,8 @@ extern "C" int pf_cond_chain_tc(const float* c, int C, const void* chain_tc, flo
     cudaStream_t st = (cudaStream_t)stream;
     const int sms = sm_count();
     switch (C) {
-        case 32: return chain_launch<32>(c, w, raw1, sb, M, sms, st);
-        case 64: return chain_launch<64>(c, w, raw1, sb, M, sms, st);
-        default: return chain_launch<128>(c, w, raw1, sb, M, sms, st);
+        case 32: return chain_launch<32>(c, w, raw1, sb, M, sms, precision, st);
+        case 64: return chain_launch<64>(c, w, raw1, sb, M, sms, precision, st);
+        default: return chain_launch<128>(c, w, raw1, sb, M, sms, precision, st);
     }
 }

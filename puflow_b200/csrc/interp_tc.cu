@@ -58,7 +58,7 @@ template <int RP>   // logits evaluated per edge (R rounded up to 4 / 8 / 16 / 3
 __global__ void __launch_bounds__(NT, 1)
     interp_tc_kernel(const float* __restrict__ xyz, const float* __restrict__ z, const int32_t* __restrict__ idx,
                      int ldidx, const uint8_t* __restrict__ wblob, float* __restrict__ out, int N, int R,
-                     int tiles_per_patch, long long total_tiles) {
+                     int tiles_per_patch, long long total_tiles, int prec) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
@@ -125,8 +125,10 @@ __global__ void __launch_bounds__(NT, 1)
                               uint32_t idesc_2n, uint32_t idesc_n, uint32_t n) {
 #pragma unroll
                 for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bh + b_step * s, idesc_2n, s > 0);
+                if (prec == PF_PREC_FP32_SPLIT) {     // reduced precision: the activations' lo products are dropped
 #pragma unroll
-                for (int s = 0; s < ks; s++) tc::mma_f16(d + n, al + a_step * s, bh + b_step * s, idesc_n, 1);
+                    for (int s = 0; s < ks; s++) tc::mma_f16(d + n, al + a_step * s, bh + b_step * s, idesc_n, 1);
+                }
             };
             auto wdesc = [&](uint32_t off, uint32_t kt) { return tc::smem_desc(sbase + off, kt * 16); };
             const uint64_t xh = tc::smem_desc(x_hi, X_SBO), xl = tc::smem_desc(x_lo, X_SBO);
@@ -149,7 +151,7 @@ __global__ void __launch_bounds__(NT, 1)
             const uint32_t mh = tmem_base + TM_M12_HI, ml = tmem_base + TM_M12_LO;
             auto t0_step = [&](int s, bool first) {
                 tc::mma_f16_ts(d_b, ml + 8u * s, xh + 16u * s, i128, first ? 0u : 1u);
-                tc::mma_f16_ts(d_b, mh + 8u * s, xl + 16u * s, i128, 1);
+                if (prec == PF_PREC_FP32_SPLIT) tc::mma_f16_ts(d_b, mh + 8u * s, xl + 16u * s, i128, 1);
                 tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, first ? 0u : 1u);
             };
             for (; t < total_tiles; t += stride) {
@@ -420,7 +422,7 @@ __global__ void __launch_bounds__(NT, 1)
 
 template <int RP>
 int launch(const float* xyz, const float* z, const int32_t* idx, int ldidx, const uint8_t* w, float* out, int Bp, int N,
-           int R, cudaStream_t st) {
+           int R, int prec, cudaStream_t st) {
     auto kern = interp_tc_kernel<RP>;
     if (int rc = pf_smem_optin(kern, SMEM_BYTES)) return rc;
     const int tiles_per_patch = (N + PT - 1) / PT;
@@ -429,7 +431,7 @@ int launch(const float* xyz, const float* z, const int32_t* idx, int ldidx, cons
     PF_CUDA(cudaGetDevice(&dev));
     PF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int grid = (int)(total < sms ? total : sms);
-    kern<<<grid, NT, SMEM_BYTES, st>>>(xyz, z, idx, ldidx, w, out, N, R, tiles_per_patch, total);
+    kern<<<grid, NT, SMEM_BYTES, st>>>(xyz, z, idx, ldidx, w, out, N, R, tiles_per_patch, total, prec);
     return pf_launch_status("interp_tc_kernel");
 }
 
@@ -442,7 +444,8 @@ extern "C" __attribute__((visibility("default"))) int pf_debug_interp_prof(long 
 #endif
 
 extern "C" int pf_interp_tc(const float* xyz, const float* z, const int32_t* idx, int ldidx, const void* wtc, float* out,
-                            int Bp, int N, int R, void* stream) {
+                            int Bp, int N, int R, int precision, void* stream) {
+    PF_CHECK_ARG(precision == PF_PREC_FP32_SPLIT || precision == PF_PREC_FP16, "pf_interp_tc: precision %d (PF_PREC_FP32_SPLIT or PF_PREC_FP16)", precision);
     PF_CHECK_ARG(xyz && z && idx && wtc && out, "pf_interp_tc: null pointer");
     PF_CHECK_ARG(Bp >= 0 && N >= KN && ldidx >= KN, "pf_interp_tc: bad sizes Bp=%d N=%d ldidx=%d", Bp, N, ldidx);
     PF_CHECK_ARG(R >= 1 && R <= 32, "pf_interp_tc: R=%d outside [1, 32]", R);
@@ -451,8 +454,8 @@ extern "C" int pf_interp_tc(const float* xyz, const float* z, const int32_t* idx
     if (Bp == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     const uint8_t* w = static_cast<const uint8_t*>(wtc);
-    if (R <= 4) return launch<4>(xyz, z, idx, ldidx, w, out, Bp, N, R, st);
-    if (R <= 8) return launch<8>(xyz, z, idx, ldidx, w, out, Bp, N, R, st);
-    if (R <= 16) return launch<16>(xyz, z, idx, ldidx, w, out, Bp, N, R, st);
-    return launch<32>(xyz, z, idx, ldidx, w, out, Bp, N, R, st);
+    if (R <= 4) return launch<4>(xyz, z, idx, ldidx, w, out, Bp, N, R, precision, st);
+    if (R <= 8) return launch<8>(xyz, z, idx, ldidx, w, out, Bp, N, R, precision, st);
+    if (R <= 16) return launch<16>(xyz, z, idx, ldidx, w, out, Bp, N, R, precision, st);
+    return launch<32>(xyz, z, idx, ldidx, w, out, Bp, N, R, precision, st);
 }

@@ -34,7 +34,8 @@ __device__ __forceinline__ void stg256(float* p, const float (&v)[8]) {
 template <int NCH, int S>   // NCH = K / 8, S = A stages
 __global__ void __launch_bounds__(NT, 1)
     linear_split_kernel(const uint8_t* __restrict__ asplit, const uint8_t* __restrict__ wblob, const float* __restrict__ bias,
-                        float* __restrict__ out, int64_t ldo, int64_t M, int N, int ny, int nworkers, int act, float slope) {
+                        float* __restrict__ out, int64_t ldo, int64_t M, int N, int ny, int nworkers, int act, float slope,
+                        int prec) {
     constexpr int K = NCH * 8;
     constexpr uint32_t A_PART = NCH * LBO, A_TILE = 2 * A_PART;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -97,12 +98,15 @@ __global__ void __launch_bounds__(NT, 1)
                 const uint32_t a_hi = sbase + W_MAX + (uint32_t)st * A_TILE, a_lo = a_hi + A_PART;
                 const uint64_t da_hi = tc::smem_desc(a_hi, 128, LBO), da_lo = tc::smem_desc(a_lo, 128, LBO);
                 const uint32_t d_tmem = tmem_base + (uint32_t)g * 128;
+                if (prec == PF_PREC_FP32_SPLIT) {
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, s > 0);
+                    for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, s > 0);
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_lo + b_step * s, idesc, 1);
+                    for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_lo + b_step * s, idesc, 1);
+                }
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, 1);   // full magnitude last
+                for (int s = 0; s < NCH / 2; s++)      // full magnitude last; alone in the single-pass mode
+                    tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, (prec == PF_PREC_FP32_SPLIT || s > 0) ? 1u : 0u);
                 tc::commit(empty + st);
                 tc::commit(acc_full + g);
             }
@@ -161,7 +165,7 @@ __global__ void __launch_bounds__(NT, 1)
 
 template <int NCH, int S>
 int launch(const uint8_t* a, const uint8_t* w, const float* bias, float* out, int64_t ldo, int64_t M, int N, int act,
-           float slope, cudaStream_t st) {
+           float slope, int prec, cudaStream_t st) {
     const size_t smem = W_MAX + (size_t)S * 2 * NCH * LBO + 128 + 512;
     auto kern = linear_split_kernel<NCH, S>;
     if (int rc = pf_smem_optin(kern, smem)) return rc;
@@ -173,14 +177,15 @@ int launch(const uint8_t* a, const uint8_t* w, const float* bias, float* out, in
     int nworkers = sms / ny;
     if (nworkers < 1) nworkers = 1;
     if ((int64_t)nworkers > ntiles) nworkers = (int)ntiles;
-    kern<<<nworkers * ny, NT, smem, st>>>(a, w, bias, out, ldo, M, N, ny, nworkers, act, slope);
+    kern<<<nworkers * ny, NT, smem, st>>>(a, w, bias, out, ldo, M, N, ny, nworkers, act, slope, prec);
     return pf_launch_status("linear_split_kernel");
 }
 
 }  // namespace
 
 extern "C" int pf_linear_tc_split(const void* a_split, const void* wtc, const float* bias, float* out, int64_t ldo, int64_t M,
-                                  int K, int N, int act, float slope, void* stream) {
+                                  int K, int N, int act, float slope, int precision, void* stream) {
+    PF_CHECK_ARG(precision == PF_PREC_FP32_SPLIT || precision == PF_PREC_FP16, "pf_linear_tc_split: precision %d (PF_PREC_FP32_SPLIT or PF_PREC_FP16)", precision);
     PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(M >= 0 && N > 0, "pf_linear_tc_split: bad sizes M=%lld N=%d", (long long)M, N);
     if (M == 0) return 0;
@@ -197,8 +202,8 @@ extern "C" int pf_linear_tc_split(const void* a_split, const void* wtc, const fl
     const uint8_t* a = static_cast<const uint8_t*>(a_split);
     const uint8_t* w = static_cast<const uint8_t*>(wtc);
     switch (K) {
-        case 32: return launch<4, 4>(a, w, bias, out, ldo, M, N, act, slope, st);
-        case 64: return launch<8, 4>(a, w, bias, out, ldo, M, N, act, slope, st);
-        default: return launch<16, 2>(a, w, bias, out, ldo, M, N, act, slope, st);
+        case 32: return launch<4, 4>(a, w, bias, out, ldo, M, N, act, slope, precision, st);
+        case 64: return launch<8, 4>(a, w, bias, out, ldo, M, N, act, slope, precision, st);
+        default: return launch<16, 2>(a, w, bias, out, ldo, M, N, act, slope, precision, st);
     }
 }

@@ -32,7 +32,7 @@ template <int NCH>   // NCH = K / 8 in {2, 4, 8, 16}
 __global__ void __launch_bounds__(NT, 1)
     linear_tc_kernel(const float* __restrict__ A, int64_t lda, const uint8_t* __restrict__ wblob,
                      const float* __restrict__ bias, float* __restrict__ out, int64_t ldo, int64_t M, int N, int ny,
-                     int nworkers, int act, float slope) {
+                     int nworkers, int act, float slope, int prec) {
     constexpr int K = NCH * 8;
     constexpr uint32_t LBO = a_lbo(NCH);
     constexpr uint32_t A_PART = NCH * LBO;
@@ -86,14 +86,17 @@ __global__ void __launch_bounds__(NT, 1)
                 tc::mbar_wait_bounded(ready + wg, rphase);
                 rphase ^= 1;
                 tc::fence_after_sync();
-#pragma unroll
                 // the small cross terms first: the accumulator adder truncates, so the fewer additions at full magnitude
-                // (the hi . hi pass) the better
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, s > 0);
+                // (the hi . hi pass) the better; the single-pass mode issues the hi . hi pass alone
+                if (prec == PF_PREC_FP32_SPLIT) {
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_lo + b_step * s, idesc, 1);
+                    for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_lo + a_step * s, db_hi + b_step * s, idesc, s > 0);
 #pragma unroll
-                for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, 1);
+                    for (int s = 0; s < NCH / 2; s++) tc::mma_f16(d_tmem, da_hi + a_step * s, db_lo + b_step * s, idesc, 1);
+                }
+#pragma unroll
+                for (int s = 0; s < NCH / 2; s++)
+                    tc::mma_f16(d_tmem, da_hi + a_step * s, db_hi + b_step * s, idesc, (prec == PF_PREC_FP32_SPLIT || s > 0) ? 1u : 0u);
                 tc::commit(mbar + wg);
             }
         }
@@ -198,7 +201,7 @@ __global__ void __launch_bounds__(NT, 1)
 
 template <int NCH>
 int launch(const float* A, int64_t lda, const uint8_t* w, const float* bias, float* out, int64_t ldo, int64_t M, int N,
-           int act, float slope, cudaStream_t st) {
+           int act, float slope, int prec, cudaStream_t st) {
     const size_t a_wg = 2 * (size_t)NCH * a_lbo(NCH) > 18432 ? 2 * (size_t)NCH * a_lbo(NCH) : 18432;
     const size_t smem = W_MAX + 2 * a_wg + 64;
     auto kern = linear_tc_kernel<NCH>;
@@ -211,14 +214,15 @@ int launch(const float* A, int64_t lda, const uint8_t* w, const float* bias, flo
     int nworkers = sms / ny;
     if (nworkers < 1) nworkers = 1;
     if ((int64_t)nworkers * 2 > ntiles) nworkers = (int)((ntiles + 1) / 2);
-    kern<<<nworkers * ny, NT, smem, st>>>(A, lda, w, bias, out, ldo, M, N, ny, nworkers, act, slope);
+    kern<<<nworkers * ny, NT, smem, st>>>(A, lda, w, bias, out, ldo, M, N, ny, nworkers, act, slope, prec);
     return pf_launch_status("linear_tc_kernel");
 }
 
 }  // namespace
 
 extern "C" int pf_linear_tc(const float* A, int64_t lda, const void* wtc, const float* bias, float* out, int64_t ldo,
-                            int64_t M, int K, int N, int act, float slope, void* stream) {
+                            int64_t M, int K, int N, int act, float slope, int precision, void* stream) {
+    PF_CHECK_ARG(precision == PF_PREC_FP32_SPLIT || precision == PF_PREC_FP16, "pf_linear_tc: precision %d (PF_PREC_FP32_SPLIT or PF_PREC_FP16)", precision);
     PF_CHECK_ARG(slope >= 0.f && slope <= 1.f, "LeakyReLU slope %g outside [0, 1]", (double)slope);
     PF_CHECK_ARG(A && wtc && out, "pf_linear_tc: null pointer");
     PF_CHECK_ARG(M >= 0 && N > 0, "pf_linear_tc: bad sizes M=%lld N=%d", (long long)M, N);
@@ -233,9 +237,9 @@ extern "C" int pf_linear_tc(const float* A, int64_t lda, const void* wtc, const 
     cudaStream_t st = (cudaStream_t)stream;
     const uint8_t* w = static_cast<const uint8_t*>(wtc);
     switch (K) {
-        case 16: return launch<2>(A, lda, w, bias, out, ldo, M, N, act, slope, st);
-        case 32: return launch<4>(A, lda, w, bias, out, ldo, M, N, act, slope, st);
-        case 64: return launch<8>(A, lda, w, bias, out, ldo, M, N, act, slope, st);
-        default: return launch<16>(A, lda, w, bias, out, ldo, M, N, act, slope, st);
+        case 16: return launch<2>(A, lda, w, bias, out, ldo, M, N, act, slope, precision, st);
+        case 32: return launch<4>(A, lda, w, bias, out, ldo, M, N, act, slope, precision, st);
+        case 64: return launch<8>(A, lda, w, bias, out, ldo, M, N, act, slope, precision, st);
+        default: return launch<16>(A, lda, w, bias, out, ldo, M, N, act, slope, precision, st);
     }
 }

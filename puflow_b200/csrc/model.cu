@@ -177,7 +177,9 @@ extern "C" int64_t pf_upsample_workspace_bytes(int Bp, int N, int R) {
 }
 
 extern "C" int pf_upsample_patches(const void* model, const float* xyz, int Bp, int N, int R, void* workspace,
-                                   int64_t workspace_bytes, float* x, float* logp, void* stream) {
+                                   int64_t workspace_bytes, float* x, float* logp, int precision, void* stream) {
+    PF_CHECK_ARG(precision == PF_PREC_FP32_SPLIT || precision == PF_PREC_FP16,
+                 "pf_upsample_patches: precision %d (PF_PREC_FP32_SPLIT or PF_PREC_FP16)", precision);
     PF_CHECK_ARG(Bp >= 0 && N >= KNN && R >= 1 && R <= 32, "pf_upsample_patches: bad sizes Bp=%d N=%d R=%d", Bp, N, R);
     PF_CHECK_ARG(N <= 65535, "pf_upsample_patches: N=%d above the 16-bit neighbour index of the EdgeConv kernel", N);
     if (Bp == 0) return 0;                     // empty batch: nothing to launch, pointers may be null
@@ -222,23 +224,23 @@ extern "C" int pf_upsample_patches(const void* model, const float* xyz, int Bp, 
         if (i == 0)
             rc = pf_linear(xyz, 3, reinterpret_cast<const float*>(m(l.feat_wpq0)), bpq, pq, r2, M, 3, r2, PF_ACT_NONE, 0.f, stream);
         else
-            rc = pf_linear_tc_split(split, m(l.feat_wpq_tc[i]), bpq, pq, r2, M, CFG[i].c_in, r2, PF_ACT_NONE, 0.f, stream);
+            rc = pf_linear_tc_split(split, m(l.feat_wpq_tc[i]), bpq, pq, r2, M, CFG[i].c_in, r2, PF_ACT_NONE, 0.f, precision, stream);
         if (rc) return rc;
         if (i == 0) snprintf(tag, sizeof(tag), "linear_k3_n%d", r2);
         else snprintf(tag, sizeof(tag), "linear_split_k%d_n%d", CFG[i].c_in, r2);
         mk.mark(tag);
         if ((rc = pf_edgeconv_tc_split(pq, idx, m(l.feat_wtc[i]), c, i + 1 < NB ? split : nullptr, Bp, N, KNN, CFG[i].g,
-                                       CFG[i].c_out, 0.05f, stream)))
+                                       CFG[i].c_out, 0.05f, precision, stream)))
             return rc;
         snprintf(tag, sizeof(tag), "edgeconv_tc_g%d_c%d_k%d", CFG[i].g, CFG[i].c_out, KNN);
         mk.mark(tag);
-        if ((rc = pf_cond_chain_tc(c, CFG[i].c_out, m(l.chain[i]), raw1 + (size_t)i * M * 64, sb + (size_t)i * M * 8, M, stream)))
+        if ((rc = pf_cond_chain_tc(c, CFG[i].c_out, m(l.chain[i]), raw1 + (size_t)i * M * 64, sb + (size_t)i * M * 8, M, precision, stream)))
             return rc;
         snprintf(tag, sizeof(tag), "cond_chain_tc_c%d", CFG[i].c_out);
         mk.mark(tag);
     }
     // a5-a11: flow forward -> z, log-likelihood
-    if ((rc = pf_flow_fwd_tc(xyz, raw1, 64, sb, m(l.flow), z, ssum, M, NB, stream))) return rc;
+    if ((rc = pf_flow_fwd_tc(xyz, raw1, 64, sb, m(l.flow), z, ssum, M, NB, precision, stream))) return rc;
     mk.mark("flow_fwd_tc");
     if (logp) {
         logp_patch_kernel<<<Bp, 256, 0, st>>>(z, ssum, reinterpret_cast<const float*>(m(l.logdet)), N, pv);
@@ -247,9 +249,9 @@ extern "C" int pf_upsample_patches(const void* model, const float* xyz, int Bp, 
         mk.mark("logp");
     }
     // a12-a15: latent interpolation (the k = 8 list is the head of the sorted K = 16 list), a10: flow inverse
-    if ((rc = pf_interp_tc(xyz, z, idx, KNN, m(l.interp), zup, Bp, N, R, stream))) return rc;
+    if ((rc = pf_interp_tc(xyz, z, idx, KNN, m(l.interp), zup, Bp, N, R, precision, stream))) return rc;
     mk.mark("interp_tc");
-    rc = pf_flow_inv_tc(zup, raw1, 64, sb, m(l.flow), x, M, R, NB, stream);
+    rc = pf_flow_inv_tc(zup, raw1, 64, sb, m(l.flow), x, M, R, NB, precision, stream);
     mk.mark("flow_inv_tc");
     return rc;
 }

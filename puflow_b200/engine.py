@@ -29,7 +29,14 @@ LOG_2PI = math.log(2.0 * math.pi)
 class PUFlowEngine:
     MAX_GRAPHS = 4
 
-    def __init__(self, state_dict: Dict[str, torch.Tensor], device):
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device, precision="fp32"):
+        """precision: "fp32" (default; fp16 hi/lo split operands, three tensor-core products per contraction: fp32-class
+        results, the path all parity numbers refer to) or "fp16" (single-pass fp16 operands, fp32 accumulation:
+        PF_PREC_FP16 of include/puflow_b200.h; tolerance stated there and in tests/test_gpu_precision.py)."""
+        from ._native import PRECISIONS
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision {precision!r} not in {sorted(k for k in PRECISIONS if isinstance(k, str))}")
+        self.prec = PRECISIONS[precision]
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError(f"PUFlowEngine needs a CUDA device, got {self.device} (no CPU fallback)")
@@ -45,7 +52,7 @@ class PUFlowEngine:
     def _linear(self, a, wd, name, bias=None, act=ACT_NONE):
         """Per-point linear layer: tensor-core kernel when a packed blob exists (K in {16..128}), FFMA otherwise."""
         if self.use_tc and (name + "_tc") in wd:
-            return ops.linear_tc(a, wd[name + "_tc"], wd[name].shape[1], bias, act)
+            return ops.linear_tc(a, wd[name + "_tc"], wd[name].shape[1], bias, act, precision=self.prec)
         return ops.linear(a, wd[name], bias, act)
 
     # ---- stages (each usable on its own; the drop-in module methods call these) -------------------
@@ -61,11 +68,11 @@ class PUFlowEngine:
         small_ffma = g < 32 and os.environ.get("PUFLOW_EDGECONV_SMALL") == "ffma"     # A/B switch for the (8,32), (16,64) blocks
         tc = self.use_tc and idx.shape[-1] == K_MAIN and not small_ffma
         if split_in is not None and "wpq_tc" in f:
-            pq = ops.linear_tc_split(split_in, Bp * N, Cin, f["wpq_tc"], f["wpq"].shape[1], f["bpq"])
+            pq = ops.linear_tc_split(split_in, Bp * N, Cin, f["wpq_tc"], f["wpq"].shape[1], f["bpq"], precision=self.prec)
         else:
             pq = self._linear(c, f, "wpq", f["bpq"])
         if tc:
-            return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05, split=split_out)
+            return ops.edgeconv_tc(pq, idx, f["wtc"], Bp, N, g, Co, 0.05, split=split_out, precision=self.prec)
         assert split_out is None
         return ops.edgeconv(pq, idx, f["wd"], f["wo"], Bp, N, g, Co, 0.05)
 
@@ -104,7 +111,7 @@ class PUFlowEngine:
             c = self.edgeconv_block(i, c, idx, Bp, N, split_in=split, split_out=nxt)
             split = nxt
             feats.append(c.view(Bp, N, -1))
-            ops.cond_chain(c, self.w["chain_tc"][i], raw1[i], sb[i])
+            ops.cond_chain(c, self.w["chain_tc"][i], raw1[i], sb[i], precision=self.prec)
             if want_cs:
                 cs.append(self.merge(i, c).view(Bp, N, -1))
         return (raw1, sb), feats, cs
@@ -115,17 +122,18 @@ class PUFlowEngine:
         raw = torch.empty((NUM_BLOCKS, M, 192), dtype=torch.float32, device=self.device)
         for i in range(NUM_BLOCKS):
             if self.use_tc and self.w["wc_tc"][i] is not None:
-                ops.linear_tc(cs[i].reshape(M, -1), self.w["wc_tc"][i], 192, None, ACT_NONE, out=raw[i])
+                ops.linear_tc(cs[i].reshape(M, -1), self.w["wc_tc"][i], 192, None, ACT_NONE, out=raw[i], precision=self.prec)
             else:
                 ops.linear(cs[i].reshape(M, -1), self.w["wc"][i], None, ACT_NONE, out=raw[i])
-        sb = ops.flow_cond(raw, self.w["cond_tc"] if self.flow_tc else self.w["cond"])
+        sb = ops.flow_cond(raw, self.w["cond_tc"] if self.flow_tc else self.w["cond"], precision=self.prec)
         return raw, sb
 
     def f(self, xyz: torch.Tensor, cond):
         """PointInterpFlow.f (interpflow.py:302-313) -> (z[Bp,N,3], log_det_J[Bp])."""
         Bp, N, _ = xyz.shape
         raw, sb = cond
-        z, ssum = ops.flow_fwd(xyz.reshape(Bp * N, 3), raw, sb, self.w["flow_tc"] if self.flow_tc else self.w["flow"])
+        z, ssum = ops.flow_fwd(xyz.reshape(Bp * N, 3), raw, sb, self.w["flow_tc"] if self.flow_tc else self.w["flow"],
+                               precision=self.prec)
         logdet = self.w["logdet_const"] * N - ssum.view(Bp, N).sum(1)
         return z.view(Bp, N, 3), logdet
 
@@ -143,7 +151,7 @@ class PUFlowEngine:
             idx = self.knn(xyz, K_INTERP)
         wi = self.w["interp"]
         if self.use_tc:
-            return ops.interp_tc(xyz, z, idx, wi["tc"], upratio)
+            return ops.interp_tc(xyz, z, idx, wi["tc"], upratio, precision=self.prec)
         pq = ops.linear(xyz.reshape(Bp * N, 3), wi["wpq"], wi["bpq"])
         return ops.interp(xyz, z, idx, pq, wi["blob"], upratio)
 
@@ -151,7 +159,8 @@ class PUFlowEngine:
         """PointInterpFlow.g (interpflow.py:315-321) on zup[Bp, N*R, 3] (row n*R + r)."""
         raw, sb = cond
         Bp = zup.shape[0]
-        x = ops.flow_inv(zup.reshape(-1, 3), raw, sb, self.w["flow_tc"] if self.flow_tc else self.w["flow"], upratio)
+        x = ops.flow_inv(zup.reshape(-1, 3), raw, sb, self.w["flow_tc"] if self.flow_tc else self.w["flow"], upratio,
+                         precision=self.prec)
         return x.view(Bp, -1, 3)
 
     # ---- whole path ----------------------------------------------------------------------------------
@@ -180,7 +189,7 @@ class PUFlowEngine:
         in x; logp_x reduced in float64 on the device.  What a non-Python host would call."""
         if xyz.dim() != 3 or xyz.shape[2] != 3:
             raise ValueError(f"expected xyz[B,N,3], got {tuple(xyz.shape)}")
-        return ops.upsample_patches(self.model_blob(), xyz.contiguous().float(), upratio)
+        return ops.upsample_patches(self.model_blob(), xyz.contiguous().float(), upratio, precision=self.prec)
 
     def sample(self, xyz: torch.Tensor, upratio: int = 4):
         return self.forward(xyz, upratio)[0]
@@ -200,7 +209,8 @@ class PUFlowEngine:
         workspace buffers owned by the engine; the result is copied out)."""
         clouds = clouds.contiguous().float()
         if not graph:
-            return ops.upsample_clouds(self.model_blob(), clouds, upratio, npoint, num_outliers, patch_points, n_patch, out=out)
+            return ops.upsample_clouds(self.model_blob(), clouds, upratio, npoint, num_outliers, patch_points, n_patch, out=out,
+                                       precision=self.prec)
         key = ("clouds", tuple(clouds.shape), int(upratio), int(npoint), int(num_outliers), int(patch_points), int(n_patch))
         ent = self._graphs.pop(key, None)
         if ent is None:
@@ -211,7 +221,7 @@ class PUFlowEngine:
                              dtype=torch.uint8, device=self.device)
             blob = self.model_blob()
             run = lambda: ops.upsample_clouds(blob, static_in, upratio, npoint, num_outliers, patch_points, n_patch,
-                                              out=static_out, workspace=ws)
+                                              out=static_out, workspace=ws, precision=self.prec)
             cur = torch.cuda.current_stream(self.device)
             side = torch.cuda.Stream(self.device)
             side.wait_stream(cur)

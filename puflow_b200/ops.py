@@ -180,7 +180,7 @@ def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = N.ACT_NONE, s
 
 
 def linear_tc(a: torch.Tensor, wtc: torch.Tensor, N_out: int, bias=None, act: int = N.ACT_NONE, slope: float = 0.0,
-              out=None):
+              out=None, precision: int = 0):
     """Tensor-core (tcgen05, split-fp16) variant of `linear`: a[M,K] fp32, wtc = packing.pack_linear_tc(W[K,N]).
     K in {16,32,64,128}, N % 16 == 0."""
     if a.dim() != 2 or a.stride(1) != 1 or not a.is_cuda or a.dtype != torch.float32:
@@ -196,7 +196,7 @@ def linear_tc(a: torch.Tensor, wtc: torch.Tensor, N_out: int, bias=None, act: in
     lda = a.stride(0) if M > 1 else max(K, a.stride(0))
     with _dev(a), _launch(f"linear_tc_k{K}_n{N_out}"):
         N.check(lib.pf_linear_tc(a.data_ptr(), lda, wtc.data_ptr(), bias.data_ptr() if bias is not None else None,
-                                 out.data_ptr(), out.stride(0), M, K, N_out, act, float(slope), _stream()),
+                                 out.data_ptr(), out.stride(0), M, K, N_out, act, float(slope), int(precision), _stream()),
                 "pf_linear_tc")
     return out
 
@@ -225,7 +225,7 @@ def split_tiles(M: int, K: int, device):
 
 
 def linear_tc_split(a_split: torch.Tensor, M: int, K: int, wtc: torch.Tensor, Nout: int, bias=None, act: int = N.ACT_NONE,
-                    slope: float = 0.0):
+                    slope: float = 0.0, precision: int = 0):
     """out[M, Nout] = act(A . W + bias) for A given pre-split (split_tiles layout, written by edgeconv_tc(split=...))."""
     _chk(a_split, "a_split", torch.uint8), _chk(wtc, "wtc", torch.uint8)
     if a_split.numel() != ((M + 127) // 128) * 512 * K or K not in (32, 64, 128) or Nout % 16:
@@ -237,12 +237,13 @@ def linear_tc_split(a_split: torch.Tensor, M: int, K: int, wtc: torch.Tensor, No
     out = torch.empty((M, Nout), dtype=torch.float32, device=a_split.device)
     with _dev(a_split), _launch(f"linear_split_k{K}_n{Nout}"):
         N.check(lib.pf_linear_tc_split(a_split.data_ptr(), wtc.data_ptr(), bias.data_ptr() if bias is not None else None,
-                                       out.data_ptr(), Nout, M, K, Nout, act, float(slope), _stream()), "pf_linear_tc_split")
+                                       out.data_ptr(), Nout, M, K, Nout, act, float(slope), int(precision), _stream()),
+                "pf_linear_tc_split")
     return out
 
 
 def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int, Npts: int, G: int, C_out: int,
-                slope: float = 0.05, split: torch.Tensor = None):
+                slope: float = 0.05, split: torch.Tensor = None, precision: int = 0):
     """Tensor-core (tcgen05, split-fp16) variant of `edgeconv` for K = 16, (G, C_out) in {(8,32), (16,64), (32,128)};
     wtc: uint8 blob from packing.pack_edgeconv_tc(wd, wo, G, C_out)."""
     _chk(pq, "pq"), _chk(idx, "idx", torch.int32), _chk(wtc, "wtc", torch.uint8)
@@ -260,12 +261,12 @@ def edgeconv_tc(pq: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, Bp: int,
     with _dev(pq), _launch(f"edgeconv_tc_g{G}_c{C_out}_k{K}"):
         N.check(lib.pf_edgeconv_tc_split(pq.data_ptr(), idx.data_ptr(), wtc.data_ptr(), out.data_ptr(),
                                          split.data_ptr() if split is not None else None, Bp, Npts, K, G, C_out,
-                                         float(slope), _stream()), "pf_edgeconv_tc")
+                                         float(slope), int(precision), _stream()), "pf_edgeconv_tc")
     return out
 
 
 # ---- (3) flow ------------------------------------------------------------------------------------
-def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
+def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor, precision: int = 0):
     """raw[nb, M, 192] -> sb[nb, M, 8] = (s0,s1,s2,b0,b1,b2,0,0): coupling2 scale/bias per input point."""
     _chk(raw, "raw")
     nb, M, w = raw.shape
@@ -275,7 +276,7 @@ def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
         if w != 192 or cond_w.shape != (nb, N.PF_COND_TC_BLOCK):
             raise ValueError("flow_cond: bad shapes")
         with _dev(raw), _launch("flow_cond_tc"):
-            N.check(lib.pf_flow_cond_tc(raw.data_ptr(), cond_w.data_ptr(), sb.data_ptr(), M, nb, _stream()),
+            N.check(lib.pf_flow_cond_tc(raw.data_ptr(), cond_w.data_ptr(), sb.data_ptr(), M, nb, int(precision), _stream()),
                     "pf_flow_cond_tc")
         return sb
     _chk(cond_w, "cond_w")
@@ -286,7 +287,7 @@ def flow_cond(raw: torch.Tensor, cond_w: torch.Tensor):
     return sb
 
 
-def cond_chain(c: torch.Tensor, chain_w: torch.Tensor, raw1: torch.Tensor, sb: torch.Tensor):
+def cond_chain(c: torch.Tensor, chain_w: torch.Tensor, raw1: torch.Tensor, sb: torch.Tensor, precision: int = 0):
     """One block of the fused conditioning chain: c[M, C] (EdgeConv output) -> raw1[M, 64], sb[M, 8] written in place
     (FeatMergeUnit interpflow.py:251-258 + first layers of the three LinearA1D nets + the coupling2 nets)."""
     _chk(c, "c"), _chk(chain_w, "chain_w", torch.uint8), _chk(raw1, "raw1"), _chk(sb, "sb")
@@ -294,12 +295,12 @@ def cond_chain(c: torch.Tensor, chain_w: torch.Tensor, raw1: torch.Tensor, sb: t
     if C not in (32, 64, 128) or chain_w.numel() != N.chain_tc_bytes(C) or raw1.shape != (M, 64) or sb.shape != (M, 8):
         raise ValueError("cond_chain: bad shapes")
     with _dev(c), _launch(f"cond_chain_tc_c{C}"):
-        N.check(lib.pf_cond_chain_tc(c.data_ptr(), C, chain_w.data_ptr(), raw1.data_ptr(), sb.data_ptr(), M, _stream()),
+        N.check(lib.pf_cond_chain_tc(c.data_ptr(), C, chain_w.data_ptr(), raw1.data_ptr(), sb.data_ptr(), M, int(precision), _stream()),
                 "pf_cond_chain_tc")
     return raw1, sb
 
 
-def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor):
+def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor, precision: int = 0):
     """x[M,3] -> (z[M,3], ssum[M]); FlowBlock.forward x nb (interpflow.py:66-74,302-313)."""
     tc = flow_w.dtype == torch.uint8         # tensor-core variant: blob from packing.pack_flow_tc
     _chk(x, "x"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w", torch.uint8 if tc else torch.float32)
@@ -312,7 +313,7 @@ def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch
     if tc:
         with _dev(x), _launch("flow_fwd_tc"):
             N.check(lib.pf_flow_fwd_tc(x.data_ptr(), raw.data_ptr(), ldraw, sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
-                                       ssum.data_ptr(), M, nb, _stream()), "pf_flow_fwd_tc")
+                                       ssum.data_ptr(), M, nb, int(precision), _stream()), "pf_flow_fwd_tc")
         return z, ssum
     with _dev(x), _launch("flow_fwd"):
         N.check(lib.pf_flow_fwd(x.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), z.data_ptr(),
@@ -320,7 +321,7 @@ def flow_fwd(x: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch
     return z, ssum
 
 
-def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor, R: int):
+def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: torch.Tensor, R: int, precision: int = 0):
     """zin[M*R,3] (row n*R+r conditioned by input point n) -> x[M*R,3]; FlowBlock.inverse x nb."""
     tc = flow_w.dtype == torch.uint8
     _chk(zin, "zin"), _chk(raw, "raw"), _chk(sb, "sb"), _chk(flow_w, "flow_w", torch.uint8 if tc else torch.float32)
@@ -332,7 +333,7 @@ def flow_inv(zin: torch.Tensor, raw: torch.Tensor, sb: torch.Tensor, flow_w: tor
     if tc:
         with _dev(zin), _launch("flow_inv_tc"):
             N.check(lib.pf_flow_inv_tc(zin.data_ptr(), raw.data_ptr(), ldraw, sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(),
-                                       M, R, nb, _stream()), "pf_flow_inv_tc")
+                                       M, R, nb, int(precision), _stream()), "pf_flow_inv_tc")
         return x
     with _dev(zin), _launch("flow_inv"):
         N.check(lib.pf_flow_inv(zin.data_ptr(), raw.data_ptr(), sb.data_ptr(), flow_w.data_ptr(), x.data_ptr(), M, R,
@@ -356,7 +357,7 @@ def interp(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, pq: torch.Tens
     return out
 
 
-def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, R: int):
+def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.Tensor, R: int, precision: int = 0):
     """Tensor-core (tcgen05, split-fp16) variant of `interp`; needs no pq.  wtc: uint8[PF_INTERP_TC_BLOB] from
     packing.pack_interp_tc."""
     _chk(xyz, "xyz"), _chk(z, "z"), _chk(idx, "idx", torch.int32), _chk(wtc, "wtc", torch.uint8)
@@ -368,7 +369,7 @@ def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.
     out = torch.empty((Bp, Npts * R, 3), dtype=torch.float32, device=xyz.device)
     with _dev(xyz), _launch("interp_tc"):
         N.check(lib.pf_interp_tc(xyz.data_ptr(), z.data_ptr(), idx.data_ptr(), idx.shape[2], wtc.data_ptr(),
-                                 out.data_ptr(), Bp, Npts, R, _stream()), "pf_interp_tc")
+                                 out.data_ptr(), Bp, Npts, R, int(precision), _stream()), "pf_interp_tc")
     return out
 
 
@@ -395,7 +396,8 @@ class _Workspaces:
 _workspaces = _Workspaces()
 
 
-def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_logp: bool = True, workspace=None):
+def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_logp: bool = True, workspace=None,
+                     precision: int = 0):
     """pf_upsample_patches: xyz[Bp,N,3] -> (x[Bp, N*R, 3], logp scalar tensor or None) with the whole of
     PointInterpFlow.forward (interpflow.py:327-337) launched from C on the current stream.  model_blob: uint8 CUDA tensor
     from packing.pack_model_blob.  The scratch buffer is kept per (device, stream, size) unless `workspace` is given;
@@ -414,7 +416,7 @@ def upsample_patches(model_blob: torch.Tensor, xyz: torch.Tensor, R: int, want_l
     with _dev(xyz):
         ws = workspace if workspace is not None else _workspaces.get(xyz.device, need)
         N.check(lib.pf_upsample_patches(model_blob.data_ptr(), xyz.data_ptr(), Bp, Npts, R, ws.data_ptr(), need,
-                                        x.data_ptr(), logp.data_ptr() if want_logp else None, _stream()),
+                                        x.data_ptr(), logp.data_ptr() if want_logp else None, int(precision), _stream()),
                 "pf_upsample_patches")
     if Bp:
         count_launches(network_launches(Bp, want_logp))
@@ -435,7 +437,7 @@ def upsample_clouds_workspace_bytes(B, Npts, R, npoint, patch_points, n_patch) -
 
 
 def upsample_clouds(model_blob: torch.Tensor, clouds: torch.Tensor, R: int, npoint: int, num_outliers: int,
-                    patch_points: int, n_patch: int, out: torch.Tensor = None, workspace=None):
+                    patch_points: int, n_patch: int, out: torch.Tensor = None, workspace=None, precision: int = 0):
     """pf_upsample_clouds: clouds[B,N,3] -> [B, npoint - num_outliers, 3]: PatchHelper.upsample(jitter=False) (+
     remove_outliers when num_outliers > 0) launched from C on the current stream (upsample.py:46-54)."""
     _chk(model_blob, "model_blob", torch.uint8), _chk(clouds, "clouds")
@@ -454,7 +456,7 @@ def upsample_clouds(model_blob: torch.Tensor, clouds: torch.Tensor, R: int, npoi
     with _dev(clouds):
         ws = workspace if workspace is not None else _workspaces.get(clouds.device, need)
         N.check(lib.pf_upsample_clouds(model_blob.data_ptr(), clouds.data_ptr(), B, Npts, R, npoint, num_outliers,
-                                       patch_points, n_patch, ws.data_ptr(), need, out.data_ptr(), _stream()),
+                                       patch_points, n_patch, ws.data_ptr(), need, out.data_ptr(), int(precision), _stream()),
                 "pf_upsample_clouds")
     count_launches(cloud_launches(B * n_patch, num_outliers))
     return out
