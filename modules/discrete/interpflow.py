@@ -10,8 +10,9 @@ convolutions:
   FlowBlock.forward / inverse           -> pf_linear + pf_flow_cond + pf_flow_fwd / pf_flow_inv
   InterpolationModule.forward           -> pf_knn_topk + pf_linear + pf_interp
 
-Inputs must be CUDA tensors; there is no CPU fallback.  DistanceEncoder, KnnContextEncoder and
-WeightEstimationUnit exist for their parameters: their arithmetic is fused inside pf_interp.
+Inputs must be CUDA tensors; there is no CPU fallback.  On the hot path DistanceEncoder, KnnContextEncoder and
+WeightEstimationUnit are evaluated fused inside pf_interp_tc; called on their own (as the reference's API allows:
+net.interp.knn_context(xyz), net.interp.weight_unit(ctx)) they run layer by layer on pf_linear.
 """
 from typing import List
 
@@ -36,6 +37,29 @@ def knn_points(p1: Tensor, p2: Tensor, K: int, return_nn: bool = False, return_s
     """pytorch3d.ops.knn_points-compatible wrapper over pf_knn_topk: (dists[B,P1,K], idx int64[B,P1,K], None)."""
     d, i = ops.knn_topk(p1.contiguous().float(), p2.contiguous().float(), K)
     return d, i.long(), None
+
+
+def _conv1x1(rows: Tensor, conv: nn.Conv2d, bn: nn.BatchNorm2d = None, act: int = ACT_NONE, slope: float = 0.0):
+    """One 1x1 Conv2d (+ eval-mode BatchNorm folded in, + activation) on per-edge rows[M, C_in] -> [M, C_out] through
+    pf_linear (the FP32 FFMA kernel): the stand-alone forms of the interpolation sub-modules, whose arithmetic the hot
+    path evaluates fused inside pf_interp_tc.  C_out must be a multiple of 8."""
+    W = conv.weight.detach().double().flatten(1)                       # [C_out, C_in]
+    b = conv.bias.detach().double() if conv.bias is not None else torch.zeros(W.shape[0], dtype=torch.float64, device=W.device)
+    if bn is not None:
+        g = bn.weight.detach().double() / torch.sqrt(bn.running_var.detach().double() + bn.eps)
+        W, b = W * g[:, None], (b - bn.running_mean.detach().double()) * g + bn.bias.detach().double()
+    return ops.linear(rows, W.t().contiguous().float(), b.float().contiguous(), act, slope)
+
+
+def _rows(f: Tensor):
+    """[B, C, N, K] -> ([B*N*K, C] contiguous fp32, (B, N, K))."""
+    B, C, N, K = f.shape
+    return f.permute(0, 2, 3, 1).reshape(B * N * K, C).contiguous().float(), (B, N, K)
+
+
+def _unrows(r: Tensor, shp):
+    B, N, K = shp
+    return r.view(B, N, K, -1).permute(0, 3, 1, 2)                      # [B, C, N, K]
 
 
 def _idx32(idx: Tensor):
@@ -158,8 +182,27 @@ class DistanceEncoder(nn.Module):
             nn.LeakyReLU(inplace=True),
             nn.Conv2d(64, dim_out, [1, 1]))
 
+    def distance_vec(self, xyz: Tensor):
+        """reference interpflow.py:101-115: kNN (pf_knn_topk) + the 10-channel edge feature [x_i, x_j, x_i - x_j, |.|]."""
+        xyz = check_input(xyz, "DistanceEncoder")
+        B, N, C = xyz.shape
+        idx = ops.knn_topk(xyz, xyz, self.k, return_dist=False)[1]                       # [B, N, k] int32, sorted
+        neighbors = ops.gather_points(xyz, idx.view(B, N * self.k).contiguous()).view(B, N, self.k, C)
+        pt_raw = xyz.unsqueeze(2).expand_as(neighbors)
+        vec = pt_raw - neighbors
+        dist = torch.sqrt(torch.sum(vec ** 2, dim=-1, keepdim=True))
+        f = torch.cat([pt_raw, neighbors, vec, dist], dim=-1).permute(0, 3, 1, 2)        # [B, 10, N, k]
+        return f, idx.long().view(B, -1)
+
     def forward(self, xyz: Tensor):
-        raise NotImplementedError("DistanceEncoder is fused into pf_interp: call InterpolationModule.forward")
+        """Stand-alone form (reference interpflow.py:117-120) -> (f[B, C_out, N, k], idx_knn[B, N*k]); three pf_linear
+        launches on the per-edge rows.  The hot path evaluates the same layers fused inside pf_interp_tc."""
+        f_dist, idx_knn = self.distance_vec(xyz)
+        r, shp = _rows(f_dist)
+        r = _conv1x1(r, self.mlp[0], self.mlp[1], ACT_LRELU, 0.01)
+        r = _conv1x1(r, self.mlp[3], self.mlp[4], ACT_LRELU, 0.01)
+        r = _conv1x1(r, self.mlp[6])
+        return _unrows(r, shp), idx_knn
 
 
 # -----------------------------------------------------------------------------------------
@@ -172,7 +215,11 @@ class KnnContextEncoder(nn.Module):
         self.feat_conv = FeatureExtractUnit(pc_channel, 128, k=k, growth_width=16, is_dynamic=False)
 
     def forward(self, xyz: Tensor):
-        raise NotImplementedError("KnnContextEncoder is fused into pf_interp: call InterpolationModule.forward")
+        """Stand-alone form (reference interpflow.py:130-134) -> (context[B, 256, N, k], idx_knn[B, N*k])."""
+        B, N, _ = xyz.shape
+        dist, idx_knn = self.distance_encoder(xyz)
+        feat = self.feat_conv(xyz, idx_knn.view(B, N, -1), is_pooling=False)
+        return torch.cat([dist, feat], dim=1), idx_knn
 
 
 # -----------------------------------------------------------------------------------------
@@ -192,7 +239,14 @@ class WeightEstimationUnit(nn.Module):
             nn.Conv2d(64, self.r_max, kernel_size=[1, 1]))
 
     def forward(self, context: Tensor):
-        raise NotImplementedError("WeightEstimationUnit is fused into pf_interp: call InterpolationModule.forward")
+        """Stand-alone form (reference interpflow.py:153-159): context[B, C, N, K] -> [B, N, R_max, K]."""
+        if not context.is_cuda:
+            raise RuntimeError("WeightEstimationUnit: puflow_b200 has no CPU fallback")
+        r, shp = _rows(context)
+        r = _conv1x1(r, self.mlp[0], self.mlp[1], ACT_LRELU, 0.01)
+        r = _conv1x1(r, self.mlp[3], self.mlp[4], ACT_LRELU, 0.01)
+        r = _conv1x1(r, self.mlp[6])
+        return _unrows(r, shp).permute(0, 2, 1, 3)
 
 
 # -----------------------------------------------------------------------------------------
@@ -271,12 +325,10 @@ class FeatureExtractUnit(nn.Module):
 
     def forward(self, x: Tensor, knn_idx: Tensor or None, is_pooling=True):
         C, g, Co = self._cfg
-        if not is_pooling or self.num_conv != 4 or (g, Co) not in ((8, 32), (16, 64), (32, 128)):
-            raise NotImplementedError("stand-alone FeatureExtractUnit on B200 kernels: pooled, 4 dense convs, "
-                                      "(growth, odim) in {(8,32),(16,64),(32,128)}; the k=8 un-pooled instance "
-                                      "of KnnContextEncoder is fused into pf_interp")
         if not x.is_cuda:
             raise RuntimeError("FeatureExtractUnit: puflow_b200 has no CPU fallback")
+        if not is_pooling or self.num_conv != 4 or (g, Co) not in ((8, 32), (16, 64), (32, 128)):
+            return self._forward_layers(x, knn_idx, is_pooling)
         B, N, _ = x.shape
         if knn_idx is None:
             if not self.is_dynamic or C != 3:
@@ -288,6 +340,27 @@ class FeatureExtractUnit(nn.Module):
         if "wtc" in w and idx32.shape[-1] == 16 and os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma":
             return ops.edgeconv_tc(pq, idx32, w["wtc"], B, N, g, Co, 0.05).view(B, N, Co)     # tcgen05 path
         return ops.edgeconv(pq, idx32, w["wd"], w["wo"], B, N, g, Co, 0.05).view(B, N, Co)
+
+
+    def _forward_layers(self, x: Tensor, knn_idx: Tensor, is_pooling: bool):
+        """General / un-pooled form (reference interpflow.py:234-248 as written: edge features, num_conv x (conv1x1 + BN +
+        LeakyReLU(0.05) + concat), conv_out [, max over K]) layer by layer through pf_linear on the per-edge rows: what
+        KnnContextEncoder's stand-alone forward calls (k = 8, growth 16, 8 convs, is_pooling=False -> [B, C, N, K])."""
+        if knn_idx is None:
+            raise ValueError("knn_idx is required")
+        x = x.contiguous().float()
+        B, N, C = x.shape
+        K = knn_idx.shape[-1]
+        nb = ops.gather_points(x, _idx32(knn_idx).view(B, N * K).contiguous()).view(B, N, K, C) if C == 3 else \
+            x[torch.arange(B, device=x.device).view(-1, 1, 1), knn_idx.long()]
+        xt = x.unsqueeze(2).expand_as(nb)
+        f = torch.cat([xt, nb, nb - xt], dim=-1).reshape(B * N * K, 3 * C).contiguous()
+        for i in range(self.num_conv):
+            f = torch.cat([f, _conv1x1(f, self.convs[i][0], self.convs[i][1], ACT_LRELU, 0.05)], dim=1).contiguous()
+        f = _conv1x1(f, self.conv_out).view(B, N, K, -1)
+        if is_pooling:
+            return f.max(dim=2)[0]                                       # [B, N, C]
+        return f.permute(0, 3, 1, 2)                                      # [B, C, N, K]
 
 
 # -----------------------------------------------------------------------------------------
