@@ -16,7 +16,6 @@ net.interp.knn_context(xyz), net.interp.weight_unit(ctx)) they run layer by laye
 """
 from typing import List
 
-import os
 import torch
 import torch.nn as nn
 import torch.nn.functional as F  # noqa: F401  (kept for API familiarity)
@@ -337,7 +336,7 @@ class FeatureExtractUnit(nn.Module):
         w = self._packed(x.device)
         pq = ops.linear(x.reshape(B * N, C).contiguous().float(), w["wpq"], w["bpq"])
         idx32 = _idx32(knn_idx)
-        if "wtc" in w and idx32.shape[-1] == 16 and os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma":
+        if "wtc" in w and idx32.shape[-1] in (8, 16, 32):
             return ops.edgeconv_tc(pq, idx32, w["wtc"], B, N, g, Co, 0.05).view(B, N, Co)     # tcgen05 path
         return ops.edgeconv(pq, idx32, w["wd"], w["wo"], B, N, g, Co, 0.05).view(B, N, Co)
 
@@ -419,6 +418,8 @@ class PointInterpFlow(nn.Module):
         # fp32-class -- the parity path) or "fp16" (single pass; tolerance stated in include/puflow_b200.h).  An attribute,
         # not an environment switch: set `net.precision = "fp16"` before the next call.
         self.precision = "fp32"
+        self.kernels = "tc"          # "ffma": the FP32 FFMA reference kernels (A/B comparison)
+        self.cuda_graph = False      # forward() replayed from a CUDA graph per input shape
 
     def invalidate_packed(self):
         """Drop the packed weights (call after editing parameters through `.data`, which the cache cannot see)."""
@@ -441,8 +442,9 @@ class PointInterpFlow(nn.Module):
                 if not fb.actnorm.is_inited:
                     raise RuntimeError("ActNorm is not initialised: load a checkpoint and call "
                                        "set_to_initialized_state() (reference upsample.py:32-33)")
-            return PUFlowEngine({k: v.detach() for k, v in self.state_dict().items()}, device, precision=self.precision)
-        return self._engine_cache.get(tensors, device, build, extra=(self.precision,))
+            return PUFlowEngine({k: v.detach() for k, v in self.state_dict().items()}, device, precision=self.precision,
+                                kernels=self.kernels)
+        return self._engine_cache.get(tensors, device, build, extra=(self.precision, self.kernels))
 
     def feat_extract(self, xyz: Tensor, knn_idx: Tensor):
         xyz = check_input(xyz, "PointInterpFlow.feat_extract")
@@ -466,16 +468,14 @@ class PointInterpFlow(nn.Module):
     def forward(self, xyz: Tensor, upratio=4):
         xyz = check_input(xyz, "PointInterpFlow")
         eng = self.engine(xyz.device)
-        # PUFLOW_CUDA_GRAPH=1: replay the launch sequence from a CUDA graph captured per input shape (same result;
-        # for small batches the ~100 launches of a call, not the kernels, bound the latency)
-        if os.environ.get("PUFLOW_CUDA_GRAPH") == "1" and not torch.is_grad_enabled():
+        # cuda_graph: replay the launch sequence from a CUDA graph captured per input shape (same result; for small
+        # batches the launches of a call, not the kernels, bound the latency)
+        if self.cuda_graph and not torch.is_grad_enabled():
             return eng.forward_graphed(xyz, upratio)
         # The whole network through the single C-ABI entry point pf_upsample_patches (same kernels, same results bit for
-        # bit, no per-kernel Python); the kernel-by-kernel path is kept for per-launch timing (bench.py's breakdown),
-        # for the FFMA A/B switches and with PUFLOW_ONE_CALL=0.
-        if eng.flow_tc and os.environ.get("PUFLOW_ONE_CALL", "1") != "0" and not ops.per_launch_events_wanted() \
-                and os.environ.get("PUFLOW_EDGECONV_SMALL") != "ffma" and os.environ.get("PUFLOW_PRESPLIT", "1") != "0" \
-                and 16 <= xyz.shape[1] <= 65535 and 1 <= upratio <= 32:
+        # bit, no per-kernel Python); the kernel-by-kernel path is kept for per-launch timing from Python (ops.LaunchLog)
+        # and for the FFMA reference kernels.
+        if eng.flow_tc and not ops.per_launch_events_wanted() and 16 <= xyz.shape[1] <= 65535 and 1 <= upratio <= 32:
             return eng.forward_c(xyz, upratio)
         return eng.forward(xyz, upratio)
 

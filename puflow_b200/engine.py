@@ -13,7 +13,6 @@ fixed sequence of puflow_b200 kernel launches on the current CUDA stream.
 (the drop-in PointInterpFlow) delegates to it.
 """
 import math
-import os
 from typing import Dict, List, Optional
 
 import torch
@@ -29,7 +28,7 @@ LOG_2PI = math.log(2.0 * math.pi)
 class PUFlowEngine:
     MAX_GRAPHS = 4
 
-    def __init__(self, state_dict: Dict[str, torch.Tensor], device, precision="fp32"):
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device, precision="fp32", kernels="tc"):
         """precision: "fp32" (default; fp16 hi/lo split operands, three tensor-core products per contraction: fp32-class
         results, the path all parity numbers refer to) or "fp16" (single-pass fp16 operands, fp32 accumulation:
         PF_PREC_FP16 of include/puflow_b200.h; tolerance stated there and in tests/test_gpu_precision.py)."""
@@ -41,11 +40,13 @@ class PUFlowEngine:
         if self.device.type != "cuda":
             raise RuntimeError(f"PUFlowEngine needs a CUDA device, got {self.device} (no CPU fallback)")
         self.w = pack_state_dict(state_dict, self.device)
-        # tensor-core (tcgen05, split-fp16) EdgeConv for the compute-bound blocks; PUFLOW_EDGECONV=ffma selects the
-        # FP32 FFMA kernel everywhere (A/B comparison, tests)
-        self.use_tc = os.environ.get("PUFLOW_EDGECONV", "tc") != "ffma"
-        # same switch for the flow stack (PUFLOW_FLOW=ffma keeps flow.cu's FP32 kernels)
-        self.flow_tc = self.use_tc and os.environ.get("PUFLOW_FLOW", "tc") != "ffma"
+        # kernels="tc": the tcgen05 kernels (the product path); kernels="ffma": the FP32 FFMA kernels of round 1 everywhere
+        # (edgeconv.cu, flow.cu, interp.cu, linear.cu), kept as the A/B reference the tests compare with.  A constructor
+        # argument, not an environment switch: the two values are the only two paths, both tested against the fixtures.
+        if kernels not in ("tc", "ffma"):
+            raise ValueError(f"kernels {kernels!r} not in ('tc', 'ffma')")
+        self.use_tc = kernels == "tc"
+        self.flow_tc = self.use_tc
         self._graphs = {}                                # (shape, upratio) -> captured CUDA graph, see forward_graphed
         self._model_blob = None                          # packed once on first use of forward_c
 
@@ -65,8 +66,7 @@ class PUFlowEngine:
         pass; split_out: buffer that receives this block's output pre-split for the next block."""
         f = self.w["feat"][i]
         Cin, g, Co = FEAT_CFG[i]
-        small_ffma = g < 32 and os.environ.get("PUFLOW_EDGECONV_SMALL") == "ffma"     # A/B switch for the (8,32), (16,64) blocks
-        tc = self.use_tc and idx.shape[-1] == K_MAIN and not small_ffma
+        tc = self.use_tc and idx.shape[-1] in (8, 16, 32)
         if split_in is not None and "wpq_tc" in f:
             pq = ops.linear_tc_split(split_in, Bp * N, Cin, f["wpq_tc"], f["wpq"].shape[1], f["bpq"], precision=self.prec)
         else:
@@ -103,8 +103,7 @@ class PUFlowEngine:
         sb = torch.empty((NUM_BLOCKS, M, 8), dtype=torch.float32, device=self.device)
         c = xyz.reshape(M, 3)
         feats, cs = [], ([] if want_cs else None)
-        presplit = idx.shape[-1] == K_MAIN and os.environ.get("PUFLOW_PRESPLIT", "1") != "0" and \
-            os.environ.get("PUFLOW_EDGECONV_SMALL") != "ffma"
+        presplit = idx.shape[-1] in (8, 16, 32)
         split = None
         for i in range(NUM_BLOCKS):
             nxt = ops.split_tiles(M, FEAT_CFG[i][2], self.device) if presplit and i + 1 < NUM_BLOCKS else None

@@ -81,7 +81,7 @@ def split_weight(mat):
     """float64/32 weights -> (hi, lo) fp16 with hi + lo ~ fp32(w) * TC_WSCALE to 22 bits.  Without the power-of-two
     factor the lo half of a typical |w| ~ 0.03 falls into the fp16 subnormals (spacing 2^-24) and the product loses
     3 bits against fp32; the kernels' epilogues multiply the accumulator by 2^-10 (exact).  |w| * 1024 must stay
-    below the fp16 maximum: a checkpoint with |w| >= 60 is refused (run it with PUFLOW_EDGECONV=ffma)."""
+    below the fp16 maximum: a checkpoint with |w| >= 60 is refused (run it with PUFlowEngine(kernels="ffma") / net.kernels = "ffma")."""
     w32 = mat.to(torch.float32)
     if w32.numel() and float(w32.abs().max()) >= 60.0:
         raise ValueError(f"weight magnitude {float(w32.abs().max()):.3g} is outside the tensor-core path's fp16 range")

@@ -552,14 +552,13 @@ def test_network_other_checkpoints(dev, golden, tag):
         assert parity.chamfer_distance(r["x"][b].cpu().numpy(), g["x"][b]) <= 1e-5
 
 
-def test_network_ffma_and_tensor_core_paths_agree(dev, state_dict, golden, monkeypatch):
-    """The FP32-FFMA EdgeConv path (PUFLOW_EDGECONV=ffma) and the default tensor-core path both meet the reference."""
+def test_network_ffma_and_tensor_core_paths_agree(dev, state_dict, golden):
+    """The FP32-FFMA kernels (PUFlowEngine(kernels="ffma")) and the default tensor-core path both meet the reference."""
     from puflow_b200.engine import PUFlowEngine
     g = golden("net_pu1k.npz")
     xyz = torch.from_numpy(g["xyz"]).to(dev)
     x_tc = PUFlowEngine(state_dict, dev).forward(xyz, 4)[0]
-    monkeypatch.setenv("PUFLOW_EDGECONV", "ffma")
-    eng = PUFlowEngine(state_dict, dev)
+    eng = PUFlowEngine(state_dict, dev, kernels="ffma")
     assert not eng.use_tc
     x_ff = eng.forward(xyz, 4)[0]
     for x in (x_tc, x_ff):

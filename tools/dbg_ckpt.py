@@ -15,8 +15,7 @@ for tag in ("pu1k", "pugan", "pugeo"):
         return float((np.abs(a - b).max(1) / np.abs(b).max(1)).max())
     print(tag, "reference fp32 vs oracle fp64:  z %.2e  x %.2e" % (nerr(g["z"], o64["z"].numpy()), nerr(g["x"], o64["x"].numpy())))
     for mode in ("tc", "ffma"):
-        os.environ["PUFLOW_EDGECONV"] = mode
-        r = PUFlowEngine(sd, dev).forward(xyz.to(dev), 4, return_all=True)
+        r = PUFlowEngine(sd, dev, kernels=mode).forward(xyz.to(dev), 4, return_all=True)
         fz = r["zup"].cpu().view(3, 256, 4, 3).permute(0, 1, 3, 2).numpy()
         print(f"  {mode:5s} vs reference fp32: feat5 %.2e cs5 %.2e z %.2e fz %.2e x %.2e | vs fp64: z %.2e x %.2e" % (
             nerr(r["feats"][5].cpu().numpy(), g["feat5"]), nerr(r["cs"][5].cpu().numpy(), g["cs5"]),
