@@ -620,6 +620,25 @@ def test_fps_bit_exact(ops, dev, B, n, npoint):
     assert np.array_equal(out, ref)
 
 
+def test_fps_points_at_the_centroid_follow_fps_py(ops, dev):
+    """Semantics pin: this FPS follows the reference's OWN modules/utils/fps.py:40-73, under which points at /
+    near the origin are ordinary candidates.  Upstream pointnet2_ops.furthest_point_sample (un-vendored; what patch.py:102,156
+    imports) additionally never selects candidates with |p|^2 <= 1e-3 -- a documented deviation (DESIGN.md section 2;
+    tools/fps_near_origin.py: 0 such points in the surface clouds of the bench, 1 of 2,048 in a volumetric cloud, none
+    selected).  Here: a centred cloud with a cluster of 40 points inside radius 0.03 of the centroid; every mode returns the
+    oracle's indices, which DO include near-origin points."""
+    rng = np.random.default_rng(3)
+    shell = rng.standard_normal((4056, 3))
+    shell /= np.linalg.norm(shell, axis=1, keepdims=True)
+    core = rng.uniform(-0.015, 0.015, (40, 3))
+    p = np.concatenate([core, shell], 0)[rng.permutation(4096)].astype(np.float32)[None]
+    ref = po.fps(p, 600)
+    assert ((p[0, ref[0]] ** 2).sum(-1) <= 1e-3).sum() >= 1
+    x = torch.from_numpy(p).to(dev)
+    for mode in ("brute", "bucket", "cluster"):
+        assert np.array_equal(ops.fps(x, 600, mode=mode).cpu().numpy(), ref)
+
+
 def test_fps_lattice_ties(ops, dev):
     p = np.stack([synth.make_cloud(1000, s, "lattice") for s in (1, 2)])
     assert np.array_equal(ops.fps(torch.from_numpy(p).to(dev), 200).cpu().numpy(), po.fps(p, 200))
