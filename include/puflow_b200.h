@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 7
+#define PF_ABI_VERSION 8
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -214,6 +214,14 @@ PF_API int pf_fps_bucketed(const float* xyz, int B, int n, int npoint, int32_t* 
  * work: pf_fps_clustered_work_floats(B, n) floats. */
 PF_API long long pf_fps_clustered_work_floats(int B, int n);
 PF_API int pf_fps_clustered(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
+/* The same indices again, bit for bit, with the dependent chain taken out of the block-wide loop ("threshold queue"):
+ * running minima only decrease, so the points above a threshold theta form a list that can only shrink, and while its
+ * maximum exceeds theta the next sample is the arg-max of the LIST.  One warp draws ~70-100 samples in a row from a list of
+ * <= 256 points held in its registers; all warps then apply those samples to the bucketed cloud in one pruned pass and
+ * collect the next list.  One CTA per cloud, any batch size; clouds above pf_fps_queued_max_points() candidates go to
+ * pf_fps_bucketed.  work: pf_fps_work_floats(B, n) floats. */
+PF_API int pf_fps_queued_max_points(void);
+PF_API int pf_fps_queued(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
 
 /* ---- caller glue as kernels ------------------------------------------------------

@@ -229,6 +229,14 @@ CloudWork cloud_layout(int64_t B, int64_t N, int64_t R, int64_t npoint, int64_t 
     return w;
 }
 
+// the sampler for a batch of clouds of n candidates: brute force below 4,096, the threshold queue up to its capacity, the
+// cluster kernel (which falls back to the single-CTA pruned kernel) above; work: pf_fps_clustered_work_floats(B, n) floats
+int fps_any(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream) {
+    if (n < 4096) return pf_fps(xyz, B, n, npoint, idx, nullptr, stream);
+    if (n <= pf_fps_queued_max_points()) return pf_fps_queued(xyz, B, n, npoint, idx, work, stream);
+    return pf_fps_clustered(xyz, B, n, npoint, idx, work, stream);
+}
+
 }  // namespace
 
 extern "C" int pf_normalize_pc(const float* pc, int B, int n, float* out, float* centroid, float* radius, void* stream) {
@@ -311,8 +319,7 @@ extern "C" int pf_upsample_clouds(const void* model, const float* clouds, int B,
     // normalise the clouds, pick the patch seeds, cut the patches (patch.py:59-64,96-125)
     if ((rc = pf_normalize_pc(clouds, B, N, F(w.pcn), F(w.gcen), F(w.grad), stream))) return rc;
     mk.mark("normalize_pc");
-    if ((rc = N >= 4096 ? pf_fps_clustered(F(w.pcn), B, N, n_patch, I(w.seed_idx), F(w.fps), stream)
-                        : pf_fps(F(w.pcn), B, N, n_patch, I(w.seed_idx), nullptr, stream)))
+    if ((rc = fps_any(F(w.pcn), B, N, n_patch, I(w.seed_idx), F(w.fps), stream)))
         return rc;
     snprintf(tag, sizeof(tag), "fps_n%d", N);
     mk.mark(tag);
@@ -329,8 +336,7 @@ extern "C" int pf_upsample_clouds(const void* model, const float* clouds, int B,
     if ((rc = pf_denorm_concat(F(w.x), F(w.patches), F(w.pcen), F(w.prad), Bp, k * R, k, F(w.cand), stream))) return rc;
     mk.mark("denorm_concat");
     // merge: farthest point sampling over all candidates of a cloud, back to the input frame (patch.py:67-70,142-158)
-    if ((rc = ncand >= 4096 ? pf_fps_clustered(F(w.cand), B, ncand, npoint, I(w.sel), F(w.fps), stream)
-                            : pf_fps(F(w.cand), B, ncand, npoint, I(w.sel), nullptr, stream)))
+    if ((rc = fps_any(F(w.cand), B, ncand, npoint, I(w.sel), F(w.fps), stream)))
         return rc;
     snprintf(tag, sizeof(tag), "fps_n%d", ncand);
     mk.mark(tag);

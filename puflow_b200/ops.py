@@ -472,7 +472,8 @@ def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
     """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0).
     mode: "brute" = cluster brute-force kernel, "bucket" = exact spatially pruned kernel (one CTA per cloud),
     "cluster" = the pruned kernel with a cloud's buckets spread over a thread-block cluster (few large clouds; falls back
-    to "bucket" when the clusters of all clouds do not fit the device), "auto" = cluster for n >= 4096.
+    to "bucket" when the clusters of all clouds do not fit the device), "queue" = the threshold-queue kernel (one warp
+    draws ~100 samples per block-wide pass), "auto" = queue for n >= 4096.
     All give identical indices."""
     _chk(xyz, "xyz")
     B, n, _ = xyz.shape
@@ -480,7 +481,11 @@ def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
     if B == 0:
         return idx
     with _dev(xyz), _launch(f"fps_n{n}"):
-        if mode == "cluster" or (mode == "auto" and n >= 4096):
+        if mode == "queue" or (mode == "auto" and n >= 4096):
+            work = torch.empty((lib.pf_fps_work_floats(B, n),), dtype=torch.float32, device=xyz.device)
+            N.check(lib.pf_fps_queued(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), work.data_ptr(), _stream()),
+                    "pf_fps_queued")
+        elif mode == "cluster":
             work = torch.empty((lib.pf_fps_clustered_work_floats(B, n),), dtype=torch.float32, device=xyz.device)
             N.check(lib.pf_fps_clustered(xyz.data_ptr(), B, n, npoint, idx.data_ptr(), work.data_ptr(), _stream()),
                     "pf_fps_clustered")

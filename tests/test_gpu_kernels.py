@@ -672,6 +672,7 @@ def test_fps_bucketed_bit_exact(ops, dev, B, n, npoint, kind):
     if n <= 102400:
         assert np.array_equal(ops.fps(x, npoint, mode="brute").cpu().numpy(), ref)
     assert np.array_equal(ops.fps(x, npoint, mode="cluster").cpu().numpy(), ref)      # buckets spread over a CTA cluster
+    assert np.array_equal(ops.fps(x, npoint, mode="queue").cpu().numpy(), ref)        # threshold queue, one warp runs the chain
 
 
 @pytest.mark.parametrize("B,n,npoint,kind", [(1, 99840, 2500, "surface"), (8, 99840, 300, "surface"), (1, 40960, 8216, "surface"),
@@ -701,6 +702,20 @@ def test_fps_clustered_bit_exact(ops, dev, B, n, npoint, kind):
     ref = po.fps(p, npoint)
     x = torch.from_numpy(np.ascontiguousarray(p)).to(dev)
     assert np.array_equal(ops.fps(x, npoint, mode="cluster").cpu().numpy(), ref)
+    assert np.array_equal(ops.fps(x, npoint, mode="queue").cpu().numpy(), ref)
+
+
+def test_fps_queue_tie_search(ops, dev):
+    """pf_fps_queued when more points tie with the maximum than the queue holds (400 exact copies of each of six far
+    points): the block-wide tie search draws the lowest original index, like the brute-force definition."""
+    rng = np.random.default_rng(7)
+    B, n, npoint = 2, 6000, 3000
+    p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    for j in range(6):
+        p[:, 400 * j:400 * (j + 1)] = rng.uniform(2, 3, (B, 1, 3)).astype(np.float32) * (1 if j % 2 else -1)
+    p = np.ascontiguousarray(p[:, rng.permutation(n)])
+    ref = po.fps(p, npoint)
+    assert np.array_equal(ops.fps(torch.from_numpy(p).to(dev), npoint, mode="queue").cpu().numpy(), ref)
 
 
 @pytest.mark.parametrize("B,nq,np_,k", [(2, 32, 2048, 256), (1, 78, 5000, 256), (2, 5, 300, 256), (1, 3, 1000, 1000)])
