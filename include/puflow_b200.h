@@ -222,6 +222,15 @@ PF_API int pf_fps_clustered(const float* xyz, int B, int n, int npoint, int32_t*
  * pf_fps_bucketed.  work: pf_fps_work_floats(B, n) floats. */
 PF_API int pf_fps_queued_max_points(void);
 PF_API int pf_fps_queued(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
+/* pf_fps_queued_static: no counterpart in the reference; added for callers that
+ * cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same inputs, outputs and indices as pf_fps_queued, but the scratch is a file-scope static __device__ array inside the
+ * library (PF_FPS_STATIC_MAX_POINTS points x 20 B = 5 MiB, resident on every GPU that loads the library until exit): the
+ * call allocates nothing.  Limit: B * ceil32(n) <= PF_FPS_STATIC_MAX_POINTS (e.g. one cloud of 99,840 candidates or six of
+ * 40,960), otherwise PF_EINVAL with a message.  All calls on a device share the array: calls that overlap on the GPU race;
+ * nothing in it needs clearing between calls (the kernel rewrites every entry it reads). */
+#define PF_FPS_STATIC_MAX_POINTS 262144
+PF_API int pf_fps_queued_static(const float* xyz, int B, int n, int npoint, int32_t* idx, void* stream);
 PF_API int pf_knn_patch(const float* q, const float* p, int B, int nq, int np, int k, int32_t* idx, void* stream);
 
 /* ---- caller glue as kernels ------------------------------------------------------

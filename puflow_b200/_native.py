@@ -45,6 +45,7 @@ SIGNATURES = {
     "pf_fps_clustered": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_queued": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_queued_max_points": [],
+    "pf_fps_queued_static": [_vp, _i, _i, _i, _vp, _vp],
     "pf_knn_patch": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
     "pf_xyz_count": [ctypes.c_char_p, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_int)],
     "pf_xyz_read": [ctypes.c_char_p, _vp, _i64, _i],
@@ -81,6 +82,7 @@ lib.pf_last_error.restype = ctypes.c_char_p
 
 PF_ABI_VERSION = 8
 PF_MODEL_ENTRIES = 27
+PF_FPS_STATIC_MAX_POINTS = 262144
 PF_COND_BLOB = 8840
 PF_FLOW_BLOB = 4480
 PF_COND_TC_BLOCK = 35360

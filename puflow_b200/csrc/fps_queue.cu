@@ -21,8 +21,15 @@
 // Exactness: the same sqdist() arithmetic everywhere, min is order-independent, a pruned bucket provably cannot
 // change, ties go to the lowest original index (all points that tie with the maximum are in L).  If more than 256
 // points are within rounding of the maximum (duplicated points), one sample is drawn by a block-wide tie search.
+#include <mutex>
+
 #include "common.cuh"
 #include "puflow_b200.h"
+
+// Scratch of pf_fps_queued_static: PF_FPS_STATIC_MAX_POINTS sorted points x 5 floats = 5 MiB, held by every GPU that loads
+// the library until the process exits.  In HOST code this name is only a stand-in for the symbol (not a device address):
+// the entry point below asks the runtime for the address, once per device.
+static __device__ __align__(256) float g_fps_static_scratch[(size_t)PF_FPS_STATIC_MAX_POINTS * 5];
 
 namespace {
 
@@ -400,6 +407,38 @@ int launch_queue(const float* xyz, int B, int n, int npoint, int32_t* idx, float
 
 // largest cloud the register-resident bucket boxes cover: 5 buckets of 32 points per lane
 extern "C" int pf_fps_queued_max_points(void) { return 32 * NW * 32 * 5; }
+
+// pf_fps_queued with its scratch in the library's own static device array: no allocation anywhere (no cudaMalloc /
+// cudaFree, no allocating library call), for callers that cannot allocate (CUDA-graph capture, serving loops).
+// All calls on a device share the one array: calls that overlap on the GPU (two streams, two threads) race.  Nothing in
+// it has to start at zero -- the kernel writes every entry it later reads (sorted coordinates, indices, running minima)
+// before the first round -- so the previous call's contents are harmless.
+extern "C" int pf_fps_queued_static(const float* xyz, int B, int n, int npoint, int32_t* idx, void* stream) {
+    PF_CHECK_ARG(xyz && idx, "pf_fps_queued_static: null pointer");
+    PF_CHECK_ARG(B >= 0 && n > 0 && npoint > 0, "pf_fps_queued_static: bad sizes B=%d n=%d npoint=%d", B, n, npoint);
+    const long long need = (long long)B * (((long long)n + 31) / 32 * 32);
+    PF_CHECK_ARG(need <= (long long)PF_FPS_STATIC_MAX_POINTS,
+                 "pf_fps_queued_static: B=%d clouds of n=%d candidates need %lld points of scratch (32-padded), the static array holds "
+                 "PF_FPS_STATIC_MAX_POINTS=%d; use pf_fps_queued with caller-owned scratch", B, n, need, PF_FPS_STATIC_MAX_POINTS);
+    if (B == 0) return 0;
+    constexpr int MAXDEV = 64;
+    static float* dev_ptr[MAXDEV] = {nullptr};        // address of the array on each device, looked up once per device
+    static std::mutex mu;
+    int dev = -1;
+    PF_CUDA(cudaGetDevice(&dev));
+    PF_CHECK_ARG(dev >= 0 && dev < MAXDEV, "pf_fps_queued_static: device ordinal %d outside [0, %d)", dev, MAXDEV);
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!dev_ptr[dev]) {
+            void* p = nullptr;
+            PF_CUDA(cudaGetSymbolAddress(&p, g_fps_static_scratch));      // with `dev` current: this device's copy
+            dev_ptr[dev] = static_cast<float*>(p);
+        }
+        scratch = dev_ptr[dev];
+    }
+    return pf_fps_queued(xyz, B, n, npoint, idx, scratch, stream);
+}
 
 extern "C" int pf_fps_queued(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream) {
     PF_CHECK_ARG(xyz && idx && work, "pf_fps_queued: null pointer (work must hold pf_fps_work_floats(B, n) floats)");
