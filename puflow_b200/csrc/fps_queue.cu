@@ -285,26 +285,60 @@ __global__ void __launch_bounds__(FT, 1)
             theta = tie_mode ? M : M * (1.f - gap);
             int* cw = ctrl + C_CNT0 + attempt % 3;
             if (tid == 0) ctrl[C_CNT0 + (attempt + 1) % 3] = 0;
+            if (tie_mode) {
 #pragma unroll
-            for (int h = 0; h < BPL; h++) {
-                unsigned mask = __ballot_sync(FULL, tie_mode ? bmr[h] == M : bmr[h] > theta);
-                while (mask) {
-                    const int k = __ffs(mask) - 1;
-                    mask &= mask - 1;
-                    const int p = pbase + 32 * (32 * h + k);
-                    const float m = MD_SMEM ? md_s[p] : mdg[p];
-                    if (tie_mode) {
+                for (int h = 0; h < BPL; h++) {
+                    unsigned mask = __ballot_sync(FULL, bmr[h] == M);
+                    while (mask) {
+                        const int k = __ffs(mask) - 1;
+                        mask &= mask - 1;
+                        const int p = pbase + 32 * (32 * h + k);
+                        const float m = MD_SMEM ? md_s[p] : mdg[p];
                         if (m == M) atomicMin(tie, ((unsigned long long)so[p] << 32) | (unsigned)p);
-                        continue;
                     }
-                    const bool in = m > theta;
-                    const unsigned bal = __ballot_sync(FULL, in);
-                    if (bal) {
-                        int slot0 = 0;
-                        if (lane == 0) slot0 = atomicAdd(cw, __popc(bal));
-                        slot0 = __shfl_sync(FULL, slot0, 0);
-                        const int slot = slot0 + __popc(bal & ((1u << lane) - 1u));
-                        if (in && slot < CAP) Lp[slot] = p, Ld[slot] = m;
+                }
+            } else {
+                // two sweeps over the warp's buckets above theta: count, ONE atomic per warp for its slots, then write
+                unsigned bm[BPL];
+                int total = 0;
+#pragma unroll
+                for (int h = 0; h < BPL; h++) {
+                    bm[h] = __ballot_sync(FULL, bmr[h] > theta);
+                    unsigned mask = bm[h];
+                    while (mask) {
+                        float m[4];
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            m[u] = 0.f;
+                            if (mask) {
+                                const int k = __ffs(mask) - 1;
+                                mask &= mask - 1;
+                                const int p = pbase + 32 * (32 * h + k);
+                                m[u] = MD_SMEM ? md_s[p] : mdg[p];
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; u++) total += __popc(__ballot_sync(FULL, m[u] > theta));   // theta >= 0
+                    }
+                }
+                if (total) {
+                    int slot0 = 0;
+                    if (lane == 0) slot0 = atomicAdd(cw, total);
+                    slot0 = __shfl_sync(FULL, slot0, 0);
+#pragma unroll
+                    for (int h = 0; h < BPL; h++) {
+                        unsigned mask = bm[h];
+                        while (mask && slot0 < CAP) {
+                            const int k = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            const int p = pbase + 32 * (32 * h + k);
+                            const float m = MD_SMEM ? md_s[p] : mdg[p];
+                            const bool in = m > theta;
+                            const unsigned bal = __ballot_sync(FULL, in);
+                            const int slot = slot0 + __popc(bal & ((1u << lane) - 1u));
+                            if (in && slot < CAP) Lp[slot] = p, Ld[slot] = m;
+                            slot0 += __popc(bal);
+                        }
                     }
                 }
             }
