@@ -31,16 +31,21 @@ def tag_of(name):
         if k in name: return k
     return None
 
-rows = list(csv.reader(l for l in open(sys.argv[1]) if not l.startswith("==")))
-hdr = rows[0]
-iname, imet, ival, iid = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("ID")
-acc = {}
-for r in rows[1:]:
-    if len(r) <= ival or not r[imet].startswith("dram__bytes"):
-        continue
-    t = tag_of(r[iname])
-    if t is None:
-        continue
-    acc.setdefault(t, {}).setdefault(r[iid], 0.0)
-    acc[t][r[iid]] += float(r[ival].replace(",", ""))
-print(json.dumps({t: round(sum(v.values()) / len(v)) for t, v in sorted(acc.items())}, indent=1))
+def main():
+    rows = list(csv.reader(l for l in open(sys.argv[1]) if not l.startswith("==")))
+    hdr = rows[0]
+    iname, imet, ival, iid = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("ID")
+    acc = {}
+    for r in rows[1:]:
+        if len(r) <= ival or not r[imet].startswith("dram__bytes"):
+            continue
+        t = tag_of(r[iname])
+        if t is None:
+            continue
+        acc.setdefault(t, {}).setdefault(r[iid], 0.0)
+        acc[t][r[iid]] += float(r[ival].replace(",", ""))
+    print(json.dumps({t: round(sum(v.values()) / len(v)) for t, v in sorted(acc.items())}, indent=1))
+
+
+if __name__ == "__main__":
+    main()
