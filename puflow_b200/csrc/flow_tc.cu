@@ -41,6 +41,7 @@ struct Wg {
     uint8_t* a_row_hi;      // this thread's row of the hi operand (chunk 0); lo is A_PART further; chunk c at + c * 128
     uint32_t a_hi;          // shared-memory address of the hi operand
     uint32_t d_tmem;        // accumulator columns of this warpgroup
+    uint32_t a_tmem;        // flow kernels: the A operand lives in tensor memory (hi: 32 columns, lo: the next 32)
     uint32_t lane_sel;      // TMEM lane quadrant of this warp
     uint64_t* mbar;         // MMA-done barrier of this warpgroup
     uint32_t phase;
@@ -108,6 +109,64 @@ __device__ __forceinline__ void hidden_mma(Wg& g, uint32_t w_addr, float (&acc)[
     for (int i = 0; i < 32; i++) acc[i] = lo32[i], acc[32 + i] = hi32[i];
 }
 
+// The same two steps with the A operand in TENSOR memory (flow forward / inverse; round 2).  ncu on the shared-memory
+// form (profiles/r02_ncu_step_full.md): L1TEX data pipe 66-70 % busy, tensor pipe 11-19 %: every 64-wide activation row was
+// written to shared memory (16 STS.128 per thread), made visible to the async proxy, and read back by the 12 MMAs' A
+// fetches.  tcgen05.st puts the row into this thread's own TMEM lane (2 fp16 per 32-bit column, K order) instead: no
+// shared-memory traffic for A at all, no proxy fence.
+__device__ __forceinline__ float store_row_t(const Wg& g, float (&h)[64]) {
+    float amax = 0.f;
+#pragma unroll
+    for (int k = 0; k < 64; k++) amax = fmaxf(amax, fabsf(h[k]));
+    const int ex = (__float_as_int(amax) >> 23) & 0xff;       // biased exponent (NaN/Inf rows stay NaN/Inf)
+    float inv = tc::WINV;                                     // the weights carry a factor 1 / WINV (tc.cuh)
+    if (ex > 127 + 13) {
+        const int k = min(ex - 140, 120);
+        const float sc = __int_as_float((127 - k) << 23);
+        inv = __int_as_float((127 + k) << 23) * tc::WINV;
+#pragma unroll
+        for (int i = 0; i < 64; i++) h[i] *= sc;
+    }
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int u = 0; u < 16; u++) tc::split2(h[32 * q + 2 * u], h[32 * q + 2 * u + 1], hi[u], lo[u]);
+        tc::st16_nowait(g.a_tmem + g.lane_sel + 16 * q, hi);
+        tc::st16_nowait(g.a_tmem + g.lane_sel + 32 + 16 * q, lo);
+    }
+    return inv;
+}
+__device__ __forceinline__ void hidden_mma_t(Wg& g, uint32_t w_addr, float (&acc)[64]) {
+    tc::tmem_st_wait();
+    tc::fence_before_sync();
+    tc::named_bar(g.bar_id, 128);        // operand rows written; previous accumulators read by everyone
+    if (g.e < 32 && tc::elect_one()) {
+        tc::fence_after_sync();
+        const uint32_t idesc = tc::idesc_f16(128, H);
+        const uint32_t a_hi = g.a_tmem, a_lo = g.a_tmem + 32;
+        const uint64_t db_hi = tc::smem_desc(w_addr, H * 16), db_lo = tc::smem_desc(w_addr + W_PART, H * 16);
+        if (g.prec == PF_PREC_FP32_SPLIT) {
+#pragma unroll
+            for (int s = 0; s < H / 16; s++) tc::mma_f16_ts(g.d_tmem, a_lo + 8u * s, db_hi + 16u * s, idesc, s > 0);
+#pragma unroll
+            for (int s = 0; s < H / 16; s++) tc::mma_f16_ts(g.d_tmem, a_hi + 8u * s, db_lo + 16u * s, idesc, 1);
+        }
+#pragma unroll
+        for (int s = 0; s < H / 16; s++)       // full magnitude last
+            tc::mma_f16_ts(g.d_tmem, a_hi + 8u * s, db_hi + 16u * s, idesc, (g.prec == PF_PREC_FP32_SPLIT || s > 0) ? 1u : 0u);
+        tc::commit(g.mbar);
+    }
+    tc::mbar_wait_bounded(g.mbar, g.phase);
+    g.phase ^= 1;
+    tc::fence_after_sync();
+    float lo32[32], hi32[32];
+    tc::ld32(g.d_tmem + g.lane_sel, lo32);
+    tc::ld32(g.d_tmem + g.lane_sel + 32, hi32);
+#pragma unroll
+    for (int i = 0; i < 32; i++) acc[i] = lo32[i], acc[32 + i] = hi32[i];
+}
+
 __device__ __forceinline__ void wg_init(Wg& g, uint8_t* smem, uint32_t a_off, uint64_t* mbars, uint32_t tmem_base,
                                         int tid, int prec) {
     g.prec = prec;
@@ -137,7 +196,7 @@ __global__ void __launch_bounds__(NT, 1)
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t w_bytes = (uint32_t)nblocks * FBLK;
     const uint32_t a_off = (w_bytes + 127u) & ~127u;
-    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off + NWG * A_WG);
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off);      // no operand tile: A lives in tensor memory
     uint64_t* mbars = wbar + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbars + NWG);
 
@@ -147,7 +206,7 @@ __global__ void __launch_bounds__(NT, 1)
         for (int i = 0; i < NWG; i++) mbar_init(mbars + i, 1);
         mbar_fence_init();
     }
-    if (warp == 0) tc::tmem_alloc(tmem_slot, 256);
+    if (warp == 0) tc::tmem_alloc(tmem_slot, 512);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
@@ -157,6 +216,8 @@ __global__ void __launch_bounds__(NT, 1)
     }
     Wg g;
     wg_init(g, smem, a_off, mbars, *tmem_slot, tid, prec);
+    g.d_tmem = *tmem_slot + (uint32_t)wg * 128;      // per warpgroup: 64 accumulator columns, then the A operand (hi 32 | lo 32)
+    g.a_tmem = g.d_tmem + 64;
     const uint32_t sbase = smem_u32(smem);
     const int64_t rows = INVERSE ? M * R : M;
     const int64_t ntiles = (rows + TP - 1) / TP;
@@ -213,11 +274,11 @@ __global__ void __launch_bounds__(NT, 1)
                     h[4 * c + 2] = lrelu(fmaf(wb.z, h1b, fmaf(wa.z, x0, h[4 * c + 2])), SLOPE);
                     h[4 * c + 3] = lrelu(fmaf(wb.w, h1b, fmaf(wa.w, x0, h[4 * c + 3])), SLOPE);
                 }
-                inv = store_row(g, h);
+                inv = store_row_t(g, h);
             }
             // layer 2 on the tensor cores, layer 4 per thread
             float acc[64];
-            hidden_mma(g, sbase + (uint32_t)blk * FBLK, acc);
+            hidden_mma_t(g, sbase + (uint32_t)blk * FBLK, acc);
             float o0 = fw[352], o1 = fw[353];
 #pragma unroll
             for (int k = 0; k < H; k++) {
@@ -254,7 +315,7 @@ __global__ void __launch_bounds__(NT, 1)
     }
     tc::fence_before_sync();
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc(*tmem_slot, 256);
+    if (warp == 0) tc::tmem_dealloc(*tmem_slot, 512);
 }
 
 // ---- conditioning: coupling2.scale_net / bias_net hidden + output layers per input point ------------------------
@@ -583,7 +644,7 @@ static int flow_tc_launch(bool inverse, const float* xin, const float* raw, int 
     PF_CHECK_ARG(((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(flow_tc) |
                    reinterpret_cast<uintptr_t>(sb)) & 31) == 0, "pf_flow_tc: pointers must be 32-byte aligned");
     if (M == 0) return 0;
-    const size_t smem = (((size_t)nblocks * FBLK + 127u) & ~(size_t)127u) + NWG * A_WG + 64;
+    const size_t smem = (((size_t)nblocks * FBLK + 127u) & ~(size_t)127u) + 64;       // weights + barriers: the A operand is in tensor memory
     const int64_t rows = inverse ? M * R : M;
     const int64_t ntiles = (rows + TP - 1) / TP;
     int grid = sm_count();
