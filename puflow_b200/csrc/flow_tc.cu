@@ -446,6 +446,40 @@ __device__ __forceinline__ void store_chunk(const Wg& g, int c, const float (&h)
     *reinterpret_cast<uint4*>(g.a_row_hi + A_PART + c * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
+// Tensor-memory forms (round 2): A at a_hi / a_lo (2 fp16 per column, 8 columns per K-step), see store_row_t above.
+__device__ __forceinline__ void issue3_t(Wg& g, uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t w_addr, uint32_t w_part,
+                                         uint32_t w_sbo, int ks, int n) {
+    tc::tmem_st_wait();
+    tc::fence_before_sync();
+    tc::named_bar(g.bar_id, 128);
+    if (g.e < 32 && tc::elect_one()) {
+        tc::fence_after_sync();
+        const uint32_t idesc = tc::idesc_f16(128, n);
+        const uint64_t db_hi = tc::smem_desc(w_addr, w_sbo), db_lo = tc::smem_desc(w_addr + w_part, w_sbo);
+        const bool split = g.prec == PF_PREC_FP32_SPLIT;
+        if (split) {
+#pragma unroll 1
+            for (int s = 0; s < ks; s++) tc::mma_f16_ts(d_tmem, a_lo + 8u * s, db_hi + 16u * s, idesc, s > 0 ? 1u : 0u);
+#pragma unroll 1
+            for (int s = 0; s < ks; s++) tc::mma_f16_ts(d_tmem, a_hi + 8u * s, db_lo + 16u * s, idesc, 1);
+        }
+#pragma unroll 1
+        for (int s = 0; s < ks; s++) tc::mma_f16_ts(d_tmem, a_hi + 8u * s, db_hi + 16u * s, idesc, (split || s > 0) ? 1u : 0u);
+        tc::commit(g.mbar);
+    }
+    tc::mbar_wait_bounded(g.mbar, g.phase);
+    g.phase ^= 1;
+    tc::fence_after_sync();
+}
+// 16 values (K-steps' worth) of this thread's operand row -> columns [8 * cp, 8 * cp + 8) of a_hi / a_lo, plain saturating split
+__device__ __forceinline__ void store_pair_t(const Wg& g, uint32_t a_hi, uint32_t a_lo, int cp, const float (&u)[8], const float (&v)[8]) {
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 4; i++) tc::split2(u[2 * i], u[2 * i + 1], hi[i], lo[i]), tc::split2(v[2 * i], v[2 * i + 1], hi[4 + i], lo[4 + i]);
+    tc::st8_nowait(a_hi + g.lane_sel + 8 * cp, hi);
+    tc::st8_nowait(a_lo + g.lane_sel + 8 * cp, lo);
+}
+
 constexpr int NWG_CH = 2, NT_CH = NWG_CH * 128;
 __host__ __device__ constexpr uint32_t chain_w1_part(int C) { return (uint32_t)C * C; }          // (C/2) x C halfs
 __host__ __device__ constexpr uint32_t chain_w2_part(int C) { return 192u * C; }                 // 192 x (C/2) halfs
@@ -462,7 +496,7 @@ __global__ void __launch_bounds__(NT_CH, 1)
     constexpr uint32_t OFF_W2 = 2 * W1P, OFF_NET = OFF_W2 + 2 * W2P, OFF_F = OFF_NET + 4 * W_PART;
     constexpr uint32_t a_off = (WBYTES + 127u) & ~127u;
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off + NWG_CH * A_WG);
+    uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + a_off);      // no operand tiles: every A operand lives in tensor memory
     uint64_t* mbars = wbar + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbars + NWG_CH);
 
@@ -484,6 +518,10 @@ __global__ void __launch_bounds__(NT_CH, 1)
     wg_init(g, smem, a_off, mbars, *tmem_slot, tid, prec);
     g.d_tmem = *tmem_slot + (uint32_t)wg * 256;          // per warpgroup: raw at +0 (192 columns), scratch at +192 (64)
     const uint32_t d_raw = g.d_tmem, d_s = g.d_tmem + 192;
+    // A operands alias accumulator columns that are dead at that point: stage 1 (K = C) in raw[0:128) (raw is produced by
+    // stage 2), stage 2 in the scratch columns (stage 1's accumulators are in registers by then), stage 3 in raw[0:64) (already
+    // stored to HBM).  A warp only ever touches its own 32 lanes, so warps of a group need no ordering among themselves.
+    const uint32_t a1_hi = d_raw, a1_lo = d_raw + 64;
     const uint32_t sbase = smem_u32(smem);
     const float* fb1 = reinterpret_cast<const float*>(smem + OFF_F);
     const float* cw = fb1 + 64;
@@ -494,17 +532,13 @@ __global__ void __launch_bounds__(NT_CH, 1)
         const int64_t r = t * TP + g.e;
         const float* crow = cin + (size_t)min(r, M - 1) * C;
         // ---- stage 1: h = relu(c . W1 + b1), K = C in slices of at most 64 through the 64-wide operand buffer ----
-        constexpr int KS1 = C < 64 ? C : 64;
-#pragma unroll 1
-        for (int k0 = 0; k0 < C; k0 += KS1) {
 #pragma unroll
-            for (int c = 0; c < KS1 / 8; c++) {
-                float u[8];
-                ldg256(crow + k0 + 8 * c, u);
-                store_chunk(g, c, u);
-            }
-            issue3(g, d_s, sbase, W1P, C * 16, k0 / 16, KS1 / 16, H1, k0 > 0);
+        for (int cp = 0; cp < C / 16; cp++) {
+            float u[8], v[8];
+            ldg256(crow + 16 * cp, u), ldg256(crow + 16 * cp + 8, v);
+            store_pair_t(g, a1_hi, a1_lo, cp, u, v);
         }
+        issue3_t(g, d_s, a1_hi, a1_lo, sbase, W1P, C * 16, C / 16, H1);
         float inv;
         {
             float h[64];
@@ -526,10 +560,11 @@ __global__ void __launch_bounds__(NT_CH, 1)
             }
 #pragma unroll
             for (int i = 0; i < H1; i++) h[i] = fmaxf(fmaf(h[i], tc::WINV, fb1[i]), 0.f);
-            inv = store_row(g, h);                      // columns beyond H1 are zero and never read by the MMAs
+            g.a_tmem = d_s;
+            inv = store_row_t(g, h);                    // columns beyond H1 are zero and never read by the MMAs
         }
         // ---- stage 2: raw = h . W2c  (N = 192) ----
-        issue3(g, d_raw, sbase + OFF_W2, W2P, H1 * 16, 0, H1 / 16, 192, false);
+        issue3_t(g, d_raw, d_s, d_s + 32, sbase + OFF_W2, W2P, H1 * 16, H1 / 16, 192);
         {
             float* dst = raw1 + (size_t)r * 64;
 #pragma unroll
@@ -556,9 +591,10 @@ __global__ void __launch_bounds__(NT_CH, 1)
                 tc::ld32(d_raw + g.lane_sel + 64 + 64 * net, lo32), tc::ld32(d_raw + g.lane_sel + 96 + 64 * net, hi32);
 #pragma unroll
                 for (int i = 0; i < 32; i++) h[i] = lrelu(lo32[i] * inv, SLOPE), h[32 + i] = lrelu(hi32[i] * inv, SLOPE);
-                inv2 = store_row(g, h);
+                g.a_tmem = d_raw;
+                inv2 = store_row_t(g, h);
             }
-            issue3(g, d_s, sbase + OFF_NET + (uint32_t)net * 2 * W_PART, W_PART, H * 16, 0, H / 16, H, false);
+            issue3_t(g, d_s, d_raw, d_raw + 32, sbase + OFF_NET + (uint32_t)net * 2 * W_PART, W_PART, H * 16, H / 16, H);
             float acc[64];
             {
                 float lo32[32], hi32[32];
@@ -591,7 +627,7 @@ __global__ void __launch_bounds__(NT_CH, 1)
 
 template <int C>
 int chain_launch(const float* c, const uint8_t* w, float* raw1, float* sb, int64_t M, int sms, int prec, cudaStream_t st) {
-    constexpr size_t smem = ((chain_bytes(C) + 127u) & ~127u) + NWG_CH * A_WG + 64;
+    constexpr size_t smem = ((chain_bytes(C) + 127u) & ~127u) + 64;      // weights + barriers
     if (int rc = pf_smem_optin(cond_chain_tc_kernel<C>, smem)) return rc;
     const int64_t ntiles = (M + TP - 1) / TP;
     int grid = sms;
