@@ -411,42 +411,8 @@ __device__ __forceinline__ void stg256(float* p, const float (&v)[8]) {
                  "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
                  : "memory");
 }
-// operands published -> one thread issues the 3 split products D[:, dcol..dcol+n) (+)= A[:, 0:16 ks] . W^T -> commit
-__device__ __forceinline__ void issue3(Wg& g, uint32_t d_tmem, uint32_t w_addr, uint32_t w_part, uint32_t w_sbo, int w_k0,
-                                       int ks, int n, bool accumulate) {
-    tc::fence_async_smem();
-    tc::fence_before_sync();
-    tc::named_bar(g.bar_id, 128);
-    if (g.e < 32 && tc::elect_one()) {       // first warp of the warpgroup, one elected lane (tc.cuh)
-        tc::fence_after_sync();
-        const uint32_t idesc = tc::idesc_f16(128, n);
-        const uint64_t da_hi = tc::smem_desc(g.a_hi, A_SBO), da_lo = tc::smem_desc(g.a_hi + A_PART, A_SBO);
-        const uint64_t db_hi = tc::smem_desc(w_addr, w_sbo) + 16u * w_k0, db_lo = tc::smem_desc(w_addr + w_part, w_sbo) + 16u * w_k0;
-        const bool split = g.prec == PF_PREC_FP32_SPLIT;
-        if (split) {
-#pragma unroll 1
-            for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_lo + 16u * s, db_hi + 16u * s, idesc, (accumulate || s > 0) ? 1u : 0u);
-#pragma unroll 1
-            for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_lo + 16u * s, idesc, 1);
-        }
-#pragma unroll 1
-        for (int s = 0; s < ks; s++) tc::mma_f16(d_tmem, da_hi + 16u * s, db_hi + 16u * s, idesc, (split || accumulate || s > 0) ? 1u : 0u);
-        tc::commit(g.mbar);
-    }
-    tc::mbar_wait_bounded(g.mbar, g.phase);
-    g.phase ^= 1;
-    tc::fence_after_sync();
-}
-// chunk c (8 values) of this thread's operand row, plain saturating split
-__device__ __forceinline__ void store_chunk(const Wg& g, int c, const float (&h)[8]) {
-    uint32_t hi[4], lo[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++) tc::split2(h[2 * u], h[2 * u + 1], hi[u], lo[u]);
-    *reinterpret_cast<uint4*>(g.a_row_hi + c * 128) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<uint4*>(g.a_row_hi + A_PART + c * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-}
-
-// Tensor-memory forms (round 2): A at a_hi / a_lo (2 fp16 per column, 8 columns per K-step), see store_row_t above.
+// operands published -> one thread issues the 3 split products D[:, 0:n) = A[:, 0:16 ks] . W^T -> commit; everybody waits.
+// A in tensor memory at a_hi / a_lo (2 fp16 per column, 8 columns per K-step), see store_row_t above.
 __device__ __forceinline__ void issue3_t(Wg& g, uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t w_addr, uint32_t w_part,
                                          uint32_t w_sbo, int ks, int n) {
     tc::tmem_st_wait();
