@@ -69,6 +69,8 @@ struct Cfg {
     static constexpr int CPR = G / 4, LCPR = ilog2(CPR);                 // 16-byte chunks per dense Q row
     static constexpr int NCH = CO / 32;                                  // conv_out steps (32 edges per thread each)
     static constexpr int STAGES = 4 + NCH;                               // ring stages per tile
+    // conv_out MMA groups: the four 32-edge column blocks of D^T are issued OW at a time (one commit each), NQ groups per tile
+    static constexpr int OW = NCH == 4 ? 1 : 4, NQ = 4 / OW;
     // ---- shared memory map (bytes) ----
     static constexpr uint32_t WD_BYTES = 24u * GP * GP;                  // W1..W3, hi and lo
     static constexpr uint32_t WO_PART = 128u * KT * 2;                   // blob: [Wd | Wo hi [128][KT/2 words] | Wo lo]
@@ -102,6 +104,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                        long long total_tiles, float slope, int prec) {
     using C = Cfg<G, CO, NWG, KN>;
     constexpr int GP = C::GP, R = C::R, R2 = C::R2, KT = C::KT, CPR = C::CPR, LCPR = C::LCPR, NCH = C::NCH, PT = C::PT;
+    constexpr int OW = C::OW, NQ = C::NQ;
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + C::BAR_OFF);
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
     if (role == 1) {
         // ================= MMA-issuing warp of warpgroup wg: one elected thread (elect_one, not lane == 0: tc.cuh) waits
         // for "operands ready", issues, commits =================
-        const uint32_t idesc_o = tc::idesc_f16(128, 32);
+        const uint32_t idesc_o = tc::idesc_f16(128, 32 * OW);
         const bool split3 = prec == PF_PREC_FP32_SPLIT;     // PF_PREC_FP16: the hi . hi products alone
         const uint64_t da_hi = tc::smem_desc(a_hi, C::A_SBO), da_lo = tc::smem_desc(a_lo, C::A_SBO);
         // D[128 edges x GP (3 - m)] (+)= h_m . [W_{m+1,m}; ..; W_{3,m}]^T, h_m from tensor memory (8 columns per K-step).
@@ -201,26 +204,24 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
 #pragma unroll
             for (int s = 0; s < GP / 16; s++) tc::mma_f16_ts(d, h_hi + 8u * s, db_hi + 16u * s, idesc, split3 || m > 0 || s > 0);
         };
-        // conv_out step c: D^T[128 rows x 32 edges] = Wo . H^T for the 128 / CO column blocks (32 edges each) that the
-        // epilogue threads read in step c (block g NCH + c for edge group g); Wo from TMEM (8 columns per K-step), H^T rows
-        // 32 cb .. 32 cb + 32 of the shared-memory operand (4 row groups = 4 SBO further per block).  One commit per step:
-        // the epilogue of step c runs while the tensor pipe computes step c + 1 (one N = 128 MMA chain kept the epilogue
-        // waiting for all 24 instructions, 1,500 cycles per tile).
-        auto issue_out = [&](int c) {
+        // conv_out group q: D^T[128 rows x 32 OW edges] = Wo . H^T for the column blocks [OW q, OW q + OW) (32 edges each;
+        // epilogue step c of edge group g reads block g NCH + c); Wo from TMEM (8 columns per K-step), H^T rows 32 cb ..
+        // of the shared-memory operand (4 row groups = 4 SBO further per block).  One commit per group.  (32, 128): four
+        // N = 32 groups, the epilogue of step c runs while the tensor pipe computes step c + 1 (measured: one N = 128 chain
+        // 1,500 cycles of waiting per tile; two N = 64 groups 3.22 ms against 2.91).  C_out < 128: a step reads blocks that
+        // are not adjacent, so the whole tile is ONE N = 128 group (a quarter of the instructions: (8, 32) 1.04 -> 0.96 ms).
+        auto issue_out = [&](int q) {
             const uint32_t wo_hi = tmem_base + C::TM_WO_HI, wo_lo = tmem_base + C::TM_WO_LO;
+            const uint32_t cb = (uint32_t)(q * OW), d = d_out + 32u * cb;
+            const uint64_t bh = da_hi + (uint64_t)(4u * cb * (C::A_SBO >> 4)), bl = da_lo + (uint64_t)(4u * cb * (C::A_SBO >> 4));
+            if (split3) {
 #pragma unroll
-            for (int g = 0; g < 128 / CO; g++) {
-                const uint32_t cb = (uint32_t)(g * NCH + c), d = d_out + 32u * cb;
-                const uint64_t bh = da_hi + (uint64_t)(4u * cb * (C::A_SBO >> 4)), bl = da_lo + (uint64_t)(4u * cb * (C::A_SBO >> 4));
-                if (split3) {
+                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_lo + 8u * s, bh + 16u * s, idesc_o, s > 0);
 #pragma unroll
-                    for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_lo + 8u * s, bh + 16u * s, idesc_o, s > 0);
-#pragma unroll
-                    for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bl + 16u * s, idesc_o, 1);
-                }
-#pragma unroll
-                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bh + 16u * s, idesc_o, split3 || s > 0);
+                for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bl + 16u * s, idesc_o, 1);
             }
+#pragma unroll
+            for (int s = 0; s < KT / 16; s++) tc::mma_f16_ts(d, wo_hi + 8u * s, bh + 16u * s, idesc_o, split3 || s > 0);
         };
         tc::mbar_wait_bounded(wbar, 0);   // dense-layer weights have landed
         if (tc::elect_one()) {
@@ -243,9 +244,9 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 tc::fence_after_sync();
                 PROF_TICK(0)
 #pragma unroll
-                for (int c = 0; c < NCH; c++) {
-                    issue_out(c);
-                    tc::commit(cbar + c);
+                for (int q = 0; q < NQ; q++) {
+                    issue_out(q);
+                    tc::commit(cbar + q);
                 }
             }
             PROF_TICK(1)
@@ -472,8 +473,10 @@ __global__ void __launch_bounds__(Cfg<G, CO, NWG, KN>::NT, 1)
                 tc::mbar_wait_bounded(qfull + b, (st >> 1) & 1);
                 st++;
                 PROF_TICK(6)
-                tc::mbar_wait_bounded(cbar + c, cphase);
-                tc::fence_after_sync();
+                if (c % (NCH / NQ) == 0) {
+                    tc::mbar_wait_bounded(cbar + c / (NCH / NQ), cphase);
+                    tc::fence_after_sync();
+                }
                 PROF_TICK(7)
                 const uint8_t* slot = ring_p + b * C::SLOT;
                 float acc[32];

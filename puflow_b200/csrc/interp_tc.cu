@@ -10,19 +10,41 @@
 // that reads coordinates takes them from a 16-wide "geo" K-slice of the activation operand
 //     geo = [x_i | x_j | x_j - x_i | |x_i - x_j| | 1 | 0..]   (bias rides on the constant 1)
 // with the reference's unfolded weights (puflow_b200/packing.py pack_interp_tc).  A tile is 128 edges = 16 points
-// x 8 neighbours; activation operand X[128 edges][K = 208] = geo(16) | dense block h (128) | distance encoder (64),
-// K-major fp16 hi/lo in shared memory.  Per tile (all MMAs M = 128, issued by a dedicated warp):
-//   1  d1 = lrelu(geo.Wd1g)  (N=64)        and  h0 = lrelu(geo.Wh0)         (N=16)
-//   2  d2 = lrelu(d1.Wd3+bd3) (N=64, K=64) and  h1 = lrelu([geo|h0].Wh1)    (N=16, K=32)
-//   3..8  h_l = lrelu([geo|h_<l].Wh_l)  (N=16, K=16+16l)
-//   9  t0^T[128 ch x 128 edges] = M12g . X^T  (K=208; M12g = mlp.0 o (mlp.6 | conv_out) composed on the host, resident
-//      in TMEM as the A operand); thread = channel; t0 is written back as an M-major (edge-contiguous) operand
-//      -- its 13 K-steps are issued as their X columns become final, behind the MMAs of stages 3..8, so only h6 / h7 remain
+// x 8 neighbours; X[128 edges][K = 208] = geo(16) | dense block h (128) | distance encoder (64), K-major fp16 hi/lo
+// in shared memory, is the B operand of the composed 208 -> 128 layer t0.
+//
+// Round-2 structure (per-stage clock64() tables in profiles/r02_interp.md).  One tile is a chain of 11 dependent
+// tensor-core round trips (~900 cycles each through mbarriers, whatever the MMA does), and the 8 dense layers were 60 %
+// of it: each a round trip of two epilogue warpgroups (TMEM load, LeakyReLU, split, STS, fence.proxy.async) plus
+// 2 (l + 1) small MMAs at ~36 cycles of issue each on the critical path (145 tcgen05.mma per tile from one thread).  A
+// second tile in flight does not fit (X is 106 KB of shared memory, and 2 x (t0 + dense accumulators) exceed the 512
+// TMEM columns), so the chain itself was shortened and everything else moved off it:
+//   warpgroup 0  the dense chain alone.  Layer l's accumulator (16 columns) -> LeakyReLU -> fp16 hi/lo -> a 16-column
+//                slice of TENSOR MEMORY (tcgen05.st, no proxy fence), the A operand of ONE wide MMA group that adds
+//                h_l's contribution to ALL later layers at once:
+//                    D[128 edges x 16 (7 - l)] += h_l . [W_{l+1,l}; ..; W_{7,l}]^T     (3 MMAs, K = 16)
+//                (the geo slice feeds all eight layers the same way, N = 128), so the critical path of a layer is
+//                three instructions and K = 16, whatever l.  It skips the softmax stage and starts the next tile's chain
+//                while warpgroup 1 finishes the current tile;
+//   warpgroup 1  everything off that path: the distance encoder (d1, d2), the shared-memory copies of h_l / d2 that t0
+//                reads as its B operand (it re-reads the same accumulator columns; its stores and proxy fences cost the
+//                chain nothing), the softmax + output stage.  Each publish has its own mbarrier (one completion per
+//                tile), so the chain may run ahead of it safely;
+//   MMA warp     one elected thread: dense groups as their slices arrive; behind each group up to three items of the
+//                work that does not gate the chain (d2, and the 13 K-steps of t0^T = M12g . X^T), chosen by TESTING
+//                (mbarrier.test_wait) which of warpgroup 1's publishes have happened -- never waiting for them.  The
+//                head of the NEXT tile (geo part of all dense layers, d1) is issued right behind the logits MMAs: the geo
+//                slice has a buffer of its own and is written during the tail.
+// Then, both warpgroups (column halves of a stage):
+//   9  t0^T[128 ch x 128 edges] (M12g = mlp.0 o (mlp.6 | conv_out) composed on the host, resident in TMEM as the A
+//      operand); thread = channel; t0 is written back as an M-major (edge-contiguous) operand
 //  10  t1 = lrelu(t0.W3 + b3)  (A = t0 M-major, N=64, K=128)      11  logits = t1.W6 + b6  (N=32, K=64)
 //  then softmax over the 8 neighbours (8 consecutive lanes) and the weighted sum of the neighbours' latents.
-// Per-stage clock64() totals (tools/dev_interp_prof.py, -DPF_INTERP_PROF) showed the MMA-issuing thread, not the tensor
-// pipe, bounding the N = 16 layers (69 cycles per tcgen05.mma issued from an `if (lane == 0)` region: an ELECT/branch
-// loop around every instruction), hence elect_one() and the 2-MMA split form below.
+// Narrow products (d1, d2, t1) use the stacked form: hi and lo of a weight matrix are adjacent row groups of ONE K-major
+// operand, a_hi . [b_hi | b_lo] is a single MMA of width 2n and only a_lo . b_hi remains.
+// 4.17 -> 3.61 ms at config 2; measured and rejected on the way: test_wait spinning on the chain's two waits (no change),
+// warpgroup 0 writing the X copies itself from its hi/lo registers (the chain's stage grows by 165 cycles: 3.75 ms),
+// d1 of the next tile before the softmax (3.75 ms), five instead of three side items per gap (3.97 ms).
 #include "common.cuh"
 #include "puflow_b200.h"
 #include "tc.cuh"
@@ -32,22 +54,33 @@ namespace {
 using namespace pf;
 
 constexpr int KN = 8, PT = 16, TM = 128;
-constexpr int NT = 288;                                   // 2 x 4 epilogue warps (column halves of one tile) + 1 MMA-issuing warp
+constexpr int NT = 288;                                   // 2 x 4 epilogue warps + 1 MMA-issuing warp
 constexpr float S_CTX = 0.05f, S_DEF = 0.01f;             // interpflow.py:206,217 / nn.LeakyReLU() default :94,97,147,150
 
 // ---- shared memory map (bytes) ----
 constexpr uint32_t W_D1 = 0, W_D2 = 4096, W_H = 20480, W_3 = 57344, W_6 = 90112, B_D3 = 98304, B_3 = 98560, B_6 = 98816;
 constexpr uint32_t W_BYTES = 98944;
-__host__ __device__ constexpr uint32_t wh_off(int l) { return W_H + 1024u * (l * (l + 1) / 2); }
-__host__ __device__ constexpr uint32_t wh_part(int l) { return 512u * (l + 1); }
+// dense block, by K-slice: Wg = the geo columns of all eight layers [128][16] (hi, lo), then S_m = the h_m columns of
+// layers m+1..7 [16 (7 - m)][16] (hi, lo), m = 0..6
+constexpr uint32_t WG_PART = 4096;
+__host__ __device__ constexpr uint32_t ws_off(int m) { return W_H + 2 * WG_PART + 1024u * (7 * m - m * (m - 1) / 2); }
+__host__ __device__ constexpr uint32_t ws_part(int m) { return 512u * (7 - m); }
 constexpr uint32_t X_OFF = 99072, KX = 208, X_SBO = KX * 16, X_PART = 128 * KX * 2;    // 53,248 per part
 constexpr uint32_t T0_OFF = X_OFF, T0_PART = 32768;       // t0 M-major [128 ch][128 edges], aliases X (dead by then)
 constexpr uint32_t T1_OFF = X_OFF + 65536, T1_PART = 16384, T1_SBO = 64 * 16;
-constexpr uint32_t BAR_OFF = X_OFF + 2 * X_PART;          // 205,568
-constexpr uint32_t SMEM_BYTES = BAR_OFF + 64;
+// the geo slice has a buffer of its own ([128][16] K-major, hi | lo): the NEXT tile's slice is written, and its first MMAs
+// are issued, under the tail of the current tile (whose t0 / t1 operands alias X)
+constexpr uint32_t GEO_OFF = X_OFF + 2 * X_PART, GEO_PART = 4096, GEO_SBO = 256;   // 205,568
+constexpr uint32_t BAR_OFF = GEO_OFF + 2 * GEO_PART;      // 213,760
+// mbarriers: weights | ready8 | readyA | mbarT | geoR | acc[8] | xbar[8] | dbar[2]
+constexpr int NBAR = 5 + 8 + 8 + 2;
+constexpr uint32_t SMEM_BYTES = BAR_OFF + 8 * NBAR + 16;
 constexpr uint32_t COL_H = 16, COL_D = 144;               // K offsets inside X
-// ---- tensor memory map (columns) ----
-constexpr uint32_t TM_M12_HI = 0, TM_M12_LO = 104, TM_DA = 208, TM_DB = 336, TM_DC = 464, TM_COLS = 512;   // DA 128, DB 128, DC 32
+// ---- tensor memory map (columns): M12g hi | lo (A operand of t0), T0 = the distance encoder's accumulators (stacked
+// form, 128) until d2 has been read, then t0's; DENSE = the eight dense layers' accumulators (16 columns each), later
+// t1's; SLICE = the current h_l as fp16 pairs (hi 8 columns | lo 8 columns); LG = the logits (DENSE and T0 already
+// belong to the next tile by then) ----
+constexpr uint32_t TM_M12_HI = 0, TM_M12_LO = 104, TM_T0 = 208, TM_DENSE = 336, TM_SLICE = 464, TM_LG = 480, TM_COLS = 512;
 constexpr uint32_t M12_GLOBAL = W_BYTES, M12_PART = 128 * 104 * 4;
 
 #ifdef PF_PROF   // dev builds only: per-stage clock64() totals of CTA 0 (epilogue thread 0 and the MMA thread), tc.cuh
@@ -62,16 +95,23 @@ __global__ void __launch_bounds__(NT, 1)
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     uint64_t* wbar = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
-    uint64_t* mbar = wbar + 1;
-    uint64_t* ready = wbar + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wbar + 3);
+    uint64_t* ready8 = wbar + 1;      // both warpgroups published (t0, t1): 8 warp arrivals
+    uint64_t* readyA = wbar + 2;      // warpgroup 0 wrote the slice h_l to tensor memory: 4 warp arrivals
+    uint64_t* mbarT = wbar + 3;       // tcgen05.commit: t0 complete / t1 / logits
+    uint64_t* geoR = wbar + 4;        // both warpgroups wrote the geo slice of the NEXT tile: 8 warp arrivals
+    uint64_t* accbar = wbar + 5;      // [8] tcgen05.commit: dense layer l's accumulator complete (once per tile each)
+    uint64_t* xbar = wbar + 13;       // [8] warpgroup 1 published: d1 | d2 (+ copies of h0, h1) | copy of h2 | .. | h7
+    uint64_t* dbar = wbar + 21;       // [2] tcgen05.commit: d1 / d2 accumulator complete
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wbar + NBAR);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const bool is_mma_warp = warp == 8;
     const int e = tid & 127;          // row of the tile (TMEM lane)
-    const int half = (warp >> 2) & 1;  // which half of every stage's columns this epilogue warpgroup handles
+    const int half = (warp >> 2) & 1;  // epilogue warpgroup: 0 = dense chain, 1 = side work; column halves elsewhere
 
     if (tid == 0) {
-        mbar_init(wbar, 1), mbar_init(mbar, 1), mbar_init(ready, 8);   // ready: one arrive per epilogue warp
+        mbar_init(wbar, 1), mbar_init(ready8, 8), mbar_init(readyA, 4), mbar_init(mbarT, 1), mbar_init(geoR, 8);
+        for (int i = 0; i < 8; i++) mbar_init(accbar + i, 1), mbar_init(xbar + i, 4);
+        mbar_init(dbar, 1), mbar_init(dbar + 1, 1);
         mbar_fence_init();
     }
     if (warp == 0) tc::tmem_alloc(tmem_slot, TM_COLS);
@@ -112,85 +152,126 @@ __global__ void __launch_bounds__(NT, 1)
     const uint32_t x_hi = sbase + X_OFF, x_lo = x_hi + X_PART;
     const long long stride = gridDim.x;
     long long t = blockIdx.x;
+    const bool split = prec == PF_PREC_FP32_SPLIT;           // PF_PREC_FP16: the activations' lo products are dropped
 
     if (is_mma_warp) {
         tc::mbar_wait_bounded(wbar, 0);
         if (tc::elect_one()) {
-            // Split products.  3-pass form (t0): al.bh, ah.bl, then ah.bh (full magnitude last, see tc.cuh).  2-MMA form for
-            // the narrow layers: hi and lo of a weight matrix are adjacent 8-row groups of ONE K-major operand, so
-            // ah . [bh | bl] is a single MMA of width 2n (big term in columns [0, n), ah.bl in [n, 2n)), and al . bh
-            // accumulates into [n, 2n); the epilogue adds the two halves.  A third fewer instructions to issue (the
-            // N = 16 layers are issue-bound, not tensor-bound) and the small terms never meet the big accumulator.
+            // Stacked form for the narrow products: a_hi . [b_hi | b_lo] is one MMA of width 2n (big term in columns [0, n),
+            // a_hi . b_lo in [n, 2n)), a_lo . b_hi accumulates into [n, 2n); the epilogue adds the two halves.
             auto issue2 = [&](uint32_t d, uint64_t ah, uint64_t al, uint32_t a_step, uint64_t bh, uint32_t b_step, int ks,
                               uint32_t idesc_2n, uint32_t idesc_n, uint32_t n) {
 #pragma unroll
                 for (int s = 0; s < ks; s++) tc::mma_f16(d, ah + a_step * s, bh + b_step * s, idesc_2n, s > 0);
-                if (prec == PF_PREC_FP32_SPLIT) {     // reduced precision: the activations' lo products are dropped
+                if (split) {
 #pragma unroll
                     for (int s = 0; s < ks; s++) tc::mma_f16(d + n, al + a_step * s, bh + b_step * s, idesc_n, 1);
                 }
             };
             auto wdesc = [&](uint32_t off, uint32_t kt) { return tc::smem_desc(sbase + off, kt * 16); };
             const uint64_t xh = tc::smem_desc(x_hi, X_SBO), xl = tc::smem_desc(x_lo, X_SBO);
-            const uint32_t d_a = tmem_base + TM_DA, d_b = tmem_base + TM_DB, d_c = tmem_base + TM_DC;
-            constexpr uint32_t i64 = tc::idesc_f16(128, 64), i16 = tc::idesc_f16(128, 16), i128 = tc::idesc_f16(128, 128),
-                               i32 = tc::idesc_f16(128, 32), AT = 1u << 15;
-            uint32_t rphase = 0;
+            const uint64_t gh = tc::smem_desc(sbase + GEO_OFF, GEO_SBO), gl = tc::smem_desc(sbase + GEO_OFF + GEO_PART, GEO_SBO);
+            const uint32_t d_t0 = tmem_base + TM_T0, d_dense = tmem_base + TM_DENSE, slice = tmem_base + TM_SLICE;
+            const uint32_t d_lg = tmem_base + TM_LG;
+            constexpr uint32_t i64 = tc::idesc_f16(128, 64), i128 = tc::idesc_f16(128, 128), i32 = tc::idesc_f16(128, 32),
+                               AT = 1u << 15;
+            uint32_t p8 = 0, pA = 0, pG = 0, tp = 0;         // parities: ready8, readyA, geoR (running), per-tile barriers
             PROF_DECL
-            auto wait_ready = [&]() {
+            auto wait_bar = [&](uint64_t* bar, uint32_t parity) {
                 PROF_TICK(1)
-                tc::mbar_wait_bounded(ready, rphase);
-                rphase ^= 1;
+                tc::mbar_wait_bounded(bar, parity);
                 tc::fence_after_sync();
                 PROF_TICK(0)
             };
-            // One K-step (16 columns of X) of t0^T = M12g . X^T, A from tensor memory (8 columns per K-step): the cross terms go
-            // to the d-branch's accumulator (dead after stage 2), the hi . hi term to d_a; the epilogue adds the two.  The 13
-            // K-steps are issued as their X columns become final, BEHIND the dense chain's own MMAs of each stage, so that
-            // the tensor pipe works on them while the epilogue warps turn the chain around; only h6 / h7 are left for stage 9.
+            // One K-step (16 columns of X) of t0^T = M12g . X^T, A from tensor memory (8 columns per K-step), 3 split
+            // products, the small cross terms first.  K-step 0 = geo, 1 + j = h_j, 9..12 = d2.
             const uint32_t mh = tmem_base + TM_M12_HI, ml = tmem_base + TM_M12_LO;
             auto t0_step = [&](int s, bool first) {
-                tc::mma_f16_ts(d_b, ml + 8u * s, xh + 16u * s, i128, first ? 0u : 1u);
-                if (prec == PF_PREC_FP32_SPLIT) tc::mma_f16_ts(d_b, mh + 8u * s, xl + 16u * s, i128, 1);
-                tc::mma_f16_ts(d_a, mh + 8u * s, xh + 16u * s, i128, first ? 0u : 1u);
+                const uint64_t bh = s == 0 ? gh : xh + 16u * s, bl = s == 0 ? gl : xl + 16u * s;
+                tc::mma_f16_ts(d_t0, ml + 8u * s, bh, i128, first ? 0u : 1u);
+                if (split) tc::mma_f16_ts(d_t0, mh + 8u * s, bl, i128, 1);
+                tc::mma_f16_ts(d_t0, mh + 8u * s, bh, i128, 1);
             };
-            for (; t < total_tiles; t += stride) {
-                // 1: d1, h0 from the geo slice
-                wait_ready();
-                issue2(d_b, xh, xl, 16, wdesc(W_D1, 16), 16, 1, i128, i64, 64);
-                issue2(d_c, xh, xl, 16, wdesc(wh_off(0), 16), 16, 1, i32, i16, 16);
-                tc::commit(mbar);
-                // 2: d2 (A = X columns [144, 208)), h1
-                wait_ready();
-                issue2(d_b, xh + (COL_D / 8) * 8, xl + (COL_D / 8) * 8, 16, wdesc(W_D2, 64), 16, 4, i128, i64, 64);
-                issue2(d_c, xh, xl, 16, wdesc(wh_off(1), 32), 16, 2, i32, i16, 16);
-                tc::commit(mbar);
-                // 3..8: h_l
-#pragma unroll
-                for (int l = 2; l < 8; l++) {
-                    wait_ready();
-                    issue2(d_c, xh, xl, 16, wdesc(wh_off(l), 16 + 16 * l), 16, l + 1, i32, i16, 16);
-                    tc::commit(mbar);
-                    // t0 K-steps whose columns are final: 0 = geo, 1 + j = h_j (published before stage j + 2), 9..12 = d2
-                    // (published before this loop; d_b is free from here on)
-                    if (l == 2) t0_step(0, true), t0_step(1, false);
-                    else if (l < 7) t0_step(l - 1, false), t0_step(l + 6, false);
-                    else t0_step(6, false);
+            // The head of a tile, issued under the tail of the tile before it: the geo part of all eight dense layers (N = 128)
+            // and d1.  DENSE (t1's accumulator, read before t1 was published) and T0 are free by then.
+            auto issue_head = [&]() {
+                wait_bar(geoR, pG), pG ^= 1;
+                const uint64_t bh = wdesc(W_H, 16), bl = wdesc(W_H + WG_PART, 16);
+                tc::mma_f16(d_dense, gh, bl, i128, 0);
+                if (split) tc::mma_f16(d_dense, gl, bh, i128, 1);
+                tc::mma_f16(d_dense, gh, bh, i128, 1);
+                tc::commit(accbar + 0);
+                issue2(d_t0, gh, gl, 16, wdesc(W_D1, 16), 16, 1, i128, i64, 64);
+                tc::commit(dbar + 0);
+            };
+            // Work that does not gate the dense chain, in the order warpgroup 1 makes it possible (xbar[i] complete = d1 | d2,
+            // h0, h1 | h2 | .. | h7 are in X): item 0 = d2 = d1 . Wd3 (A = X columns [144, 208)), items 1..13 = t0's K-steps
+            // geo, h0, h1, d2 x 4, h2 .. h7.  Behind every chain group up to `budget` items whose inputs are there are issued;
+            // the barriers are only TESTED (mbarrier.test_wait), so a late warpgroup 1 never stalls the chain.
+            constexpr int NSIDE = 14;
+            int side = 0, xdone = 0;
+            auto side_work = [&](int budget, bool drain) {
+                while (side < NSIDE && budget > 0) {
+                    const int need = side == 0 ? 0 : (side <= 7 ? 1 : side - 6);
+                    while (xdone <= need) {
+                        if (drain) tc::mbar_wait_bounded(xbar + xdone, tp);
+                        else if (!mbar_test(xbar + xdone, tp)) break;
+                        xdone++;
+                        tc::fence_after_sync();
+                    }
+                    if (xdone <= need) break;
+                    if (side == 0) {
+                        issue2(d_t0, xh + (COL_D / 8) * 8, xl + (COL_D / 8) * 8, 16, wdesc(W_D2, 64), 16, 4, i128, i64, 64);
+                        tc::commit(dbar + 1);
+                        budget -= 3;
+                    } else {
+                        t0_step(side <= 3 ? side - 1 : (side <= 7 ? side + 5 : side - 5), side == 1);
+                        budget -= 1;
+                    }
+                    side++;
                 }
-                // 9: the rest of t0^T: h6, h7
-                wait_ready();
-                t0_step(7, false), t0_step(8, false);
-                tc::commit(mbar);
+            };
+            if (t < total_tiles) issue_head();
+            for (; t < total_tiles; t += stride, tp ^= 1) {
+                side = 0, xdone = 0;
+                // dense groups m = 0..6: h_m (tensor-memory slice) x the h_m columns of layers m+1..7; behind each, work
+                // that does not gate the chain (its inputs were published at least a stage earlier)
+#pragma unroll
+                for (int m = 0; m < 7; m++) {
+                    wait_bar(readyA, pA), pA ^= 1;
+                    {
+                        const uint64_t bh = wdesc(ws_off(m), 16), bl = wdesc(ws_off(m) + ws_part(m), 16);
+                        const uint32_t d = d_dense + 16u * (m + 1), idesc = tc::idesc_f16(128, 16 * (7 - m));
+                        tc::mma_f16_ts(d, slice, bl, idesc, 1);
+                        if (split) tc::mma_f16_ts(d, slice + 8, bh, idesc, 1);
+                        tc::mma_f16_ts(d, slice, bh, idesc, 1);
+                        tc::commit(accbar + m + 1);
+                    }
+                    side_work(3, false);
+                }
+                side_work(1 << 20, true);                   // whatever is left: at least h7's K-step
+                tc::commit(mbarT);
                 // 10: t1 = t0 . W3^T, A = t0 M-major (8-edge groups 128 B apart, 8-channel groups 2048 B apart)
-                wait_ready();
-                issue2(d_a, tc::smem_desc(sbase + T0_OFF, 128, 2048), tc::smem_desc(sbase + T0_OFF + T0_PART, 128, 2048), 256,
+                wait_bar(ready8, p8), p8 ^= 1;
+                issue2(d_dense, tc::smem_desc(sbase + T0_OFF, 128, 2048), tc::smem_desc(sbase + T0_OFF + T0_PART, 128, 2048), 256,
                        wdesc(W_3, 128), 16, 8, i128 | AT, i64 | AT, 64);
-                tc::commit(mbar);
-                // 11: logits = t1 . W6^T
-                wait_ready();
-                issue2(d_a, tc::smem_desc(sbase + T1_OFF, T1_SBO), tc::smem_desc(sbase + T1_OFF + T1_PART, T1_SBO), 16,
-                       wdesc(W_6, 64), 16, 4, i64, i32, 32);
-                tc::commit(mbar);
+                tc::commit(mbarT);
+                // 11: logits = t1 . W6^T: three split products into one 32-column accumulator of their own
+                wait_bar(ready8, p8), p8 ^= 1;
+                {
+                    const uint64_t ah = tc::smem_desc(sbase + T1_OFF, T1_SBO), al = tc::smem_desc(sbase + T1_OFF + T1_PART, T1_SBO);
+                    const uint64_t bh = wdesc(W_6, 64), bl = bh + (uint64_t)((32u * 64u * 2u) >> 4);
+#pragma unroll
+                    for (int s = 0; s < 4; s++) tc::mma_f16(d_lg, ah + 16u * s, bl + 16u * s, i32, s > 0);
+                    if (split) {
+#pragma unroll
+                        for (int s = 0; s < 4; s++) tc::mma_f16(d_lg, al + 16u * s, bh + 16u * s, i32, 1);
+                    }
+#pragma unroll
+                    for (int s = 0; s < 4; s++) tc::mma_f16(d_lg, ah + 16u * s, bh + 16u * s, i32, 1);
+                }
+                tc::commit(mbarT);
+                if (t + stride < total_tiles) issue_head();
             }
             PROF_TICK(1)
             PROF_DUMP(16, 2)
@@ -204,8 +285,9 @@ __global__ void __launch_bounds__(NT, 1)
         const float* bd3 = reinterpret_cast<const float*>(smem + B_D3);
         const float* b3 = reinterpret_cast<const float*>(smem + B_3);
         const float* b6 = reinterpret_cast<const float*>(smem + B_6);
-        const uint32_t d_a = tmem_base + TM_DA + lane_sel, d_b = tmem_base + TM_DB + lane_sel, d_c = tmem_base + TM_DC + lane_sel;
-        uint32_t phase = 0;
+        const uint32_t d_t0 = tmem_base + TM_T0 + lane_sel, d_a = tmem_base + TM_DENSE + lane_sel,
+                       slice = tmem_base + TM_SLICE + lane_sel, d_lg = tmem_base + TM_LG + lane_sel;
+        uint32_t phase = 0, tp = 0;                          // mbarT (running), per-tile barriers
         // v[8] -> fp16 hi/lo -> 16-byte chunk `chunk` of this thread's row of X
         auto store8 = [&](uint32_t chunk, const float* v) {
             uint32_t hi[4], lo[4];
@@ -215,17 +297,26 @@ __global__ void __launch_bounds__(NT, 1)
             *reinterpret_cast<uint4*>(xl_p + x_row + chunk * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         };
         // This warp's operand rows are written and its accumulator reads are done.  No block barrier: epilogue threads never
-        // read each other's shared-memory writes (only the MMA does), and the MMA warp waits for all 8 warps' arrivals.
-        auto publish = [&]() {
+        // read each other's shared-memory writes (only the MMA does), and the MMA warp waits for the warps' arrivals.
+        auto publish = [&](uint64_t* bar) {
             tc::fence_async_smem();
             tc::fence_before_sync();
             __syncwarp();
-            if (lane == 0) mbar_arrive(ready);
+            if (lane == 0) mbar_arrive(bar);
         };
-        auto wait_mma = [&]() {
-            tc::mbar_wait_bounded(mbar, phase);
-            phase ^= 1;
+        auto wait_bar = [&](uint64_t* bar, uint32_t parity) {
+            tc::mbar_wait_bounded(bar, parity);
             tc::fence_after_sync();
+        };
+        auto wait_tail = [&]() {
+            wait_bar(mbarT, phase);
+            phase ^= 1;
+        };
+        // dense layer l of this thread's edge: accumulator -> LeakyReLU (the bias rode on geo's constant 1)
+        auto dense_act = [&](int l, float (&a)[16]) {
+            tc::ld16(d_a + 16u * l, a);
+#pragma unroll
+            for (int u = 0; u < 16; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
         };
         tc::mbar_wait_bounded(wbar, 0);   // biases live in the weight blob
 
@@ -239,98 +330,116 @@ __global__ void __launch_bounds__(NT, 1)
         int p0_n = 0, j_n = 0;
         size_t row_i_n = 0, base_n = 0;
         float xi_n[3] = {0.f, 0.f, 0.f}, xj_n[3] = {0.f, 0.f, 0.f};
+        // geo slice of the tile whose coordinates are in xi_n / xj_n -> its own buffer; warpgroup 0 writes columns 0..7,
+        // warpgroup 1 columns 8..15
+        auto geo_publish = [&]() {
+            const float dx = xi_n[0] - xj_n[0], dy = xi_n[1] - xj_n[1], dz = xi_n[2] - xj_n[2];
+            const float dist = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+            const float g0[8] = {xi_n[0], xi_n[1], xi_n[2], xj_n[0], xj_n[1], xj_n[2], -dx, -dy};
+            const float g1[8] = {-dz, dist, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            const float* g = half == 0 ? g0 : g1;
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) tc::split2(g[2 * u], g[2 * u + 1], hi[u], lo[u]);
+            uint8_t* dst = smem + GEO_OFF + (uint32_t)(e >> 3) * GEO_SBO + (uint32_t)half * 128 + (uint32_t)(e & 7) * 16;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + GEO_PART) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            publish(geoR);
+        };
         if (t < total_tiles) {
             base_n = tile_rows(t, p0_n, row_i_n);
             j_n = min(max(__ldg(idx + row_i_n * ldidx + (e & 7)), 0), N - 1);
 #pragma unroll
             for (int a = 0; a < 3; a++) xi_n[a] = __ldg(xyz + row_i_n * 3 + a), xj_n[a] = __ldg(xyz + (base_n + j_n) * 3 + a);
+            geo_publish();
         }
         PROF_DECL
-        for (; t < total_tiles; t += stride) {
+        for (; t < total_tiles; t += stride, tp ^= 1) {
             const int p0 = p0_n;
             const size_t row_i = row_i_n, row_j = base_n + j_n;
-            const float xi0 = xi_n[0], xi1 = xi_n[1], xi2 = xi_n[2], xj0 = xj_n[0], xj1 = xj_n[1], xj2 = xj_n[2];
             const bool has_next = t + stride < total_tiles;
             int j_raw = 0;
             if (has_next) {
                 base_n = tile_rows(t + stride, p0_n, row_i_n);
-                j_raw = __ldg(idx + row_i_n * ldidx + (e & 7));             // consumed after stage 2 below
+                j_raw = __ldg(idx + row_i_n * ldidx + (e & 7));             // consumed after the first chain stage below
 #pragma unroll
                 for (int a = 0; a < 3; a++) xi_n[a] = __ldg(xyz + row_i_n * 3 + a);
             }
-            // ---- geo slice ----
-            {
-                const float dx = xi0 - xj0, dy = xi1 - xj1, dz = xi2 - xj2;
-                const float dist = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
-                const float g0[8] = {xi0, xi1, xi2, xj0, xj1, xj2, -dx, -dy};
-                const float g1[8] = {-dz, dist, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                if (half == 0) store8(0, g0); else store8(1, g1);
-            }
-            publish();
             PROF_TICK(0)
-            // ---- 1: d1 -> X[:, 144:208), h0 -> X[:, 16:32) ----
-            wait_mma();
-            PROF_TICK(1)
-            {
-                const int c = half;
-                float a[32], b[32];                                      // big half, small half (see issue2)
-                tc::ld32(d_b + 32 * c, a), tc::ld32(d_b + 64 + 32 * c, b);
-#pragma unroll
-                for (int u = 0; u < 32; u++) a[u] = lrelu((a[u] + b[u]) * tc::WINV, S_DEF);
-#pragma unroll
-                for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
-            }
-            {
-                float a[8];
-                tc::ld8_sum(d_c + 8 * half, d_c + 16 + 8 * half, a);
-#pragma unroll
-                for (int u = 0; u < 8; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
-                store8(COL_H / 8 + half, a);
-            }
-            publish();
-            PROF_TICK(2)
-            // ---- 2: d2 (overwrites d1), h1 ----
-            wait_mma();
-            PROF_TICK(3)
-            {
-                const int c = half;
-                float a[32], b[32];
-                tc::ld32(d_b + 32 * c, a), tc::ld32(d_b + 64 + 32 * c, b);
-#pragma unroll
-                for (int u = 0; u < 32; u++) a[u] = lrelu(fmaf(a[u] + b[u], tc::WINV, bd3[32 * c + u]), S_DEF);
-#pragma unroll
-                for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
-            }
-            if (has_next) {                                              // second hop of the prefetch: x_j of the next tile
-                j_n = min(max(j_raw, 0), N - 1);
-#pragma unroll
-                for (int a = 0; a < 3; a++) xj_n[a] = __ldg(xyz + (base_n + j_n) * 3 + a);
-            }
+            if (half == 0) {
+                // ---- warpgroup 0: the dense chain.  h_l -> tensor-memory slice (hi 8 columns | lo 8 columns) ----
 #pragma unroll 1
-            for (int l = 1; l < 8; l++) {
-                if (l > 1) {
-                    wait_mma();
-                    PROF_TICK(5)
-                }
-                float a[8];
-                tc::ld8_sum(d_c + 8 * half, d_c + 16 + 8 * half, a);
+                for (int l = 0; l < 7; l++) {
+                    wait_bar(accbar + l, tp);
+                    PROF_TICK(1)
+                    float a[16];
+                    dense_act(l, a);
+                    uint32_t hi[8], lo[8];
 #pragma unroll
-                for (int u = 0; u < 8; u++) a[u] = lrelu(a[u] * tc::WINV, S_CTX);
-                store8(COL_H / 8 + 2 * l + half, a);
-                publish();
-                if (l > 1) { PROF_TICK(6) } else { PROF_TICK(4) }
+                    for (int u = 0; u < 8; u++) tc::split2(a[2 * u], a[2 * u + 1], hi[u], lo[u]);
+                    tc::st8_nowait(slice, hi);
+                    tc::st8_nowait(slice + 8, lo);
+                    tc::tmem_st_wait();
+                    tc::fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(readyA);
+                    PROF_TICK(2)
+                    if (l == 0 && has_next) {                                // second hop of the prefetch: x_j of the next tile
+                        j_n = min(max(j_raw, 0), N - 1);
+#pragma unroll
+                        for (int a2 = 0; a2 < 3; a2++) xj_n[a2] = __ldg(xyz + (base_n + j_n) * 3 + a2);
+                    }
+                }
+            } else {
+                // ---- warpgroup 1: distance encoder and the shared-memory copies of the slices (B operand of t0) ----
+                auto d_stage = [&](bool with_bias) {                         // d1 / d2 -> X[:, 144:208)
+#pragma unroll 1
+                    for (int c = 0; c < 2; c++) {
+                        float a[32], b[32];                                  // big half, small half (stacked form)
+                        tc::ld32(d_t0 + 32 * c, a), tc::ld32(d_t0 + 64 + 32 * c, b);
+#pragma unroll
+                        for (int u = 0; u < 32; u++)
+                            a[u] = lrelu(fmaf(a[u] + b[u], tc::WINV, with_bias ? bd3[32 * c + u] : 0.f), S_DEF);
+#pragma unroll
+                        for (int u = 0; u < 4; u++) store8(COL_D / 8 + 4 * c + u, a + 8 * u);
+                    }
+                };
+                auto copy_slice = [&](int l) {
+                    wait_bar(accbar + l, tp);
+                    float a[16];
+                    dense_act(l, a);
+                    store8(COL_H / 8 + 2 * l, a), store8(COL_H / 8 + 2 * l + 1, a + 8);
+                };
+                wait_bar(dbar + 0, tp);
+                d_stage(false);
+                publish(xbar + 0);
+                if (has_next) {
+                    j_n = min(max(j_raw, 0), N - 1);
+#pragma unroll
+                    for (int a2 = 0; a2 < 3; a2++) xj_n[a2] = __ldg(xyz + (base_n + j_n) * 3 + a2);
+                }
+                copy_slice(0), copy_slice(1);
+                wait_bar(dbar + 1, tp);
+                d_stage(true);
+                publish(xbar + 1);
+#pragma unroll 1
+                for (int l = 2; l < 8; l++) {
+                    copy_slice(l);
+                    publish(xbar + l);
+                }
             }
+            PROF_TICK(3)
             // ---- 9: t0^T: thread = channel e; write t0 back as an M-major operand (aliases X, dead now) ----
-            wait_mma();
-            PROF_TICK(7)
+            wait_tail();
+            PROF_TICK(4)
             {
                 uint8_t* th = smem + T0_OFF + (uint32_t)(e >> 3) * 2048 + (uint32_t)(e & 7) * 16;
 #pragma unroll 1
                 for (int c = 2 * half; c < 2 * half + 2; c++) {
-                    float a[32], b[32];                                  // hi . hi part, cross terms (t0_step)
-                    tc::ld32(d_a + 32 * c, a), tc::ld32(d_b + 32 * c, b);
+                    float a[32];
+                    tc::ld32(d_t0 + 32 * c, a);
 #pragma unroll
-                    for (int u = 0; u < 32; u++) a[u] = lrelu((a[u] + b[u]) * tc::WINV, S_DEF);
+                    for (int u = 0; u < 32; u++) a[u] = lrelu(a[u] * tc::WINV, S_DEF);
 #pragma unroll
                     for (int g = 0; g < 4; g++) {
                         uint32_t hi[4], lo[4];
@@ -341,11 +450,11 @@ __global__ void __launch_bounds__(NT, 1)
                     }
                 }
             }
-            publish();
-            PROF_TICK(8)
+            publish(ready8);
+            PROF_TICK(5)
             // ---- 10: t1 (thread = edge again) -> K-major operand ----
-            wait_mma();
-            PROF_TICK(9)
+            wait_tail();
+            PROF_TICK(6)
             {
                 uint8_t* t1h = smem + T1_OFF + (uint32_t)(e >> 3) * T1_SBO + (uint32_t)(e & 7) * 16;
                 {
@@ -364,33 +473,33 @@ __global__ void __launch_bounds__(NT, 1)
                     }
                 }
             }
-            publish();
-            PROF_TICK(10)
-            // ---- 11: logits -> softmax over the 8 neighbours (8 consecutive lanes) -> weighted latent sum ----
-            const float z0 = __ldg(z + row_j * 3), z1 = __ldg(z + row_j * 3 + 1), z2 = __ldg(z + row_j * 3 + 2);
-            wait_mma();
-            PROF_TICK(11)
-            {
-                constexpr int RH = RP / 2;                                 // logits per warpgroup: r in [r0, r0 + RH)
-                const int r0 = half * RH;
-                float lg[RH];
-                if constexpr (RH == 16) {
-                    float a16[16], s16[16];
-                    tc::ld16(d_a + r0, a16), tc::ld16(d_a + 32 + r0, s16);
-#pragma unroll
-                    for (int r = 0; r < RH; r++) lg[r] = a16[r] + s16[r];
+            publish(ready8);
+            if (has_next) geo_publish();                                   // the next tile's head runs under this tile's last stage
+            PROF_TICK(7)
+            // ---- 11: logits -> softmax over the 8 neighbours (8 consecutive lanes) -> weighted latent sum: warpgroup 1 alone
+            // (R is small); warpgroup 0 goes straight to the next tile's dense chain, whose head is already in flight ----
+            if (half == 0) {
+                phase ^= 1;                                                // the logits phase of mbarT, not waited for
+            } else {
+                const float z0 = __ldg(z + row_j * 3), z1 = __ldg(z + row_j * 3 + 1), z2 = __ldg(z + row_j * 3 + 2);
+                wait_tail();
+                PROF_TICK(8)
+                float lg[RP];
+                if constexpr (RP == 32) {
+                    tc::ld32(d_lg, lg);
+                } else if constexpr (RP == 16) {
+                    tc::ld16(d_lg, lg);
                 } else {
-                    float a8[8], s8[8];
-                    tc::ld8(d_a + r0, a8), tc::ld8(d_a + 32 + r0, s8);
+                    float a8[8];
+                    tc::ld8(d_lg, a8);
 #pragma unroll
-                    for (int r = 0; r < RH; r++) lg[r] = a8[r] + s8[r];
+                    for (int r = 0; r < RP; r++) lg[r] = a8[r];
                 }
                 const bool writer = (e & 7) == 0 && (p0 + (e >> 3)) < N;
                 float* dst = out + row_i * R * 3;
 #pragma unroll
-                for (int rr = 0; rr < RH; rr++) {
-                    const int r = r0 + rr;
-                    float v = fmaf(lg[rr], tc::WINV, b6[r]);
+                for (int r = 0; r < RP; r++) {
+                    float v = fmaf(lg[r], tc::WINV, b6[r]);
                     float mx = v;
 #pragma unroll
                     for (int o = 1; o < 8; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -410,10 +519,11 @@ __global__ void __launch_bounds__(NT, 1)
                 }
             }
             // no barrier at the tile end either: every MMA that reads X / t0 / t1 has completed (the logits commit was waited
-            // for), and the next tile's first MMA is issued only after all 8 warps have arrived again
-            PROF_TICK(12)
+            // for); the next tile's head, already issued, touches only the geo buffer, DENSE and T0
+            PROF_TICK(9)
         }
-        if (tid == 0) { PROF_DUMP(0, 13) }
+        if (tid == 0) { PROF_DUMP(0, 10) }
+        if (tid == 128) { PROF_DUMP(20, 10) }
     }
     tc::fence_before_sync();
     __syncthreads();

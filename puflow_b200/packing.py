@@ -221,8 +221,9 @@ def pack_interp_tc(sd):
         geo = [x_i (3) | x_j (3) | x_j - x_i (3) | |x_i - x_j| | 1 | 0 x 5],
     with the reference's UNFOLDED weights (no (W1-W3) x_i + (W2+W3) x_j cancellation) and the bias on the constant 1.
     Shared-memory part (B operands, [N][K] K-major, fp16 hi then lo each):
-        Wd1g[64][16] | Wd2[64][64] | Wh_l[16][16+16l] (l = 0..7, K = geo | h_<l) | W3[64][128] | W6[32][64]
-        | fp32 bd3[64] | b3[64] | b6[32]
+        Wd1g[64][16] | Wd2[64][64] | Wg[128][16] (the geo columns of the eight dense layers, layer l = rows 16l..)
+        | S_m[16 (7 - m)][16] (m = 0..6: the h_m columns of layers m+1..7 -- the kernel multiplies every new slice h_m
+        against all later layers at once) | W3[64][128] | W6[32][64] | fp32 bd3[64] | b3[64] | b6[32]
     Tensor-memory part (A operand of the transposed composed layer, plain row-major fp16 [128][208], hi then lo):
         M12g = [geo part | M2 (h, 128) | M1 (d2, 64)]."""
     p = "interp.knn_context.distance_encoder.mlp"
@@ -246,9 +247,13 @@ def pack_interp_tc(sd):
     add(geo(Wd0[:, 0:3], Wd0[:, 3:6], -Wd0[:, 6:9], Wd0[:, 9], bd0))          # d1 = lrelu(Wd1g . geo)
     add(Wd3)                                                                     # d2 = lrelu(Wd3 . d1 + bd3)
     fc = "interp.knn_context.feat_conv"
+    full = []                                                                    # layer l on [geo (16) | h_0 .. h_{l-1}]
     for l in range(8):
         W, b = _conv_bn(sd, f"{fc}.convs.{l}.0", f"{fc}.convs.{l}.1")           # [16, 9 + 16 l]
-        add(torch.cat([geo(W[:, 0:3], W[:, 3:6], W[:, 6:9], None, b), W[:, 9:]], dim=1))
+        full.append(torch.cat([geo(W[:, 0:3], W[:, 3:6], W[:, 6:9], None, b), W[:, 9:]], dim=1))
+    add(torch.cat([w[:, 0:16] for w in full]))                                   # geo slice of all eight layers [128, 16]
+    for m in range(7):                                                           # S_m: h_m's columns of layers m+1..7
+        add(torch.cat([full[j][:, 16 + 16 * m:32 + 16 * m] for j in range(m + 1, 8)]))
     Wco, bco = _conv_bn(sd, f"{fc}.conv_out")                                   # [128, 9 + 128]
     q = "interp.weight_unit.mlp"
     W0, b0 = _conv_bn(sd, q + ".0", q + ".1")              # [128,256] on [dist feats 128 | context feats 128]

@@ -19,11 +19,13 @@ lib = _native.lib if hasattr(_native, "lib") else _native._lib
 lib.pf_debug_interp_prof.argtypes = [ctypes.c_void_p]
 assert lib.pf_debug_interp_prof(buf) == 0
 v = list(buf)
-names = ["geo+publish", "wait s1", "epi d1/h0", "wait s2", "epi d2/h1", "wait h2..7", "epi h2..7", "wait t0", "epi t0",
-         "wait t1", "epi t1", "wait logits", "softmax+store+bar"]
+names = ["geo+publish", "chain: wait acc", "chain: act+slice+publish", "(side work / chain end)", "wait t0", "epi t0",
+         "wait t1", "epi t1", "wait logits", "softmax+store"]
 tiles = -(-Bp * N // 16) // 148 + 1
-tot = sum(v[:13])
-print(f"epilogue thread 0 of CTA 0: {tot} cycles total, ~{tiles} tiles -> {tot / tiles:.0f} cycles per tile")
-for n, c in zip(names, v[:13]):
-    print(f"  {n:20s} {c / tiles:8.0f} cyc/tile  {100 * c / tot:5.1f}%")
-print(f"MMA thread: issue {v[16] / tiles:.0f} cyc/tile, wait {v[17] / tiles:.0f} cyc/tile")
+for base, who in ((0, "warpgroup 0 (dense chain), thread 0"), (20, "warpgroup 1 (side work), thread 128")):
+    tot = sum(v[base:base + 10])
+    print(f"{who} of CTA 0: {tot} cycles total, ~{tiles} tiles -> {tot / tiles:.0f} cycles per tile")
+    for n, c in zip(names, v[base:base + 10]):
+        print(f"  {n:28s} {c / tiles:8.0f} cyc/tile  {100 * c / tot:5.1f}%")
+print("warpgroup 1 softmax split: ld logits", v[30] / tiles, " wait z", v[31] / tiles)
+print(f"MMA thread: wait {v[16] / tiles:.0f} cyc/tile, issue {v[17] / tiles:.0f} cyc/tile")
