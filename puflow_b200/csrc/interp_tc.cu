@@ -24,8 +24,8 @@
 //                h_l's contribution to ALL later layers at once:
 //                    D[128 edges x 16 (7 - l)] += h_l . [W_{l+1,l}; ..; W_{7,l}]^T     (3 MMAs, K = 16)
 //                (the geo slice feeds all eight layers the same way, N = 128), so the critical path of a layer is
-//                three instructions and K = 16, whatever l.  It skips the softmax stage and starts the next tile's chain
-//                while warpgroup 1 finishes the current tile;
+//                three instructions and K = 16, whatever l.  It skips the softmax stage, starts the next tile's chain
+//                while warpgroup 1 finishes the current tile, and does its half of that softmax when the chain is done;
 //   warpgroup 1  everything off that path: the distance encoder (d1, d2), the shared-memory copies of h_l / d2 that t0
 //                reads as its B operand (it re-reads the same accumulator columns; its stores and proxy fences cost the
 //                chain nothing), the softmax + output stage.  Each publish has its own mbarrier (one completion per
@@ -42,9 +42,10 @@
 //  then softmax over the 8 neighbours (8 consecutive lanes) and the weighted sum of the neighbours' latents.
 // Narrow products (d1, d2, t1) use the stacked form: hi and lo of a weight matrix are adjacent row groups of ONE K-major
 // operand, a_hi . [b_hi | b_lo] is a single MMA of width 2n and only a_lo . b_hi remains.
-// 4.17 -> 3.61 ms at config 2; measured and rejected on the way: test_wait spinning on the chain's two waits (no change),
+// 4.17 -> 3.59 ms at config 2 (warpgroup 0 also copies h6 / h7 and does its softmax half one tile late, in the idle time
+// at the end of the next chain); measured and rejected on the way: test_wait spinning on the chain's two waits (no change),
 // warpgroup 0 writing the X copies itself from its hi/lo registers (the chain's stage grows by 165 cycles: 3.75 ms),
-// d1 of the next tile before the softmax (3.75 ms), five instead of three side items per gap (3.97 ms).
+// d1 of the next tile before the softmax (3.75 ms), four / five instead of three side items per gap (3.62 / 3.97 ms).
 #include "common.cuh"
 #include "puflow_b200.h"
 #include "tc.cuh"
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(NT, 1)
     uint64_t* mbarT = wbar + 3;       // tcgen05.commit: t0 complete / t1 / logits
     uint64_t* geoR = wbar + 4;        // both warpgroups wrote the geo slice of the NEXT tile: 8 warp arrivals
     uint64_t* accbar = wbar + 5;      // [8] tcgen05.commit: dense layer l's accumulator complete (once per tile each)
-    uint64_t* xbar = wbar + 13;       // [8] warpgroup 1 published: d1 | d2 (+ copies of h0, h1) | copy of h2 | .. | h7
+    uint64_t* xbar = wbar + 13;       // [8] published in X: d1 | d2 (+ copies of h0, h1) | copy of h2 | .. | h7 (h6, h7: warpgroup 0)
     uint64_t* dbar = wbar + 21;       // [2] tcgen05.commit: d1 / d2 accumulator complete
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wbar + NBAR);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -353,6 +354,44 @@ __global__ void __launch_bounds__(NT, 1)
             for (int a = 0; a < 3; a++) xi_n[a] = __ldg(xyz + row_i_n * 3 + a), xj_n[a] = __ldg(xyz + (base_n + j_n) * 3 + a);
             geo_publish();
         }
+        // this warpgroup's half of the R logits of a tile whose logits are complete: r in [half RP/2, half RP/2 + RP/2)
+        auto softmax_half = [&](bool writer, float* dst, float z0, float z1, float z2) {
+            constexpr int RH = RP / 2;
+            const int r0 = half * RH;
+            float lg[RH];
+            if constexpr (RH == 16) {
+                tc::ld16(d_lg + r0, lg);
+            } else {
+                float a8[8];
+                tc::ld8(d_lg + r0, a8);
+#pragma unroll
+                for (int r = 0; r < RH; r++) lg[r] = a8[r];
+            }
+#pragma unroll
+            for (int rr = 0; rr < RH; rr++) {
+                const int r = r0 + rr;
+                float v = fmaf(lg[rr], tc::WINV, b6[r]);
+                float mx = v;
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                const float ex = expf(v - mx);
+                float sum = ex;
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                const float w = ex * (1.f / sum);
+                float o0 = w * z0, o1 = w * z1, o2 = w * z2;
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) {
+                    o0 += __shfl_xor_sync(0xffffffffu, o0, o);
+                    o1 += __shfl_xor_sync(0xffffffffu, o1, o);
+                    o2 += __shfl_xor_sync(0xffffffffu, o2, o);
+                }
+                if (writer && r < R) dst[r * 3] = o0, dst[r * 3 + 1] = o1, dst[r * 3 + 2] = o2;
+            }
+        };
+        bool pend = false, pend_writer = false;                            // warpgroup 0: softmax half of the previous tile
+        float* pend_dst = out;
+        float pz0 = 0.f, pz1 = 0.f, pz2 = 0.f;
         PROF_DECL
         for (; t < total_tiles; t += stride, tp ^= 1) {
             const int p0 = p0_n;
@@ -383,12 +422,34 @@ __global__ void __launch_bounds__(NT, 1)
                     tc::fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(readyA);
+                    if (l == 6) {                                            // h6's copy into X from the halves at hand
+                        uint8_t* ph = xh_p + x_row + (COL_H / 8 + 12) * 128;
+                        uint8_t* pl = xl_p + x_row + (COL_H / 8 + 12) * 128;
+                        *reinterpret_cast<uint4*>(ph) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                        *reinterpret_cast<uint4*>(ph + 128) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                        *reinterpret_cast<uint4*>(pl) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                        *reinterpret_cast<uint4*>(pl + 128) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                        publish(xbar + 6);
+                    }
                     PROF_TICK(2)
                     if (l == 0 && has_next) {                                // second hop of the prefetch: x_j of the next tile
                         j_n = min(max(j_raw, 0), N - 1);
 #pragma unroll
                         for (int a2 = 0; a2 < 3; a2++) xj_n[a2] = __ldg(xyz + (base_n + j_n) * 3 + a2);
                     }
+                }
+                // the chain is done; what is left costs nobody anything: h7's copy into X (warpgroup 1 is the busier one),
+                // then this warpgroup's softmax half of the PREVIOUS tile
+                {
+                    wait_bar(accbar + 7, tp);
+                    float a[16];
+                    dense_act(7, a);
+                    store8(COL_H / 8 + 14, a), store8(COL_H / 8 + 15, a + 8);
+                    publish(xbar + 7);
+                }
+                if (pend) {
+                    softmax_half(pend_writer, pend_dst, pz0, pz1, pz2);
+                    pend = false;
                 }
             } else {
                 // ---- warpgroup 1: distance encoder and the shared-memory copies of the slices (B operand of t0) ----
@@ -423,7 +484,7 @@ __global__ void __launch_bounds__(NT, 1)
                 d_stage(true);
                 publish(xbar + 1);
 #pragma unroll 1
-                for (int l = 2; l < 8; l++) {
+                for (int l = 2; l < 6; l++) {                               // (h6 and h7: warpgroup 0)
                     copy_slice(l);
                     publish(xbar + l);
                 }
@@ -476,47 +537,22 @@ __global__ void __launch_bounds__(NT, 1)
             publish(ready8);
             if (has_next) geo_publish();                                   // the next tile's head runs under this tile's last stage
             PROF_TICK(7)
-            // ---- 11: logits -> softmax over the 8 neighbours (8 consecutive lanes) -> weighted latent sum: warpgroup 1 alone
-            // (R is small); warpgroup 0 goes straight to the next tile's dense chain, whose head is already in flight ----
-            if (half == 0) {
-                phase ^= 1;                                                // the logits phase of mbarT, not waited for
-            } else {
+            // ---- 11: logits -> softmax over the 8 neighbours -> weighted latent sum.  Warpgroup 1 does its half of the logits
+            // now; warpgroup 0 goes straight to the next tile's dense chain (whose head is already in flight) and does its half
+            // in the idle time at the end of that chain -- the logits' accumulator columns are not reused before ----
+            if (half == 1) {
                 const float z0 = __ldg(z + row_j * 3), z1 = __ldg(z + row_j * 3 + 1), z2 = __ldg(z + row_j * 3 + 2);
                 wait_tail();
                 PROF_TICK(8)
-                float lg[RP];
-                if constexpr (RP == 32) {
-                    tc::ld32(d_lg, lg);
-                } else if constexpr (RP == 16) {
-                    tc::ld16(d_lg, lg);
-                } else {
-                    float a8[8];
-                    tc::ld8(d_lg, a8);
-#pragma unroll
-                    for (int r = 0; r < RP; r++) lg[r] = a8[r];
-                }
-                const bool writer = (e & 7) == 0 && (p0 + (e >> 3)) < N;
-                float* dst = out + row_i * R * 3;
-#pragma unroll
-                for (int r = 0; r < RP; r++) {
-                    float v = fmaf(lg[r], tc::WINV, b6[r]);
-                    float mx = v;
-#pragma unroll
-                    for (int o = 1; o < 8; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-                    const float ex = expf(v - mx);
-                    float sum = ex;
-#pragma unroll
-                    for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                    const float w = ex * (1.f / sum);
-                    float o0 = w * z0, o1 = w * z1, o2 = w * z2;
-#pragma unroll
-                    for (int o = 1; o < 8; o <<= 1) {
-                        o0 += __shfl_xor_sync(0xffffffffu, o0, o);
-                        o1 += __shfl_xor_sync(0xffffffffu, o1, o);
-                        o2 += __shfl_xor_sync(0xffffffffu, o2, o);
-                    }
-                    if (writer && r < R) dst[r * 3] = o0, dst[r * 3 + 1] = o1, dst[r * 3 + 2] = o2;
-                }
+                softmax_half((e & 7) == 0 && (p0 + (e >> 3)) < N, out + row_i * R * 3, z0, z1, z2);
+            } else if (has_next) {
+                phase ^= 1;                                                // the logits phase of mbarT, not waited for
+                pend = true, pend_writer = (e & 7) == 0 && (p0 + (e >> 3)) < N, pend_dst = out + row_i * R * 3;
+                pz0 = __ldg(z + row_j * 3), pz1 = __ldg(z + row_j * 3 + 1), pz2 = __ldg(z + row_j * 3 + 2);
+            } else {
+                const float z0 = __ldg(z + row_j * 3), z1 = __ldg(z + row_j * 3 + 1), z2 = __ldg(z + row_j * 3 + 2);
+                wait_tail();
+                softmax_half((e & 7) == 0 && (p0 + (e >> 3)) < N, out + row_i * R * 3, z0, z1, z2);
             }
             // no barrier at the tile end either: every MMA that reads X / t0 / t1 has completed (the logits commit was waited
             // for); the next tile's head, already issued, touches only the geo buffer, DENSE and T0
