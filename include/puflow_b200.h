@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 8
+#define PF_ABI_VERSION 9
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -300,6 +300,25 @@ PF_API int pf_profile_enable(int on);
 PF_API int pf_profile_intervals(void);
 PF_API int pf_profile_interval(int i, char* name40, float* ms);
 PF_API int pf_profile_clear(void);
+
+/* ---- continuous (CNF) variant, inference ------------------------------------------------
+ * pf_cnf_flow replaces one FlowBlock of /root/reference/modules/continuous/interpflow.py:19-50 at inference time
+ * (batch_norm=False: identity norms): CNF.forward (modules/continuous/cnf.py:51-112) -> torchdiffeq.odeint(dopri5) over
+ * ODEfunc / ODEnet / ConcatSquashLinear (modules/continuous/odefunc.py:66-111,121-143, diffeq_layers.py:72-86).
+ *   y_in[M][3] -> y_out[M][3] = y(t1) of dy/dt = ODEnet([t, c], y), y(t0) = y_in; forward pass t0 = 0, t1 = T =
+ *   sqrt_end_time^2, inverse t0 = T, t1 = 0.  Point p uses conditioning row p / rep (rep = 1 forward, = the up-sampling ratio
+ *   on the inverse: the reference's repeat_interleave(c, R)).
+ *   ctx[ceil(M / rep)][ld_ctx >= PF_CNF_CTX]: the c-dependent part of every layer's gate and bias, one row per INPUT point:
+ *   c . Wctx + bctx with (Wctx, bctx, wblob) from puflow_b200/packing.py pack_cnf_block (computed with pf_linear[_tc]).
+ *   wblob: PF_CNF_BLOB bytes.  nfe: NULL or int32[M], function evaluations per point (negative: step budget exhausted).
+ * Adaptive Dormand-Prince 5(4), atol / rtol as the reference passes them (1e-5); every point controls its own step and the
+ * last step is clipped at t1 -- torchdiffeq (absent from the reference tree: solver parity unpinned) uses one batch-wide
+ * error norm and interpolates at t1; oracle/cnf_oracle.py restates both and a solver-independent RK4 reference.
+ * Not built: log p (Hutchinson trace estimate, odefunc.py:8-32) and the backward pass. */
+#define PF_CNF_CTX 264
+#define PF_CNF_BLOB 19520
+PF_API int pf_cnf_flow(const float* y_in, const float* ctx, int ld_ctx, const float* wblob, float* y_out, int32_t* nfe, int M,
+                       int rep, float t0, float t1, float atol, float rtol, void* stream);
 
 /* ---- on-disk format (host code, no CUDA) ------------------------------------------
  * The reference reads clouds with np.loadtxt(path, dtype=np.float32) (/root/reference/modules/discrete/upsample.py:42)

@@ -40,6 +40,7 @@ SIGNATURES = {
     "pf_cond_chain_tc": [_vp, _i, _vp, _vp, _vp, _i64, _i, _vp],
     "pf_interp": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
     "pf_interp_tc": [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp],
+    "pf_cnf_flow": [_vp, _vp, _i, _vp, _vp, _vp, _i, _i, _f, _f, _f, _f, _vp],
     "pf_fps": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_bucketed": [_vp, _i, _i, _i, _vp, _vp, _vp],
     "pf_fps_clustered": [_vp, _i, _i, _i, _vp, _vp, _vp],
@@ -80,7 +81,7 @@ lib.pf_upsample_clouds_workspace_bytes.restype = ctypes.c_int64
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 8
+PF_ABI_VERSION = 9
 PF_MODEL_ENTRIES = 27
 PF_FPS_STATIC_MAX_POINTS = 262144
 PF_COND_BLOB = 8840
@@ -95,6 +96,8 @@ def chain_tc_bytes(C: int) -> int:
 PF_INTERP_BLOB = 46304
 PF_EDGECONV_TC_BLOB = 90112
 PF_INTERP_TC_BLOB = 205440
+PF_CNF_CTX = 264
+PF_CNF_BLOB = 19520
 ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
 PREC_FP32_SPLIT, PREC_FP16 = 0, 1          # PF_PREC_*: precision argument of the tensor-core entry points
 PRECISIONS = {"fp32": PREC_FP32_SPLIT, "fp32_split": PREC_FP32_SPLIT, "fp16": PREC_FP16, 0: 0, 1: 1}

@@ -284,3 +284,73 @@ class PUFlowEngine:
         graph.replay()
         ops.count_launches(n_launch)
         return x.clone(), logp.clone()
+
+
+class CNFEngine(PUFlowEngine):
+    """The continuous variant, inference: PointInterpFlow of /root/reference/modules/continuous/interpflow.py:53-139.  Same
+    conditioner (kNN, six EdgeConv blocks, merge units) and interpolation module as the discrete model -- the same kernels --
+    and six CNF blocks integrated by pf_cnf_flow (csrc/cnf.cu).  log p is not computed (the reference estimates it with a
+    random Hutchinson probe, odefunc.py:8-32; sample() never reads it)."""
+
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device, precision="fp32", atol: float = 1e-5, rtol: float = 1e-5):
+        from ._native import PRECISIONS
+        from .packing import pack_cnf_state_dict
+        if precision not in PRECISIONS:
+            raise ValueError(f"precision {precision!r} not in {sorted(k for k in PRECISIONS if isinstance(k, str))}")
+        self.prec = PRECISIONS[precision]
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError(f"CNFEngine needs a CUDA device, got {self.device} (no CPU fallback)")
+        self.w = pack_cnf_state_dict(state_dict, self.device)
+        self.use_tc, self.flow_tc = True, False
+        self.atol, self.rtol = float(atol), float(rtol)           # cnf.py:37: solver='dopri5', atol = rtol = 1e-5
+        self._graphs, self._model_blob = {}, None
+
+    def contexts(self, cs: List[torch.Tensor]):
+        """The c part of every CNF layer's gate and bias, per INPUT point and block: [M, 272] each."""
+        out = []
+        for i in range(NUM_BLOCKS):
+            b = self.w["cnf"][i]
+            out.append(self._linear(cs[i].reshape(-1, cs[i].shape[-1]), b, "wctx", b["bctx"]))
+        return out
+
+    def f(self, xyz: torch.Tensor, ctxs):
+        """PointInterpFlow.f (continuous/interpflow.py:96-106): blocks 0..5, each integrated over [0, T_i]."""
+        y = xyz.reshape(-1, 3)
+        for i in range(NUM_BLOCKS):
+            b = self.w["cnf"][i]
+            y = ops.cnf_flow(y, ctxs[i], b["blob"], 0.0, b["T"], 1, self.atol, self.rtol)
+        return y.view(xyz.shape)
+
+    def g(self, zup: torch.Tensor, ctxs, upratio: int):
+        """PointInterpFlow.g (continuous/interpflow.py:108-115) on zup[Bp, N*R, 3] (row n*R + r): blocks 5..0 over [T_i, 0]."""
+        y = zup.reshape(-1, 3)
+        for i in reversed(range(NUM_BLOCKS)):
+            b = self.w["cnf"][i]
+            y = ops.cnf_flow(y, ctxs[i], b["blob"], b["T"], 0.0, upratio, self.atol, self.rtol)
+        return y.view(zup.shape)
+
+    @torch.no_grad()
+    def forward(self, xyz: torch.Tensor, upratio: int = 4, return_all: bool = False):
+        """xyz[Bp,N,3] fp32 CUDA -> (x[Bp, N*R, 3], None)  (continuous/interpflow.py:121-130; log p not computed)."""
+        if xyz.dim() != 3 or xyz.shape[2] != 3:
+            raise ValueError(f"expected xyz[B,N,3], got {tuple(xyz.shape)}")
+        xyz = xyz.contiguous().float()
+        idx = self.knn(xyz, K_MAIN)
+        cs = self.feat_extract(xyz, idx)
+        ctxs = self.contexts(cs)
+        z = self.f(xyz, ctxs)
+        zup = self.interp(z, xyz, upratio, idx)
+        x = self.g(zup, ctxs, upratio)
+        if return_all:
+            return dict(knn_idx=idx, cs=cs, z=z, zup=zup, x=x)
+        return x, None
+
+    def forward_c(self, xyz, upratio: int = 4):
+        raise NotImplementedError("the one-call C entry points cover the discrete model")
+
+    def upsample_clouds(self, *a, **k):
+        raise NotImplementedError("the one-call C entry points cover the discrete model; use modules.utils.patch.PatchHelper")
+
+    def forward_graphed(self, xyz, upratio: int = 4):
+        return self.forward(xyz, upratio)

@@ -373,6 +373,26 @@ def interp_tc(xyz: torch.Tensor, z: torch.Tensor, idx: torch.Tensor, wtc: torch.
     return out
 
 
+def cnf_flow(y: torch.Tensor, ctx: torch.Tensor, blob: torch.Tensor, t0: float, t1: float, rep: int = 1, atol: float = 1e-5,
+             rtol: float = 1e-5, return_nfe: bool = False):
+    """One CNF block of the continuous variant (pf_cnf_flow): y[M,3] at t0 -> y at t1 under dy/dt = ODEnet([t, c], y).
+    ctx[ceil(M / rep), >= PF_CNF_CTX]: the c part of the gates / biases (packing.pack_cnf_block), row p // rep for point p;
+    blob: fp32[PF_CNF_BLOB / 4]."""
+    _chk(y, "y"), _chk(ctx, "ctx"), _chk(blob, "blob")
+    M = y.shape[0]
+    if y.dim() != 2 or y.shape[1] != 3 or ctx.dim() != 2 or ctx.shape[1] < N.PF_CNF_CTX or blob.numel() * 4 != N.PF_CNF_BLOB:
+        raise ValueError("cnf_flow: bad shapes")
+    if ctx.shape[0] * rep < M:
+        raise ValueError(f"cnf_flow: {ctx.shape[0]} conditioning rows x rep {rep} < {M} points")
+    out = torch.empty_like(y)
+    nfe = torch.empty(M, dtype=torch.int32, device=y.device) if return_nfe else None
+    with _dev(y), _launch("cnf_flow"):
+        N.check(lib.pf_cnf_flow(y.data_ptr(), ctx.data_ptr(), ctx.stride(0), blob.data_ptr(), out.data_ptr(),
+                                nfe.data_ptr() if return_nfe else None, M, int(rep), float(t0), float(t1), float(atol),
+                                float(rtol), _stream()), "pf_cnf_flow")
+    return (out, nfe) if return_nfe else out
+
+
 # ---- whole network in one C call ---------------------------------------------------------------------
 class _Workspaces:
     """Scratch buffers of the one-call entry points, one per (device, stream, size): two streams (or two host threads on

@@ -460,6 +460,82 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
     return cast(out)
 
 
+CNF_CTX, CNF_CTX_LD, CNF_BLOB_FLOATS = 264, 272, 4880
+
+
+def pack_cnf_block(sd, i: int):
+    """FlowBlock i of the continuous variant (modules/continuous/interpflow.py:19-31: ODEnet with hidden (64, 64),
+    ConcatSquashLinear layers, diffeq_layers.py:72-86) -> dict for pf_cnf_flow:
+      wctx[cdim, 272], bctx[272]  the c part of every gate / bias pre-activation, one GEMM per input point:
+                                  columns [0,64) gate0 | [64,128) bias0 | [128,192) gate1 | [192,256) bias1 | [256,259) gate2 |
+                                  [259,262) bias2 | zero padding (the hyper layers' column 0 multiplies t and goes to the blob)
+      blob[4880] fp32             (W0[j][0..2], b0[j]) x 64 | gate0_t[64] | bias0_t[64] | W1[64][64] | b1 | gate1_t | bias1_t |
+                                  W2[3][64] | b2[3] | gate2_t[3] | bias2_t[3] | pad
+      T                           sqrt_end_time ** 2 (cnf.py:74-77)."""
+    p = f"flow_blocks.{i}.cnf.odefunc.diffeq.layers."
+    L = [{k: _f64(sd[f"{p}{l}.{k}"]) for k in ("_layer.weight", "_layer.bias", "_hyper_bias.weight", "_hyper_gate.weight",
+                                                "_hyper_gate.bias")} for l in range(3)]
+    assert L[0]["_layer.weight"].shape == (64, 3) and L[1]["_layer.weight"].shape == (64, 64) and \
+        L[2]["_layer.weight"].shape == (3, 64), "pf_cnf_flow is built for ODEnet hidden dims (64, 64) on 3 channels"
+    cdim = L[0]["_hyper_gate.weight"].shape[1] - 1
+    wctx = torch.zeros(cdim, CNF_CTX_LD, dtype=torch.float64)
+    bctx = torch.zeros(CNF_CTX_LD, dtype=torch.float64)
+    col = 0
+    tcols = []
+    for l in range(3):
+        n = L[l]["_layer.weight"].shape[0]
+        wctx[:, col:col + n] = L[l]["_hyper_gate.weight"][:, 1:].t()
+        bctx[col:col + n] = L[l]["_hyper_gate.bias"]
+        wctx[:, col + n:col + 2 * n] = L[l]["_hyper_bias.weight"][:, 1:].t()
+        tcols.append((L[l]["_hyper_gate.weight"][:, 0], L[l]["_hyper_bias.weight"][:, 0]))
+        col += 2 * n
+    assert col == 262
+    blob = torch.cat([
+        torch.cat([L[0]["_layer.weight"], L[0]["_layer.bias"][:, None]], dim=1).reshape(-1), tcols[0][0], tcols[0][1],
+        L[1]["_layer.weight"].reshape(-1), L[1]["_layer.bias"], tcols[1][0], tcols[1][1],
+        L[2]["_layer.weight"].reshape(-1), L[2]["_layer.bias"], tcols[2][0], tcols[2][1],
+        torch.zeros(CNF_BLOB_FLOATS - 4873, dtype=torch.float64)])
+    assert blob.numel() == CNF_BLOB_FLOATS
+    out = dict(wctx=wctx.contiguous(), bctx=bctx, blob=blob, T=float(sd[f"flow_blocks.{i}.cnf.sqrt_end_time"]) ** 2)
+    if linear_tc_ok(*wctx.shape):
+        out["wctx_tc"] = pack_linear_tc(wctx)
+    return out
+
+
+def pack_cnf_state_dict(sd: Dict[str, torch.Tensor], device="cpu") -> Dict:
+    """The continuous variant (modules/continuous/interpflow.py:53-84): the discrete model's feature extractor, merge units
+    and interpolation module (same keys, same kernels) + six CNF blocks."""
+    out = {"feat": [], "merge": [], "cnf": []}
+    for i, (C, g, Co) in enumerate(FEAT_CFG):
+        out["feat"].append(pack_edgeconv(sd, f"feat_convs.{i}", C, g, Co))
+        out["feat"][-1]["wtc"] = pack_edgeconv_tc(out["feat"][-1]["wd"], out["feat"][-1]["wo"], g, Co)
+        if linear_tc_ok(*out["feat"][-1]["wpq"].shape):
+            out["feat"][-1]["wpq_tc"] = pack_linear_tc(out["feat"][-1]["wpq"])
+        out["merge"].append(dict(
+            w1=_f64(sd[f"merge_convs.{i}.conv1.weight"]).t().contiguous(),
+            b1=_f64(sd[f"merge_convs.{i}.conv1.bias"]),
+            w2=_f64(sd[f"merge_convs.{i}.conv2.weight"]).t().contiguous()))
+        for nm in ("w1", "w2"):
+            if linear_tc_ok(*out["merge"][-1][nm].shape):
+                out["merge"][-1][nm + "_tc"] = pack_linear_tc(out["merge"][-1][nm])
+        out["cnf"].append(pack_cnf_block(sd, i))
+    out["interp"] = pack_interp(sd)
+    out["interp"]["tc"] = pack_interp_tc(sd)
+    return _cast_tree(out, device)
+
+
+def _cast_tree(o, device):
+    if isinstance(o, torch.Tensor):
+        if o.dtype == torch.uint8:
+            return o.contiguous().to(device)
+        return o.to(torch.float32).contiguous().to(device)
+    if isinstance(o, dict):
+        return {k: _cast_tree(v, device) for k, v in o.items()}
+    if isinstance(o, list):
+        return [_cast_tree(v, device) for v in o]
+    return o
+
+
 def pack_model_blob(w: Dict) -> torch.Tensor:
     """pack_state_dict(...) result -> the single uint8 blob pf_upsample_patches takes (layout: csrc/model.cu, enumerated
     through pf_model_entry so that C and Python cannot disagree).  CPU tensor; `.to(device)` it, or `.numpy().tofile(path)`
