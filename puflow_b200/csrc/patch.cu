@@ -156,6 +156,76 @@ int launch_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, cudaStr
     return pf_launch_status("fps_kernel");
 }
 
+// ---- the same sampler, one CTA per cloud: batches of MANY small clouds (the 32-seed FPS of a 128-cloud batch) ----------
+// 128 clusters of 8 CTAs do not fit the GPU at once (two waves, and a cluster barrier per round): 0.26 ms for 32 rounds.  With
+// one 512-thread CTA per cloud the whole batch is one wave and a round is: register update -> warp arg-max -> one block
+// barrier -> every warp reduces the 16 warp candidates -> the winner's coordinates from the shared-memory copy of the cloud.
+// Same arithmetic, same (value, lowest index) order: bit-identical indices.
+template <int PPT>
+__global__ void __launch_bounds__(FT, 1) fps_cta_kernel(const float* __restrict__ xyz, int n, int npoint,
+                                                        int32_t* __restrict__ out) {
+    extern __shared__ __align__(16) float pts[];           // [n][3]
+    __shared__ float wval[2][NW];
+    __shared__ int widx[2][NW];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const float* pb = xyz + (size_t)b * n * 3;
+    for (int i = tid; i < n * 3; i += FT) pts[i] = pb[i];
+    __syncthreads();
+    float px[PPT], py[PPT], pz[PPT], md[PPT];
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        const int i = k * FT + tid;
+        const bool ok = i < n;
+        px[k] = ok ? pts[i * 3] : 0.f, py[k] = ok ? pts[i * 3 + 1] : 0.f, pz[k] = ok ? pts[i * 3 + 2] : 0.f;
+        md[k] = ok ? 1e10f : -1.f;
+    }
+    int far = 0;
+    float cx = pts[0], cy = pts[1], cz = pts[2];
+    for (int s = 0; s < npoint; s++) {
+        if (tid == 0) out[(size_t)b * npoint + s] = far;
+        if (s + 1 == npoint) break;
+        float bv = -2.f;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            float dx = __fsub_rn(px[k], cx), dy = __fsub_rn(py[k], cy), dz = __fsub_rn(pz[k], cz);
+            float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            float m = md[k];
+            m = (m >= 0.f && d < m) ? d : m;
+            md[k] = m;
+            const int i = k * FT + tid;
+            if (better(m, i, bv, bi)) bv = m, bi = i;
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, bv, off);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            if (better(ov, oi, bv, bi)) bv = ov, bi = oi;
+        }
+        const int par = s & 1;                              // double buffered: one barrier per round
+        if (lane == 0) wval[par][wid] = bv, widx[par][wid] = bi;
+        __syncthreads();
+        float v = lane < NW ? wval[par][lane] : -3.f;
+        int i = lane < NW ? widx[par][lane] : 0x7fffffff;
+#pragma unroll
+        for (int off = 8; off > 0; off >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, v, off);
+            int oi = __shfl_xor_sync(0xffffffffu, i, off);
+            if (better(ov, oi, v, i)) v = ov, i = oi;
+        }
+        far = __shfl_sync(0xffffffffu, i, 0);
+        cx = pts[far * 3], cy = pts[far * 3 + 1], cz = pts[far * 3 + 2];
+    }
+}
+
+template <int PPT>
+int launch_fps_cta(const float* xyz, int B, int n, int npoint, int32_t* idx, cudaStream_t st) {
+    const size_t smem = (size_t)n * 12;
+    if (int rc = pf_smem_optin(fps_cta_kernel<PPT>, smem)) return rc;
+    fps_cta_kernel<PPT><<<B, FT, smem, st>>>(xyz, n, npoint, idx);
+    return pf_launch_status("fps_cta_kernel");
+}
+
 // ---- k nearest of np points for a handful of seed queries: full bitonic sort of packed keys -------
 // key = (float bits of the squared distance) << 32 | index : unsigned order == (distance, index) order
 constexpr int ST = 1024;
@@ -203,6 +273,15 @@ extern "C" int pf_fps(const float* xyz, int B, int n, int npoint, int32_t* idx, 
     PF_CHECK_ARG((long long)B * CS < 0x7fffffffLL, "pf_fps: B too large");
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    // many small clouds: one CTA per cloud (a single wave) instead of one 8-CTA cluster per cloud (several waves)
+    if (B * CS > 2 * 148 && n <= 16 * FT) {
+        const int pc = (n + FT - 1) / FT;
+        if (pc <= 1) return launch_fps_cta<1>(xyz, B, n, npoint, idx, st);
+        if (pc <= 2) return launch_fps_cta<2>(xyz, B, n, npoint, idx, st);
+        if (pc <= 4) return launch_fps_cta<4>(xyz, B, n, npoint, idx, st);
+        if (pc <= 8) return launch_fps_cta<8>(xyz, B, n, npoint, idx, st);
+        return launch_fps_cta<16>(xyz, B, n, npoint, idx, st);
+    }
     const int per = (n + CS * FT - 1) / (CS * FT);
     if (per <= 1) return launch_fps<1>(xyz, B, n, npoint, idx, st);
     if (per <= 2) return launch_fps<2>(xyz, B, n, npoint, idx, st);

@@ -611,7 +611,8 @@ def test_full_size_properties(dev, state_dict):
 
 
 # ---- caller side -----------------------------------------------------------------------------------
-@pytest.mark.parametrize("B,n,npoint", [(3, 2048, 32), (2, 5000, 78), (2, 40960, 700), (1, 12345, 300), (4, 100, 100)])
+@pytest.mark.parametrize("B,n,npoint", [(3, 2048, 32), (2, 5000, 78), (2, 40960, 700), (1, 12345, 300), (4, 100, 100),
+                                        (40, 2048, 32), (64, 700, 50), (40, 3000, 40), (130, 33, 33)])   # B >= 38: one CTA per cloud
 def test_fps_bit_exact(ops, dev, B, n, npoint):
     rng = np.random.default_rng(n)
     p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
