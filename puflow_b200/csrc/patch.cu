@@ -226,31 +226,19 @@ int launch_fps_cta(const float* xyz, int B, int n, int npoint, int32_t* idx, cud
     return pf_launch_status("fps_cta_kernel");
 }
 
-// ---- k nearest of np points for a handful of seed queries: full bitonic sort of packed keys -------
-// key = (float bits of the squared distance) << 32 | index : unsigned order == (distance, index) order
-constexpr int ST = 1024;
+// ---- k nearest of np points for a handful of seed queries: radix select, then a sort of the selected keys only ----
+// key = (float bits of the squared distance) << 32 | index : unsigned order == (distance, index) order.
+// Round 1 sorted all np keys (np = 2,048: 66 block-wide compare-exchange stages of a 1,024-thread CTA, 0.42 ms for the 4,096
+// seeds of config 2 -- the barriers, not the compares, were the cost).  Now: (1) four 8-bit histogram passes find T = the
+// k-th smallest DISTANCE; (2) the keys with distance <= T (k of them plus ties at T) are compacted; (3) only those are sorted
+// (k = 256: 36 stages of 128 pairs) and the first k written.  More than SEL_CAP keys at or below T (massively duplicated
+// points) falls back to the full sort.  Same (distance, index) order: bit-identical indices.
+constexpr int ST = 256, SEL_CAP = 1024;
 
-__global__ void __launch_bounds__(ST) knn_patch_kernel(const float* __restrict__ q, const float* __restrict__ p,
-                                                       int nq, int np, int npad, int k, int32_t* __restrict__ idx) {
-    extern __shared__ __align__(16) unsigned long long keys[];
-    const int b = blockIdx.y, qi = blockIdx.x;
-    const float* qq = q + ((size_t)b * nq + qi) * 3;
-    const float qx = qq[0], qy = qq[1], qz = qq[2];
-    const float* pb = p + (size_t)b * np * 3;
-    for (int i = threadIdx.x; i < npad; i += ST) {
-        unsigned long long key = ~0ull;
-        if (i < np) {
-            float dx = __fsub_rn(qx, pb[(size_t)i * 3]), dy = __fsub_rn(qy, pb[(size_t)i * 3 + 1]),
-                  dz = __fsub_rn(qz, pb[(size_t)i * 3 + 2]);
-            float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-            key = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)i;
-        }
-        keys[i] = key;
-    }
-    __syncthreads();
-    for (int size = 2; size <= npad; size <<= 1) {
+__device__ __forceinline__ void bitonic_sort_block(unsigned long long* keys, int n) {      // n a power of two, whole CTA
+    for (int size = 2; size <= n; size <<= 1) {
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int i = threadIdx.x; i < npad / 2; i += ST) {
+            for (int i = threadIdx.x; i < n / 2; i += ST) {
                 int lo = 2 * i - (i & (stride - 1));           // index with bit `stride` clear
                 int hi = lo + stride;
                 bool up = (lo & size) == 0;
@@ -260,8 +248,84 @@ __global__ void __launch_bounds__(ST) knn_patch_kernel(const float* __restrict__
             __syncthreads();
         }
     }
+}
+
+__global__ void __launch_bounds__(ST) knn_patch_kernel(const float* __restrict__ q, const float* __restrict__ p,
+                                                       int nq, int np, int npad, int k, int32_t* __restrict__ idx) {
+    extern __shared__ __align__(16) unsigned long long keys[];          // [npad] | sel[SEL_CAP]
+    unsigned long long* sel = keys + npad;
+    __shared__ unsigned hist[256];
+    __shared__ unsigned s_bin, s_rank, s_count;
+    const int b = blockIdx.y, qi = blockIdx.x, tid = threadIdx.x;
+    const float* qq = q + ((size_t)b * nq + qi) * 3;
+    const float qx = qq[0], qy = qq[1], qz = qq[2];
+    const float* pb = p + (size_t)b * np * 3;
+    for (int i = tid; i < npad; i += ST) {
+        unsigned long long key = ~0ull;
+        if (i < np) {
+            float dx = __fsub_rn(qx, pb[(size_t)i * 3]), dy = __fsub_rn(qy, pb[(size_t)i * 3 + 1]),
+                  dz = __fsub_rn(qz, pb[(size_t)i * 3 + 2]);
+            float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            key = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)i;
+        }
+        keys[i] = key;
+    }
+    // (1) T = the k-th smallest distance (as its bit pattern: non-negative floats order like unsigned integers)
+    unsigned prefix = 0, mask = 0, rank = (unsigned)k;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        hist[tid] = 0;                                                   // ST == 256 bins
+        if (tid == 0) s_count = 0;
+        __syncthreads();                                                 // (also: keys[] written)
+        for (int i = tid; i < np; i += ST) {
+            const unsigned d = (unsigned)(keys[i] >> 32);
+            if ((d & mask) == prefix) atomicAdd(&hist[(d >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (tid < 32) {                                                  // bin in which the cumulative count reaches `rank`
+            unsigned c[8], tot = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) c[j] = hist[8 * tid + j], tot += c[j];
+            unsigned incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (tid >= o) incl += v;
+            }
+            unsigned before = incl - tot;
+            if (before < rank && rank <= incl) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (before < rank && rank <= before + c[j]) s_bin = 8u * tid + j, s_rank = rank - before;
+                    before += c[j];
+                }
+            }
+        }
+        __syncthreads();
+        prefix |= s_bin << shift, mask |= 255u << shift, rank = s_rank;
+    }
+    // (2) every key at or below T, in any order
+    for (int i = tid; i < np; i += ST) {
+        const unsigned long long key = keys[i];
+        if ((unsigned)(key >> 32) <= prefix) {
+            const unsigned slot = atomicAdd(&s_count, 1u);
+            if (slot < (unsigned)SEL_CAP) sel[slot] = key;
+        }
+    }
+    __syncthreads();
+    const unsigned total = s_count;
     int32_t* o = idx + ((size_t)b * nq + qi) * k;
-    for (int i = threadIdx.x; i < k; i += ST) o[i] = (int32_t)(keys[i] & 0xffffffffu);
+    if (total <= (unsigned)SEL_CAP) {
+        // (3) sort the selected keys alone
+        int P = 2;
+        while (P < (int)total) P <<= 1;
+        for (int i = (int)total + tid; i < P; i += ST) sel[i] = ~0ull;
+        __syncthreads();
+        bitonic_sort_block(sel, P);
+        for (int i = tid; i < k; i += ST) o[i] = (int32_t)(sel[i] & 0xffffffffu);
+    } else {
+        bitonic_sort_block(keys, npad);
+        for (int i = tid; i < k; i += ST) o[i] = (int32_t)(keys[i] & 0xffffffffu);
+    }
 }
 
 }  // namespace
@@ -303,8 +367,8 @@ extern "C" int pf_knn_patch(const float* q, const float* p, int B, int nq, int n
     if (B == 0 || nq == 0) return 0;
     int npad = 2;
     while (npad < np) npad <<= 1;
-    const size_t smem = (size_t)npad * sizeof(unsigned long long);
-    PF_CHECK_ARG(smem <= 224 * 1024, "pf_knn_patch: np=%d too large for the shared-memory sort (max 16384)", np);
+    const size_t smem = (size_t)(npad + SEL_CAP) * sizeof(unsigned long long);
+    PF_CHECK_ARG((size_t)npad * 8 <= 208 * 1024, "pf_knn_patch: np=%d too large for the shared-memory sort (max 16384)", np);
     if (int rc = pf_smem_optin(knn_patch_kernel, smem)) return rc;
     dim3 grid(nq, B);
     knn_patch_kernel<<<grid, ST, smem, (cudaStream_t)stream>>>(q, p, nq, np, npad, k, idx);

@@ -727,3 +727,21 @@ def test_knn_patch_bit_exact(ops, dev, B, nq, np_, k):
     ref = po.knn(q, p, k)[1]
     out = ops.knn_patch(torch.from_numpy(q).to(dev), torch.from_numpy(p).to(dev), k).cpu().numpy()
     assert np.array_equal(out.astype(np.int64), ref)
+
+
+@pytest.mark.parametrize("kind", ["lattice", "duplicates", "identical"])
+def test_knn_patch_ties(ops, dev, kind):
+    """The select-then-sort path keeps the (distance, index) order under ties at the k-th distance; more than 1,024 keys at or
+    below it (every point identical) take the full-sort fallback."""
+    rng = np.random.default_rng(17)
+    B, n, nq, k = 2, 2048, 5, 256
+    if kind == "lattice":
+        p = rng.integers(0, 8, (B, n, 3)).astype(np.float32)
+    elif kind == "duplicates":
+        p = np.repeat(rng.uniform(-1, 1, (B, n // 4, 3)), 4, axis=1).astype(np.float32)
+    else:
+        p = np.full((B, n, 3), 0.25, np.float32)
+    q = p[:, :nq].copy()
+    ref = po.knn(q, p, k)[1]
+    out = ops.knn_patch(torch.from_numpy(q).to(dev), torch.from_numpy(p).to(dev), k).cpu().numpy()
+    assert np.array_equal(out.astype(np.int64), ref)
