@@ -504,6 +504,24 @@ def test_interp_tensor_core(ops, dev, packed, Bp, N, R):
         assert torch.equal(sub, out[1:3])
 
 
+def test_interp_tensor_core_tile_pipeline_is_deterministic(ops, dev, packed):
+    """The interpolation kernel overlaps a tile's tail with the next tile's head and schedules its side work by polling
+    (csrc/interp_tc.cu): a CTA that runs MANY tiles must produce, bit for bit, what one-tile-per-CTA launches produce, run after
+    run.  (A scheduling bug of an early version only showed in the second tile of a CTA, and only as run-to-run differences.)"""
+    Bp, N, R = 96, 256, 4                                  # 1,536 tiles on <= 148 CTAs: 10-11 tiles per CTA
+    p = synth.make_patches(Bp, N, seed=5, shape="surface")
+    xyz = torch.from_numpy(p).to(dev)
+    z = (torch.randn(Bp, N, 3, generator=torch.Generator().manual_seed(1)) * 0.6).to(dev)
+    idx = torch.from_numpy(po.knn(p, p, 16)[1]).int().to(dev)
+    wtc = packed["interp"]["tc"].to(dev)
+    first = ops.interp_tc(xyz, z, idx, wtc, R)
+    for _ in range(5):
+        assert torch.equal(ops.interp_tc(xyz, z, idx, wtc, R), first)
+    for b in (0, 1, 37, 95):                               # 16 tiles each: one tile per CTA, no cross-tile overlap
+        one = ops.interp_tc(xyz[b:b + 1].contiguous(), z[b:b + 1].contiguous(), idx[b:b + 1].contiguous(), wtc, R)
+        assert torch.equal(one[0], first[b])
+
+
 # ---- whole path ------------------------------------------------------------------------------------
 def test_network_stages_match_reference(dev, state_dict, golden):
     from puflow_b200.engine import PUFlowEngine
