@@ -68,7 +68,7 @@ __host__ __device__ constexpr uint32_t ws_off(int m) { return W_H + 2 * WG_PART 
 __host__ __device__ constexpr uint32_t ws_part(int m) { return 512u * (7 - m); }
 constexpr uint32_t X_OFF = 99072, KX = 208, X_SBO = KX * 16, X_PART = 128 * KX * 2;    // 53,248 per part
 constexpr uint32_t T0_OFF = X_OFF, T0_PART = 32768;       // t0 M-major [128 ch][128 edges], aliases X (dead by then)
-constexpr uint32_t T1_OFF = X_OFF + 65536, T1_PART = 16384, T1_SBO = 64 * 16;
+constexpr uint32_t T1_OFF = X_OFF + 65536, T1_PART = 16384, T1_SBO = 64 * 16;   // t1 K-major [128 edges][64], behind t0
 // the geo slice has a buffer of its own ([128][16] K-major, hi | lo): the NEXT tile's slice is written, and its first MMAs
 // are issued, under the tail of the current tile (whose t0 / t1 operands alias X)
 constexpr uint32_t GEO_OFF = X_OFF + 2 * X_PART, GEO_PART = 4096, GEO_SBO = 256;   // 205,568

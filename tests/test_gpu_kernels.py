@@ -737,6 +737,33 @@ def test_fps_queue_tie_search(ops, dev):
     assert np.array_equal(ops.fps(torch.from_numpy(p).to(dev), npoint, mode="queue").cpu().numpy(), ref)
 
 
+@pytest.mark.parametrize("kind,B,n,npoint", [("surface", 1, 99840, 20024), ("surface", 3, 70001, 1500), ("lattice", 2, 80000, 600),
+                                             ("ties", 2, 66000, 3000), ("dup", 1, 90000, 2500), ("same", 2, 66000, 50)])
+def test_fps_cluster_queue_bit_exact(ops, dev, kind, B, n, npoint):
+    """The threshold queue with a cloud's buckets spread over an 8-CTA cluster (fps_cqueue_kernel: what pf_fps_queued runs for few
+    clouds of >= 65,536 candidates) against the brute-force definition: config 3's full merge (20,024 of 99,840), a ragged size,
+    lattice ties, more points tying with the maximum than the queue holds (the cluster-wide tie search), triplicated points, all
+    points identical."""
+    rng = np.random.default_rng(n + npoint)
+    if kind == "surface":
+        p = np.stack([synth.make_cloud(n, 41 + b, synth.SHAPES[b % 3]) for b in range(B)])
+    elif kind == "lattice":
+        p = rng.integers(0, 40, (B, n, 3)).astype(np.float32)
+    elif kind == "ties":
+        p = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+        for j in range(6):
+            p[:, 400 * j:400 * (j + 1)] = rng.uniform(2, 3, (B, 1, 3)).astype(np.float32) * (1 if j % 2 else -1)
+        p = np.ascontiguousarray(p[:, rng.permutation(n)])
+    elif kind == "dup":
+        base = rng.uniform(-1, 1, (B, n // 3, 3)).astype(np.float32)
+        p = np.concatenate([base, base, base], 1)[:, rng.permutation(n // 3 * 3)]
+    else:
+        p = np.full((B, n, 3), 0.25, np.float32)
+    ref = po.fps(p, npoint)
+    out = ops.fps(torch.from_numpy(np.ascontiguousarray(p)).to(dev), npoint, mode="queue").cpu().numpy()
+    assert np.array_equal(out, ref)
+
+
 @pytest.mark.parametrize("B,nq,np_,k", [(2, 32, 2048, 256), (1, 78, 5000, 256), (2, 5, 300, 256), (1, 3, 1000, 1000)])
 def test_knn_patch_bit_exact(ops, dev, B, nq, np_, k):
     rng = np.random.default_rng(np_)

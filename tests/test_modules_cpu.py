@@ -27,7 +27,7 @@ def test_header_constants_match_binding():
     hdr = open(os.path.join(ROOT, "include", "puflow_b200.h")).read()
     from puflow_b200 import _native
     for name in ("PF_COND_BLOB", "PF_FLOW_BLOB", "PF_INTERP_BLOB", "PF_ABI_VERSION", "PF_COND_TC_BLOCK",
-                 "PF_FLOW_TC_BLOCK", "PF_EDGECONV_TC_BLOB", "PF_INTERP_TC_BLOB", "PF_MODEL_ENTRIES"):
+                 "PF_FLOW_TC_BLOCK", "PF_EDGECONV_TC_BLOB", "PF_INTERP_TC_BLOB", "PF_MODEL_ENTRIES", "PF_CNF_CTX", "PF_CNF_BLOB"):
         assert int(re.search(rf"#define {name} (\d+)", hdr).group(1)) == getattr(_native, name)
 
 
