@@ -219,7 +219,8 @@ PF_API int pf_fps_clustered(const float* xyz, int B, int n, int npoint, int32_t*
  * maximum exceeds theta the next sample is the arg-max of the LIST.  One warp draws ~70-100 samples in a row from a list of
  * <= 256 points held in its registers; all warps then apply those samples to the bucketed cloud in one pruned pass and
  * collect the next list.  One CTA per cloud, any batch size; clouds above pf_fps_queued_max_points() candidates go to
- * pf_fps_bucketed.  work: pf_fps_work_floats(B, n) floats. */
+ * pf_fps_bucketed.  Few large clouds (n >= 65,536 and every cloud's 8-CTA cluster resident at once) run the same algorithm with
+ * a cloud's buckets spread over a thread-block cluster (fps_cqueue_kernel: config 3's merge FPS).  work: pf_fps_work_floats(B, n) floats. */
 PF_API int pf_fps_queued_max_points(void);
 PF_API int pf_fps_queued(const float* xyz, int B, int n, int npoint, int32_t* idx, float* work, void* stream);
 /* pf_fps_queued_static: no counterpart in the reference; added for callers that
