@@ -22,7 +22,7 @@ def tag_of(name):
     m = re.search(r"knn_kernel<(\d+)>", name)
     if m: return "chamfer_nn" if m.group(1) == "1" else f"knn_topk_k{m.group(1)}"
     if "knn_patch_kernel" in name: return "knn_patch"
-    if "fps_bucket_kernel" in name or "fps_queue_kernel" in name or "fps_cluster_kernel" in name: return "fps_n40960"
+    if any(k in name for k in ("fps_bucket_kernel", "fps_queue_kernel", "fps_cqueue_kernel", "fps_cluster_kernel")): return "fps_n40960"
     if re.search(r"\bfps_kernel", name) or "fps_cta_kernel" in name: return "fps_n2048"
     if "linear_kernel" in name: return "linear_k3_n128"
     m = re.search(r"normalize_kernel<(\w+)>", name)
