@@ -77,6 +77,61 @@ __device__ __forceinline__ float boxd2(float cx, float cy, float cz, float lx, f
 // control words in shared memory
 enum { C_CNT0 = 0, C_S = 3, C_NCENT = 4, C_WORDS = 8 };
 
+// The chain (one warp): the queue's `cnt` entries live in registers, E per lane (slot 32 e + lane); a sample is one warp arg-max
+// (ties: lowest original index), one broadcast of its coordinates, E distance updates per lane -- repeated until the queue's
+// maximum falls to theta.  E is chosen from the queue's length (2 / 4 / 8): the list is steered towards 128 entries, and an
+// empty register slot costs as much as a full one (440 cycles per sample with E = 8).  emit(j, c, s): publish sample j.
+template <int E, class Emit>
+__device__ __forceinline__ void run_chain(int cnt, const int* Lp, const float* Ld, float4* Lc, const float* sx, const float* sy,
+                                          const float* sz, const unsigned* so, float theta, int npoint, int lane, int& s, int& j,
+                                          Emit&& emit) {
+    float d[E], x[E], y[E], z[E];
+    unsigned o[E];
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+        const int slot = 32 * e + lane;
+        const bool ok = slot < cnt;
+        const int p = ok ? Lp[slot] : 0;
+        d[e] = ok ? Ld[slot] : 0.f;
+        x[e] = sx[p], y[e] = sy[p], z[e] = sz[p], o[e] = ok ? so[p] : 0xffffffffu;
+    }
+#pragma unroll
+    for (int e = 0; e < E; e++) Lc[32 * e + lane] = make_float4(x[e], y[e], z[e], __uint_as_float(o[e]));
+    __syncwarp();
+    while (s < npoint && j < JMAX) {
+        float lm = d[0];
+#pragma unroll
+        for (int e = 1; e < E; e++) lm = fmaxf(lm, d[e]);
+        const float Mq = warp_max_pos(lm);
+        if (!(Mq > theta)) break;
+        unsigned myo = 0xffffffffu;
+        int mye = 0;
+#pragma unroll
+        for (int e = 0; e < E; e++)
+            if (d[e] == Mq && o[e] < myo) myo = o[e], mye = e;
+        const unsigned bal = __ballot_sync(FULL, lm == Mq);
+        int src = __ffs(bal) - 1;
+        if (bal & (bal - 1)) {      // several lanes attain the maximum: lowest original index
+            const unsigned om = __reduce_min_sync(FULL, lm == Mq ? myo : 0xffffffffu);
+            src = __ffs(__ballot_sync(FULL, lm == Mq && myo == om)) - 1;
+        }
+        const int slot = __shfl_sync(FULL, 32 * mye + lane, src);
+        const float4 c = Lc[slot];
+        emit(j, c, s);
+        j++, s++;
+#pragma unroll
+        for (int e = 0; e < E; e++) d[e] = fminf(d[e], sqdist(x[e], y[e], z[e], c.x, c.y, c.z));
+    }
+}
+template <class Emit>
+__device__ __forceinline__ void run_chain_any(int cnt, const int* Lp, const float* Ld, float4* Lc, const float* sx, const float* sy,
+                                              const float* sz, const unsigned* so, float theta, int npoint, int lane, int& s, int& j,
+                                              Emit&& emit) {
+    if (cnt <= 64) run_chain<2>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
+    else if (cnt <= 128) run_chain<4>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
+    else run_chain<EPL>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
+}
+
 // work (per cloud, npad = 32 * nb entries each): sx | sy | sz | oidx | md (md only used when !MD_SMEM)
 // Bucket b (32 sorted points) belongs to warp b / KB, lane (b % KB) % 32, register slot (b % KB) / 32.
 template <bool MD_SMEM, int BPL>
@@ -380,44 +435,10 @@ __global__ void __launch_bounds__(FT, 1)
             else if (cnt > CAP / 2) gap *= 0.85f;
             // ---- (3) the chain: warp 0 draws samples from the queue until its maximum falls to theta ----
             if (w == 0) {
-                float d[EPL], x[EPL], y[EPL], z[EPL];
-                unsigned o[EPL];
-#pragma unroll
-                for (int e = 0; e < EPL; e++) {
-                    const int slot = 32 * e + lane;
-                    const bool ok = slot < cnt;
-                    const int p = ok ? Lp[slot] : 0;
-                    d[e] = ok ? Ld[slot] : 0.f;
-                    x[e] = sx[p], y[e] = sy[p], z[e] = sz[p], o[e] = ok ? so[p] : 0xffffffffu;
-                }
-#pragma unroll
-                for (int e = 0; e < EPL; e++) Lc[32 * e + lane] = make_float4(x[e], y[e], z[e], __uint_as_float(o[e]));
-                __syncwarp();
                 int j = 0;
-                while (s < npoint && j < JMAX) {
-                    float lm = d[0];
-#pragma unroll
-                    for (int e = 1; e < EPL; e++) lm = fmaxf(lm, d[e]);
-                    const float Mq = warp_max_pos(lm);
-                    if (!(Mq > theta)) break;
-                    unsigned myo = 0xffffffffu;
-                    int mye = 0;
-#pragma unroll
-                    for (int e = 0; e < EPL; e++)
-                        if (d[e] == Mq && o[e] < myo) myo = o[e], mye = e;
-                    const unsigned bal = __ballot_sync(FULL, lm == Mq);
-                    int src = __ffs(bal) - 1;
-                    if (bal & (bal - 1)) {      // several lanes attain the maximum: lowest original index
-                        const unsigned om = __reduce_min_sync(FULL, lm == Mq ? myo : 0xffffffffu);
-                        src = __ffs(__ballot_sync(FULL, lm == Mq && myo == om)) - 1;
-                    }
-                    const int slot = __shfl_sync(FULL, 32 * mye + lane, src);
-                    const float4 c = Lc[slot];
-                    if (lane == 0) cent[j] = c, outc[s] = (int32_t)__float_as_uint(c.w);
-                    j++, s++;
-#pragma unroll
-                    for (int e = 0; e < EPL; e++) d[e] = fminf(d[e], sqdist(x[e], y[e], z[e], c.x, c.y, c.z));
-                }
+                run_chain_any(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, [&](int jj, const float4& c, int ss) {
+                    if (lane == 0) cent[jj] = c, outc[ss] = (int32_t)__float_as_uint(c.w);
+                });
                 if (lane == 0) ctrl[C_S] = s, ctrl[C_NCENT] = j;
             }
             __syncthreads();                                                       // B3
@@ -768,45 +789,11 @@ __global__ void __launch_bounds__(FT, 1)
             else if (cnt > CAP / 2) gap *= 0.85f;
             // ---- (3) the chain: warp 0 draws samples from the queue until its maximum falls to theta ----
             if (r == 0 && w == 0) {
-                float d[EPL], x[EPL], y[EPL], z[EPL];
-                unsigned o[EPL];
-#pragma unroll
-                for (int e = 0; e < EPL; e++) {
-                    const int slot = 32 * e + lane;
-                    const bool ok = slot < cnt;
-                    const int p = ok ? Lp[slot] : 0;
-                    d[e] = ok ? Ld[slot] : 0.f;
-                    x[e] = sx[p], y[e] = sy[p], z[e] = sz[p], o[e] = ok ? so[p] : 0xffffffffu;
-                }
-#pragma unroll
-                for (int e = 0; e < EPL; e++) Lc[32 * e + lane] = make_float4(x[e], y[e], z[e], __uint_as_float(o[e]));
-                __syncwarp();
                 int j = 0;
-                while (s < npoint && j < JMAX) {
-                    float lm = d[0];
-#pragma unroll
-                    for (int e = 1; e < EPL; e++) lm = fmaxf(lm, d[e]);
-                    const float Mq = warp_max_pos(lm);
-                    if (!(Mq > theta)) break;
-                    unsigned myo = 0xffffffffu;
-                    int mye = 0;
-#pragma unroll
-                    for (int e = 0; e < EPL; e++)
-                        if (d[e] == Mq && o[e] < myo) myo = o[e], mye = e;
-                    const unsigned bal = __ballot_sync(FULL, lm == Mq);
-                    int src = __ffs(bal) - 1;
-                    if (bal & (bal - 1)) {      // several lanes attain the maximum: lowest original index
-                        const unsigned om = __reduce_min_sync(FULL, lm == Mq ? myo : 0xffffffffu);
-                        src = __ffs(__ballot_sync(FULL, lm == Mq && myo == om)) - 1;
-                    }
-                    const int slot = __shfl_sync(FULL, 32 * mye + lane, src);
-                    const float4 c = Lc[slot];
-                    if (lane < NC) cluster.map_shared_rank(cent, lane)[j] = c;     // the sample, into every CTA
-                    if (lane == 0) outc[s] = (int32_t)__float_as_uint(c.w);
-                    j++, s++;
-#pragma unroll
-                    for (int e = 0; e < EPL; e++) d[e] = fminf(d[e], sqdist(x[e], y[e], z[e], c.x, c.y, c.z));
-                }
+                run_chain_any(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, [&](int jj, const float4& c, int ss) {
+                    if (lane < NC) cluster.map_shared_rank(cent, lane)[jj] = c;    // the sample, into every CTA
+                    if (lane == 0) outc[ss] = (int32_t)__float_as_uint(c.w);
+                });
                 if (lane < NC) {
                     int* c = cluster.map_shared_rank(ctrl, lane);
                     c[C_S] = s, c[C_NCENT] = j;
