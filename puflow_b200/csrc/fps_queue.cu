@@ -44,6 +44,11 @@ constexpr float SAFE = 0.9999f;              // box lower bound is scaled down: 
 constexpr int CAP = 256, EPL = CAP / 32;     // queue capacity, entries per lane of the chain warp
 constexpr int JMAX = 256;                    // samples per pass at most
 constexpr float GAP0 = 0.1f, GAP_MIN = 1e-6f;
+#ifndef PF_STEER_LO
+#define PF_STEER_LO 32
+#define PF_STEER_HI 64
+#endif
+constexpr int STEER_LO = PF_STEER_LO, STEER_HI = PF_STEER_HI;   // the gap is steered to keep the queue between these lengths
 constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ unsigned morton4(unsigned x, unsigned y, unsigned z) {
@@ -79,8 +84,9 @@ enum { C_CNT0 = 0, C_S = 3, C_NCENT = 4, C_WORDS = 8 };
 
 // The chain (one warp): the queue's `cnt` entries live in registers, E per lane (slot 32 e + lane); a sample is one warp arg-max
 // (ties: lowest original index), one broadcast of its coordinates, E distance updates per lane -- repeated until the queue's
-// maximum falls to theta.  E is chosen from the queue's length (2 / 4 / 8): the list is steered towards 128 entries, and an
-// empty register slot costs as much as a full one (440 cycles per sample with E = 8).  emit(j, c, s): publish sample j.
+// maximum falls to theta.  E is chosen from the queue's length (1 / 2 / 4 / 8): an empty register slot costs as much as a full
+// one (440 cycles per sample with E = 8), and the gap is steered to keep the queue between 32 and 64 entries (measured best:
+// a shorter queue ends its chain sooner and pays more passes, a longer one pays per sample).  emit(j, c, s): publish sample j.
 template <int E, class Emit>
 __device__ __forceinline__ void run_chain(int cnt, const int* Lp, const float* Ld, float4* Lc, const float* sx, const float* sy,
                                           const float* sz, const unsigned* so, float theta, int npoint, int lane, int& s, int& j,
@@ -127,7 +133,8 @@ template <class Emit>
 __device__ __forceinline__ void run_chain_any(int cnt, const int* Lp, const float* Ld, float4* Lc, const float* sx, const float* sy,
                                               const float* sz, const unsigned* so, float theta, int npoint, int lane, int& s, int& j,
                                               Emit&& emit) {
-    if (cnt <= 64) run_chain<2>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
+    if (cnt <= 32) run_chain<1>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
+    else if (cnt <= 64) run_chain<2>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
     else if (cnt <= 128) run_chain<4>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
     else run_chain<EPL>(cnt, Lp, Ld, Lc, sx, sy, sz, so, theta, npoint, lane, s, j, emit);
 }
@@ -431,8 +438,8 @@ __global__ void __launch_bounds__(FT, 1)
             if (tid == 0) *tie = ~0ull;
             gap = GAP_MIN * 4.f;
         } else {
-            if (cnt < CAP / 4) gap = fminf(1.f, gap * 1.5f);
-            else if (cnt > CAP / 2) gap *= 0.85f;
+            if (cnt < STEER_LO) gap = fminf(1.f, gap * 1.5f);
+            else if (cnt > STEER_HI) gap *= 0.85f;
             // ---- (3) the chain: warp 0 draws samples from the queue until its maximum falls to theta ----
             if (w == 0) {
                 int j = 0;
@@ -785,8 +792,8 @@ __global__ void __launch_bounds__(FT, 1)
             cluster.sync();
             gap = GAP_MIN * 4.f;
         } else {
-            if (cnt < CAP / 4) gap = fminf(1.f, gap * 1.5f);
-            else if (cnt > CAP / 2) gap *= 0.85f;
+            if (cnt < STEER_LO) gap = fminf(1.f, gap * 1.5f);
+            else if (cnt > STEER_HI) gap *= 0.85f;
             // ---- (3) the chain: warp 0 draws samples from the queue until its maximum falls to theta ----
             if (r == 0 && w == 0) {
                 int j = 0;
@@ -889,10 +896,13 @@ extern "C" int pf_fps_queued(const float* xyz, int B, int n, int npoint, int32_t
     if (n > pf_fps_queued_max_points()) return pf_fps_bucketed(xyz, B, n, npoint, idx, work, stream);
     const int nb = (n + 31) / 32, KB = (nb + NW - 1) / NW;
     cudaStream_t st = (cudaStream_t)stream;
-    // few LARGE clouds: a cloud's buckets over a cluster of 2..8 CTAs (fps_cqueue_kernel), when all clusters are resident at
-    // once (clusters cannot span GPCs: B = 16 clusters of 8 ran in two waves, 7.1 ms against 3.9).  Below ~65,000 candidates
-    // the chain, not the sweeps, is the pass: one 40,960-candidate cloud measured 3.55 ms either way.
-    if (n >= 65536) {
+    // FEW clouds: a cloud's buckets over a cluster of 8 CTAs (fps_cqueue_kernel), when all clusters are resident at once (clusters
+    // cannot span GPCs: B = 16 clusters of 8 ran in two waves, 7.1 ms against 3.9).  One 40,960-candidate cloud 3.42 -> 2.39 ms,
+    // eight 99,840-candidate clouds 14.4 -> 6.5 ms.
+#ifndef PF_CQ_MIN
+#define PF_CQ_MIN 16384
+#endif
+    if (n >= PF_CQ_MIN) {
         const int NC = 8;
         const int nbc = (nb + NC - 1) / NC, kbc = (nbc + NW - 1) / NW, bplc = (kbc + 31) / 32;
         if (bplc <= 2 && cqueue_smem(nbc) <= 227 * 1024) {
