@@ -1,4 +1,4 @@
-// Continuous-flow (CNF) block of the continuous variant: y(t1) of dy/dt = ODEnet([t, c], y), one thread per point.
+// Continuous-flow (CNF) block of the continuous variant: y(t1) of dy/dt = ODEnet([t, c], y), one or two lanes per point.
 //
 // Replaces CNF.forward + torchdiffeq.odeint(method='dopri5') + ODEfunc / ODEnet / ConcatSquashLinear for the inference path
 // (/root/reference/modules/continuous/cnf.py:51-112, odefunc.py:66-111,121-143, diffeq_layers.py:72-86; the block around it
@@ -18,93 +18,247 @@
 // whole batch, so a point's result depends on its batch-mates and every step needs a grid-wide reduction), and the last step
 // is clipped to end at t1 (torchdiffeq steps past it and interpolates).  Same ODE, same tolerance.
 //
-// FP32 FFMA kernel: 4,480 MACs + 131 sigmoids + 128 tanh per evaluation, 14-130 evaluations per block and point (the later
-// blocks are stiff under real conditioning vectors); the 64 x 64 layer reads its weights as warp-broadcast LDS.128.  The
-// tensor-core version -- 128 points = one M tile, the hidden layer as a split-fp16 MMA per stage -- is the next step for this
-// row (measured times in profiles/r02_cnf.md).
+// FP32 kernel: 4,480 MACs + 131 sigmoids + 128 tanh per evaluation, 14-250 evaluations per block and point (the later
+// blocks are stiff under real conditioning vectors).  What shaped it (profiles/r02_cnf.md):
+//   * code size -- the evaluation is a few rolled loops (6 KB of SASS), not 100 KB of straight-line code that misses the
+//     32 KB instruction cache on every fetch;
+//   * issue slots -- the 64 x 64 layer as packed FFMA2 on warp-broadcast LDS.128 weights, per-channel constants and the
+//     conditioning row re-laid in shared memory so that a channel's constants are two wide loads, sigmoid / tanh as
+//     ex2.approx.ftz + rcp.approx.ftz on pre-scaled arguments;
+//   * points per SM -- forward (a 1 KB conditioning row per point: 128 points fill shared memory) runs two lanes per point;
+//     the inverse (rep points share a row) one lane per point, three 128-point CTAs per SM (register-bound).
+// Compile-time switches below (PF_CNF_*) are the measured alternatives; the defaults are what shipped.
 #include "common.cuh"
 #include "puflow_b200.h"
 
 namespace {
 
-constexpr int NT = 128;                       // points per CTA
 constexpr int CTXW = PF_CNF_CTX;              // 264 floats per conditioning row
-constexpr int CTXS = CTXW + 1;                // row stride in shared memory (odd: conflict-free column reads)
-// weight blob (floats): see packing.pack_cnf_block
+// weight blob in global memory (floats): see packing.pack_cnf_block
 constexpr int O_W0 = 0, O_TG0 = 256, O_TB0 = 320, O_W1 = 384, O_B1 = 4480, O_TG1 = 4544, O_TB1 = 4608, O_W2 = 4672,
               O_L2 = 4864, WBLOB = PF_CNF_BLOB / 4;
 static_assert(WBLOB == 4880, "blob layout");
+// The kernel's own copy in shared memory, re-laid so that everything one output channel needs arrives in two or three wide
+// loads (the scalar LDS of the per-channel constants were a sixth of an evaluation's instructions):
+//   S_L0 [64][8]  W0[j][0..2], b0[j], gate0_t[j] *, bias0_t[j], 0, 0
+//   S_W1 [64][68] W1[j][i] (rows padded to W1S)
+//   S_L1 [64][8]  b1[j], gate1_t[j] *, bias1_t[j], W2[0][j], W2[1][j], W2[2][j], 0, 0
+//   S_L2 [12]     b2[3], gate2_t[3] *, bias2_t[3]
+// and a conditioning row as (gate0_c[j] *, bias0_c[j]) pairs, (gate1_c[j] *, bias1_c[j]) pairs, gate2_c[3] *, bias2_c[3].
+// * = pre-multiplied by -log2(e): a gate is 1 / (1 + 2^(g_t t + g_c)) with no multiply in front of the ex2.
+constexpr int W1S = 68;                       // W1 row stride (floats): the two lanes of a split point read rows j, j + 1 --
+                                              // 68 j mod 32 puts them in different banks
+constexpr int S_L0 = 0, S_W1 = 512, S_L1 = S_W1 + 64 * W1S, S_L2 = S_L1 + 512, SWP = S_L2 + 12;    // SWP % 4 == 0
+constexpr int CTXS = 266;                     // row stride in shared memory (floats): even for the 8-byte pair loads, and
+                                              // 266 l mod 32 takes 16 distinct even values over a half-warp (conflict-free)
+constexpr float NLOG2E = -1.4426950408889634f;
 
-// sigmoid and tanh through ex2.approx + rcp.approx (__expf, __fdividef): 2-3 ulp each plus |x| 2^-24 in the exponent, i.e. a
-// relative error below 2e-6 for the |x| < 20 that occur -- an order of magnitude under the integrator's 1e-5 step tolerance
-// (the accurate expf / tanhf cost 5,000 of an evaluation's 9,500 instructions; these 1,300).  The rest of the library is built
-// without fast-math: there the results are compared at 1e-4 with a reference that has no solver tolerance to hide behind.
-__device__ __forceinline__ float sigmoidf(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
-__device__ __forceinline__ float tanh_fast(float x) {
-    const float e = __expf(2.f * fminf(x, 20.f));                  // e^40 is finite; tanh(20) == 1 in fp32
-    return 1.f - __fdividef(2.f, e + 1.f);
+// sigmoid and tanh through ex2.approx.ftz + rcp.approx.ftz (2 ulp and 1 ulp): a relative error below 2e-6 for the |x| < 20
+// that occur -- an order of magnitude under the integrator's 1e-5 step tolerance (the accurate expf / tanhf cost 5,000 of
+// an evaluation's 9,500 instructions; __expf / __fdividef 1,300 with their range fix-ups; these 650).  Saturation needs
+// no clamp: 2^x overflows to +inf, whose reciprocal is 0.  The rest of the library is built without fast-math: there the
+// results are compared at 1e-4 with a reference that has no solver tolerance to hide behind.
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 }
+__device__ __forceinline__ float rcp_ftz(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float sigmoid_scaled(float xs) { return rcp_ftz(1.f + ex2_ftz(xs)); }     // xs = -x log2(e)
+__device__ __forceinline__ float tanh_fast(float x) { return fmaf(-2.f, rcp_ftz(ex2_ftz(x * (-2.f * NLOG2E)) + 1.f), 1.f); }
 
-// dy = ODEnet([t, c], y).  w: the block's weights in shared memory; cx: this point's conditioning row in shared memory.
-__device__ __noinline__ void dynamics(const float* __restrict__ w, const float* __restrict__ cx, float t, float y0, float y1,
-                                      float y2, float& d0, float& d1, float& d2) {
-    float h0[64], h1[64];
+// dy = ODEnet([t, c], y).  w: the block's weights in shared memory; cx: this point's conditioning row in shared memory;
+// stg: this thread's column of the staging buffer (HST floats, stride NT).
+//
+// Code size matters here: the fully unrolled version (4,500 FFMA + 1,100 LDS + the activations, ~100 KB of SASS) ran out of
+// the 32 KB L1.5 instruction cache -- `stalled_no_instruction` was 2.5-3.3 warps per issue, the issue slots 22-41 % busy
+// (profiles/r02_cnf.md).  So the 64-output loops are real loops: the hidden layer four outputs per iteration (four independent
+// FFMA chains, its input h0 in registers with static indices), the output layer folded into it (h1 is never stored), and the
+// first layer HST outputs at a time through a private shared-memory column, because a rolled loop cannot index registers.
+constexpr int HST = 16;
+#ifndef PF_CNF_FFMA2
+#define PF_CNF_FFMA2 1
+#endif
+#ifndef PF_CNF_UNROLL
+#define PF_CNF_UNROLL 2
+#endif
+#ifndef PF_CNF_INV_NT
+#define PF_CNF_INV_NT 128
+#endif
+#ifndef PF_CNF_INV_OCC
+#define PF_CNF_INV_OCC 3
+#endif
+#ifndef PF_CNF_INV_SPLIT
+#define PF_CNF_INV_SPLIT 1
+#endif
+#ifndef PF_CNF_FWD_SPLIT
+#define PF_CNF_FWD_SPLIT 2
+#endif
+constexpr int UNR = PF_CNF_UNROLL;
+#ifndef PF_CNF_U1
+#define PF_CNF_U1 4
+#endif
+constexpr int U1 = PF_CNF_U1;
+// two FP32 FMAs per instruction (fma.rn.f32x2, FFMA2): the hidden layer's 64-term dot product runs as two 32-term partial
+// sums (even / odd inputs) in one register pair, halving the FMA issue slots of an evaluation.
+__device__ __forceinline__ unsigned long long ffma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+    unsigned long long d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+    return d;
+}
+// SPLIT = 2: two adjacent lanes share a point -- each computes every second output channel of both hidden layers (h0 is
+// exchanged through the staging column, the three output sums by one shuffle each) and both carry the same solver state.
+// Used where shared memory, not registers, bounds the points per SM (the forward direction: a 1 KB conditioning row each).
+template <int NPT, int SPLIT>
+__device__ __noinline__ void dynamics(const float* __restrict__ w, const float* __restrict__ cx, float* __restrict__ stg, float t,
+                                      float y0, float y1, float y2, float& d0, float& d1, float& d2) {
+    constexpr int NT = NPT;                                                                    // staging stride
+    const int half = SPLIT == 2 ? (threadIdx.x & 1) : 0;
+    const unsigned pair = SPLIT == 2 ? 3u << (threadIdx.x & 30) : 0u;                          // the two lanes of this point
+#if PF_CNF_FFMA2
+    unsigned long long h0[32];                                                                // (h0[2i], h0[2i + 1])
+#else
+    float h0[64];
+#endif
 #pragma unroll
-    for (int j = 0; j < 64; j++) {
-        const float4 wj = *reinterpret_cast<const float4*>(w + O_W0 + 4 * j);                 // W0[j][0..2], b0[j]
-        const float pre = fmaf(wj.x, y0, fmaf(wj.y, y1, fmaf(wj.z, y2, wj.w)));
-        const float gate = sigmoidf(fmaf(w[O_TG0 + j], t, cx[j]));
-        h0[j] = tanh_fast(fmaf(pre, gate, fmaf(w[O_TB0 + j], t, cx[64 + j])));
+    for (int q = 0; q < 64 / HST; q++) {
+#pragma unroll U1
+        for (int u0 = 0; u0 < HST / SPLIT; u0++) {
+            const int u = SPLIT * u0 + half, j = q * HST + u;
+            const float4 wj = *reinterpret_cast<const float4*>(w + S_L0 + 8 * j);             // W0[j][0..2], b0[j]
+            const float2 tj = *reinterpret_cast<const float2*>(w + S_L0 + 8 * j + 4);         // gate0_t *, bias0_t
+            const float2 cj = *reinterpret_cast<const float2*>(cx + 2 * j);                   // gate0_c *, bias0_c
+            const float pre = fmaf(wj.x, y0, fmaf(wj.y, y1, fmaf(wj.z, y2, wj.w)));
+            const float gate = sigmoid_scaled(fmaf(tj.x, t, cj.x));
+            stg[u * NT] = tanh_fast(fmaf(pre, gate, fmaf(tj.y, t, cj.y)));
+        }
+        if (SPLIT == 2) __syncwarp(pair);
+#pragma unroll
+#if PF_CNF_FFMA2
+        for (int u = 0; u < HST / 2; u++) h0[q * (HST / 2) + u] = pack2(stg[2 * u * NT], stg[(2 * u + 1) * NT]);
+#else
+        for (int u = 0; u < HST; u++) h0[q * HST + u] = stg[u * NT];
+#endif
+        if (SPLIT == 2) __syncwarp(pair);
     }
+    float o[3] = {w[S_L2], w[S_L2 + 1], w[S_L2 + 2]};                                          // b2
+    if (SPLIT == 2 && half) o[0] = o[1] = o[2] = 0.f;
+    // Hidden layer, software-pipelined by hand: the dot products of outputs group g (UNR independent FFMA2 chains) are issued
+    // together with the activations of group g - 1 (two dependent MUFU round trips each), which would otherwise drain alone
+    // at the end of every iteration with three warps per scheduler to cover them.
+    auto dot = [&](int j) -> float {
+#if PF_CNF_FFMA2
+        unsigned long long acc2 = pack2(w[S_L1 + 8 * j], 0.f);                                 // b1
+        const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(w + S_W1 + W1S * j);
 #pragma unroll
-    for (int j = 0; j < 64; j++) {
-        float acc = w[O_B1 + j];
-        const float4* wr = reinterpret_cast<const float4*>(w + O_W1 + 64 * j);
+        for (int i = 0; i < 16; i++) {
+            const ulonglong2 v = wr[i];
+            acc2 = ffma2(v.y, h0[2 * i + 1], ffma2(v.x, h0[2 * i], acc2));
+        }
+        float acc, acc_odd;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(acc), "=f"(acc_odd) : "l"(acc2));
+        return acc + acc_odd;
+#else
+        float acc = w[S_L1 + 8 * j];
+        const float4* wr = reinterpret_cast<const float4*>(w + S_W1 + W1S * j);
 #pragma unroll
         for (int i = 0; i < 16; i++) {
             const float4 v = wr[i];
             acc = fmaf(v.x, h0[4 * i], fmaf(v.y, h0[4 * i + 1], fmaf(v.z, h0[4 * i + 2], fmaf(v.w, h0[4 * i + 3], acc))));
         }
-        const float gate = sigmoidf(fmaf(w[O_TG1 + j], t, cx[128 + j]));
-        h1[j] = tanh_fast(fmaf(acc, gate, fmaf(w[O_TB1 + j], t, cx[192 + j])));
+        return acc;
+#endif
+    };
+    auto act = [&](int j, float acc) {
+        const float4 lj = *reinterpret_cast<const float4*>(w + S_L1 + 8 * j);                 // b1, gate1_t *, bias1_t, W2[0][j]
+        const float2 l2 = *reinterpret_cast<const float2*>(w + S_L1 + 8 * j + 4);             // W2[1][j], W2[2][j]
+        const float2 cj = *reinterpret_cast<const float2*>(cx + 128 + 2 * j);                 // gate1_c *, bias1_c
+        const float gate = sigmoid_scaled(fmaf(lj.y, t, cj.x));
+        const float h1 = tanh_fast(fmaf(acc, gate, fmaf(lj.z, t, cj.y)));
+        o[0] = fmaf(lj.w, h1, o[0]), o[1] = fmaf(l2.x, h1, o[1]), o[2] = fmaf(l2.y, h1, o[2]);
+    };
+    constexpr int NG = 64 / SPLIT / UNR;
+    float pa[UNR];
+#pragma unroll
+    for (int u = 0; u < UNR; u++) pa[u] = dot(SPLIT * u + half);
+#pragma unroll 1
+    for (int g = 1; g < NG; g++) {
+        float na[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; u++) na[u] = dot(SPLIT * (g * UNR + u) + half);
+#pragma unroll
+        for (int u = 0; u < UNR; u++) act(SPLIT * ((g - 1) * UNR + u) + half, pa[u]);
+#pragma unroll
+        for (int u = 0; u < UNR; u++) pa[u] = na[u];
     }
-    float o[3];
+#pragma unroll
+    for (int u = 0; u < UNR; u++) act(SPLIT * ((NG - 1) * UNR + u) + half, pa[u]);
+    if (SPLIT == 2) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) o[a] += __shfl_xor_sync(pair, o[a], 1);                    // a + b == b + a: both lanes agree
+    }
 #pragma unroll
     for (int a = 0; a < 3; a++) {
-        float acc = w[O_L2 + a];                                                               // b2
-        const float4* wr = reinterpret_cast<const float4*>(w + O_W2 + 64 * a);
-#pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const float4 v = wr[i];
-            acc = fmaf(v.x, h1[4 * i], fmaf(v.y, h1[4 * i + 1], fmaf(v.z, h1[4 * i + 2], fmaf(v.w, h1[4 * i + 3], acc))));
-        }
-        const float gate = sigmoidf(fmaf(w[O_L2 + 3 + a], t, cx[256 + a]));
-        o[a] = fmaf(acc, gate, fmaf(w[O_L2 + 6 + a], t, cx[259 + a]));
+        const float gate = sigmoid_scaled(fmaf(w[S_L2 + 3 + a], t, cx[256 + a]));
+        o[a] = fmaf(o[a], gate, fmaf(w[S_L2 + 6 + a], t, cx[259 + a]));
     }
     d0 = o[0], d1 = o[1], d2 = o[2];
 }
 
 __device__ __forceinline__ float rms3(float a, float b, float c) { return sqrtf((a * a + b * b + c * c) * (1.f / 3.f)); }
 
-__global__ void __launch_bounds__(NT, 2)
+template <int NT, int OCC, int SPLIT>
+__global__ void __launch_bounds__(NT, OCC)
     cnf_flow_kernel(const float* __restrict__ y_in, const float* __restrict__ ctx, int ld_ctx, const float* __restrict__ wblob,
                     float* __restrict__ y_out, int32_t* __restrict__ nfe_out, int M, int rep, float t0, float t1, float atol,
                     float rtol) {
     extern __shared__ __align__(16) float sm[];
     float* w = sm;
-    float* cs = sm + WBLOB;
+    constexpr int NPT = NT / SPLIT;                           // points per CTA
+    float* stg = sm + SWP + threadIdx.x / SPLIT;              // HST x NPT staging columns
+    float* cs = sm + SWP + HST * NPT;
     const int tid = threadIdx.x;
-    const long long p = (long long)blockIdx.x * NT + tid;
-    const long long row0 = ((long long)blockIdx.x * NT) / rep;
-    long long rowl = ((long long)blockIdx.x * NT + NT - 1);
+    const long long p = (long long)blockIdx.x * NPT + tid / SPLIT;
+    const long long row0 = ((long long)blockIdx.x * NPT) / rep;
+    long long rowl = ((long long)blockIdx.x * NPT + NPT - 1);
     if (rowl > M - 1) rowl = M - 1;
     const int nrows = (int)(rowl / rep - row0) + 1;
-    for (int i = tid; i < WBLOB; i += NT) w[i] = __ldg(wblob + i);
+    // weights: global blob order -> the shared-memory layout above
+    for (int i = tid; i < 64 * 8; i += NT) {
+        const int j = i >> 3, c = i & 7;
+        w[S_L0 + i] = c < 4 ? __ldg(wblob + O_W0 + 4 * j + c)
+                            : (c == 4 ? NLOG2E * __ldg(wblob + O_TG0 + j) : (c == 5 ? __ldg(wblob + O_TB0 + j) : 0.f));
+        w[S_L1 + i] = c == 0 ? __ldg(wblob + O_B1 + j)
+                             : (c == 1 ? NLOG2E * __ldg(wblob + O_TG1 + j)
+                                       : (c == 2 ? __ldg(wblob + O_TB1 + j) : (c < 6 ? __ldg(wblob + O_W2 + 64 * (c - 3) + j) : 0.f)));
+    }
+    for (int i = tid; i < 4096; i += NT) w[S_W1 + W1S * (i >> 6) + (i & 63)] = __ldg(wblob + O_W1 + i);
+    if (tid < 9) w[S_L2 + tid] = (tid >= 3 && tid < 6 ? NLOG2E : 1.f) * __ldg(wblob + O_L2 + tid);
+    // conditioning rows: columns [gate0 | bias0 | gate1 | bias1 | gate2 (3) | bias2 (3)] -> interleaved pairs, gates scaled
     for (int i = tid; i < nrows * (CTXW / 4); i += NT) {          // 66 float4 per row
         const int r = i / (CTXW / 4), c4 = i % (CTXW / 4);
         const float4 v = __ldg(reinterpret_cast<const float4*>(ctx + (row0 + r) * (long long)ld_ctx) + c4);
-        float* d = cs + r * CTXS + 4 * c4;
-        d[0] = v.x, d[1] = v.y, d[2] = v.z, d[3] = v.w;
+        const float vv[4] = {v.x, v.y, v.z, v.w};
+        float* d = cs + r * CTXS;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int c = 4 * c4 + u;
+            if (c < 256) {
+                const int blk = c >> 6, j = c & 63;                // blk: 0 gate0, 1 bias0, 2 gate1, 3 bias1
+                d[128 * (blk >> 1) + 2 * j + (blk & 1)] = (blk & 1) ? vv[u] : NLOG2E * vv[u];
+            } else if (c < 262) {
+                d[c] = c < 259 ? NLOG2E * vv[u] : vv[u];
+            }
+        }
     }
     __syncthreads();
     if (p >= M) return;
@@ -116,7 +270,7 @@ __global__ void __launch_bounds__(NT, 2)
     float k[7][3];
     auto f = [&](float s, float a0, float a1, float a2, float (&out)[3]) {
         float d0, d1, d2;
-        dynamics(w, cx, fmaf(sgn, s, t0), a0, a1, a2, d0, d1, d2);
+        dynamics<NPT, SPLIT>(w, cx, stg, fmaf(sgn, s, t0), a0, a1, a2, d0, d1, d2);
         out[0] = sgn * d0, out[1] = sgn * d1, out[2] = sgn * d2;
     };
     int nfe = 2;
@@ -180,6 +334,7 @@ __global__ void __launch_bounds__(NT, 2)
         const float fac = ratio == 0.f ? 10.f : fminf(10.f, fmaxf(0.9f / powf(ratio, 0.2f), ratio < 1.f ? 1.f : 0.2f));
         h = hs * fac;
     }
+    if (SPLIT == 2 && (tid & 1)) return;
     y_out[p * 3] = y[0], y_out[p * 3 + 1] = y[1], y_out[p * 3 + 2] = y[2];
     if (nfe_out) nfe_out[p] = s >= span ? nfe : -nfe;          // negative: the step budget ran out (never seen; tests assert > 0)
 }
@@ -196,11 +351,18 @@ extern "C" int pf_cnf_flow(const float* y_in, const float* ctx, int ld_ctx, cons
                  "pf_cnf_flow: ctx and wblob must be 16-byte aligned");
     PF_CHECK_ARG(atol > 0.f && rtol >= 0.f && t0 == t0 && t1 == t1, "pf_cnf_flow: atol=%g rtol=%g t0=%g t1=%g", (double)atol,
                  (double)rtol, (double)t0, (double)t1);
-    // conditioning rows a CTA's 128 points can touch: 128 for rep = 1, 33 for rep = 4 (then two CTAs share an SM)
-    const int rows_max = (NT + rep - 1) / rep + 1;
-    const size_t smem = (size_t)(WBLOB + (rows_max < NT ? rows_max : NT) * CTXS) * 4;
-    if (int rc = pf_smem_optin(cnf_flow_kernel, smem)) return rc;
-    const int grid = (M + NT - 1) / NT;
-    cnf_flow_kernel<<<grid, NT, smem, (cudaStream_t)stream>>>(y_in, ctx, ld_ctx, wblob, y_out, nfe, M, rep, t0, t1, atol, rtol);
+    // rep = 1 (forward: a conditioning row per point, 1,060 bytes each): 128 points per CTA, one CTA per SM.
+    // rep >= 2 (inverse: rep points share a row): PF_CNF_INV_NT points per CTA, PF_CNF_INV_OCC CTAs per SM.
+    auto launch = [&](auto kernel, int nt, int npt) -> int {
+        const int rows_max = (npt + rep - 1) / rep + 1;
+        const size_t smem = (size_t)(SWP + HST * npt + (rows_max < npt ? rows_max : npt) * CTXS) * 4;
+        if (int rc = pf_smem_optin(kernel, smem)) return rc;
+        kernel<<<(M + npt - 1) / npt, nt, smem, (cudaStream_t)stream>>>(y_in, ctx, ld_ctx, wblob, y_out, nfe, M, rep, t0, t1, atol, rtol);
+        return 0;
+    };
+    if (int rc = rep >= 4 ? launch(cnf_flow_kernel<PF_CNF_INV_NT, PF_CNF_INV_OCC, PF_CNF_INV_SPLIT>, PF_CNF_INV_NT,
+                                   PF_CNF_INV_NT / PF_CNF_INV_SPLIT)
+                          : launch(cnf_flow_kernel<128 * PF_CNF_FWD_SPLIT, 1, PF_CNF_FWD_SPLIT>, 128 * PF_CNF_FWD_SPLIT, 128))
+        return rc;
     return pf_launch_status("cnf_flow_kernel");
 }

