@@ -76,7 +76,10 @@ PF_API int pf_knn_topk(const float* q, const float* p, int B, int nq, int np, in
  * Replaces chamfer_3D.forward / NmDistanceKernel,
  * /root/reference/metric/PyTorchCD/chamfer3D/chamfer3D.cu:12-154 (both directions, one call).
  * a[B][n][3], b[B][m][3] -> dist1[B][n], idx1[B][n] (nearest in b), dist2[B][m], idx2[B][m]
- * (nearest in a); squared distances; the lowest index wins ties (strict <, chamfer3D.cu:36-69,126).  dist2 and idx2 may both be NULL: only the a -> b direction is computed. */
+ * (nearest in a); squared distances; the lowest index wins ties (strict <, chamfer3D.cu:36-69,126).  dist2 and idx2 may both be NULL: only the a -> b direction is computed.
+ * A direction with 256..8,192 candidates and >= 1,024 queries per cloud is pruned with a grid over the candidates (exact:
+ * the same bits as the exhaustive scan, csrc/nn.cu); a non-finite candidate coordinate is never selected (as NaN / inf
+ * distances never compare below), and idx is -1 where no candidate has a finite distance. */
 PF_API int pf_chamfer_nn(const float* a, int n, const float* b, int m, int B, float* dist1, int32_t* idx1, float* dist2,
                   int32_t* idx2, void* stream);
 

@@ -32,6 +32,9 @@ namespace {
 constexpr int QT = 128;     // queries (threads) per CTA
 constexpr int CT = 512;     // candidates per shared-memory tile (6 KB raw x2 buffers + 6 KB transposed)
 constexpr float INF = __builtin_huge_valf();
+#ifndef PF_NN_GRID_MIN
+#define PF_NN_GRID_MIN 256              // candidates per cloud from which pf_chamfer_nn prunes with a grid
+#endif
 
 // ---- packed fp32 (two candidates per instruction) ----
 __device__ __forceinline__ uint64_t pk(float a, float b) {
@@ -324,6 +327,224 @@ int launch_knn(const float* q, const float* p, int B, int nq, int np, int kout, 
     return pf_launch_status("knn_kernel");
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Grid-pruned exact nearest neighbour (K = 1) for the Chamfer pass: same result as knn_kernel<1>, bit for bit (squared
+// distance by the same individually rounded operations, the lowest index among equal distances), from ~30 candidates per
+// query instead of all np.
+//
+// Every CTA bins its cloud's np candidates into a G^3 grid over their bounding box in shared memory (counting sort: cell
+// histogram by shared-memory atomics, block scan, scatter as (x, y, z, index) float4 -- the order inside a cell is whatever
+// the atomics give and does not matter: the minimum is taken over (distance, index)).  Four adjacent lanes serve one query:
+// they walk the cells of ring r = 1, 2, ... around the query's cell (Chebyshev distance <= 1, then == r) as rows of x-adjacent
+// cells (contiguous in the sorted array), every lane a quarter of each row's points, and combine their (distance, index)
+// minima by two shuffles per ring.  The search stops when the best
+// distance is below the distance to the nearest face of the searched cube that has grid behind it (minus a rounding
+// allowance: 1e-5 of the coordinates' scale on the gap and 1e-5 on its square, against ~1e-7 of rounding in the distances
+// and in the binning), or when the cube covers the grid.  Everything outside the cube is provably farther than the
+// incumbent, so neither the minimum nor the tie order can change.  A cloud whose bounding box is not finite takes a plain
+// scan of all candidates in the same kernel.
+constexpr int GT = 256;                        // threads per CTA: 64 four-lane query groups
+#ifndef PF_NN_GQ
+#define PF_NN_GQ 16
+#endif
+#ifndef PF_NN_G
+#define PF_NN_G 16
+#endif
+constexpr int GQ = PF_NN_GQ;                   // queries per group -> 1,024 queries per CTA
+
+template <int G>
+struct GridSmem {
+    static constexpr int NC = G * G * G;
+    static size_t bytes(int np) { return (size_t)((np + 3) & ~3) * 16 + (size_t)(2 * NC + 4) * 4; }
+};
+
+template <int G>
+__global__ void __launch_bounds__(GT) nn_grid_kernel(const float* __restrict__ q, const float* __restrict__ p, int nq, int np,
+                                                     int32_t* __restrict__ idx, float* __restrict__ dist) {
+    constexpr int NC = G * G * G, CPT = (NC + GT - 1) / GT;
+    extern __shared__ __align__(16) uint8_t gsm[];
+    float4* pts = reinterpret_cast<float4*>(gsm);
+    int* cstart = reinterpret_cast<int*>(pts + ((np + 3) & ~3));      // [NC + 1]
+    int* cur = cstart + NC + 4;                                      // [NC] histogram, then scatter cursors
+    __shared__ float red[GT / 32][6];
+    __shared__ float bb[10];                                         // min[3], cell size[3], 1 / cell size[3], rounding allowance
+    __shared__ int wsum[GT / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, b = blockIdx.y;
+    const float* pb = p + (size_t)b * np * 3;
+    const float* qb = q + (size_t)b * nq * 3;
+
+    // ---- bounding box ----
+    float lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
+    for (int i = tid; i < np; i += GT) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const float v = __ldg(pb + 3 * i + a);
+            lo[a] = fminf(lo[a], v), hi[a] = fmaxf(hi[a], v);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+        if (lane == 0) red[warp][a] = lo[a], red[warp][3 + a] = hi[a];
+    }
+    for (int i = tid; i < NC; i += GT) cur[i] = 0;
+    __syncthreads();
+    if (tid < 3) {
+        float l = red[0][tid], h = red[0][3 + tid];
+        for (int w = 1; w < GT / 32; w++) l = fminf(l, red[w][tid]), h = fmaxf(h, red[w][3 + tid]);
+        const float ext = h - l;
+        bb[tid] = l, bb[3 + tid] = ext / G, bb[6 + tid] = ext > 0.f ? G / ext : 0.f;
+        red[0][tid] = ext;                                           // (read back below, after the barrier)
+    }
+    __syncthreads();
+    const float ex = red[0][0], ey = red[0][1], ez = red[0][2];
+    const bool finite_box = ex < INF && ey < INF && ez < INF && ex == ex && ey == ey && ez == ez;   // uniform
+    const float mnx = bb[0], mny = bb[1], mnz = bb[2], hx = bb[3], hy = bb[4], hz = bb[5], ivx = bb[6], ivy = bb[7], ivz = bb[8];
+    const float ext_max = fmaxf(ex, fmaxf(ey, ez));
+    auto cell1 = [](float v, float mn, float iv) { return min(G - 1, max(0, (int)((v - mn) * iv))); };
+
+    if (finite_box) {
+        // ---- counting sort of the candidates by cell ----
+        for (int i = tid; i < np; i += GT) {
+            const int c = (cell1(__ldg(pb + 3 * i + 2), mnz, ivz) * G + cell1(__ldg(pb + 3 * i + 1), mny, ivy)) * G +
+                          cell1(__ldg(pb + 3 * i), mnx, ivx);
+            atomicAdd(cur + c, 1);
+        }
+        __syncthreads();
+        int cnt[CPT], tot = 0;
+#pragma unroll
+        for (int k = 0; k < CPT; k++) {
+            const int c = tid * CPT + k;
+            cnt[k] = c < NC ? cur[c] : 0;
+            tot += cnt[k];
+        }
+        int incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        int base = incl - tot;
+        for (int w = 0; w < warp; w++) base += wsum[w];
+#pragma unroll
+        for (int k = 0; k < CPT; k++) {
+            const int c = tid * CPT + k;
+            if (c < NC) cstart[c] = base, cur[c] = base;
+            base += cnt[k];
+        }
+        if (tid == GT - 1) cstart[NC] = base;
+        __syncthreads();
+        for (int i = tid; i < np; i += GT) {
+            const float x = __ldg(pb + 3 * i), y = __ldg(pb + 3 * i + 1), z = __ldg(pb + 3 * i + 2);
+            const int c = (cell1(z, mnz, ivz) * G + cell1(y, mny, ivy)) * G + cell1(x, mnx, ivx);
+            pts[atomicAdd(cur + c, 1)] = make_float4(x, y, z, __int_as_float(i));
+        }
+        __syncthreads();
+    }
+
+    // ---- queries: four lanes each ----
+    const int grp = tid >> 2, sub = tid & 3;
+    const unsigned gmask = 0xFu << (lane & 28);
+    auto better = [](float d, int i, float bd, int bi) { return d < bd || (d == bd && i < bi); };
+#ifdef PF_NN_SKIPQ
+    if (nq > 0) return;
+#endif
+    for (int k = 0; k < GQ; k++) {
+        const int qi = (blockIdx.x * GQ + k) * (GT / 4) + grp;
+        if (qi >= nq) break;
+        const float qx = __ldg(qb + 3 * qi), qy = __ldg(qb + 3 * qi + 1), qz = __ldg(qb + 3 * qi + 2);
+        float best = INF;
+        int bi = -1;
+        auto visit = [&](float x, float y, float z, int i) {
+            const float dx = __fsub_rn(qx, x), dy = __fsub_rn(qy, y), dz = __fsub_rn(qz, z);
+            const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            if (better(d, i, best, bi)) best = d, bi = i;
+        };
+        auto combine = [&]() {
+#pragma unroll
+            for (int o = 1; o < 4; o <<= 1) {
+                const float od = __shfl_xor_sync(gmask, best, o);
+                const int oi = __shfl_xor_sync(gmask, bi, o);
+                if (better(od, oi, best, bi) && oi >= 0) best = od, bi = oi;
+            }
+        };
+        if (!finite_box) {
+            for (int s = sub; s < np; s += 4) visit(__ldg(pb + 3 * s), __ldg(pb + 3 * s + 1), __ldg(pb + 3 * s + 2), s);
+            combine();
+        } else {
+            const int cx = cell1(qx, mnx, ivx), cy = cell1(qy, mny, ivy), cz = cell1(qz, mnz, ivz);
+            const float eps = 1e-5f * (ext_max + fabsf(qx) + fabsf(qy) + fabsf(qz));
+            auto scan = [&](int c0, int c1) {                          // the points of cells [c0, c1]: one contiguous range
+                const int s1 = cstart[c1 + 1];
+                for (int s = cstart[c0] + sub; s < s1; s += 4) {
+                    const float4 v = pts[s];
+                    visit(v.x, v.y, v.z, __float_as_int(v.w));
+                }
+            };
+            // ring 1 first (the 3 x 3 x 3 block: the query's own cell alone almost never proves anything), as 9 rows of
+            // x-adjacent cells -- a row's points are contiguous in the sorted array; ring r >= 2: full rows on the shell's
+            // z / y faces, the two end cells of the others
+            for (int r = 1;; r++) {
+                const int x0 = max(cx - r, 0), x1 = min(cx + r, G - 1), y0 = max(cy - r, 0), y1 = min(cy + r, G - 1),
+                          z0 = max(cz - r, 0), z1 = min(cz + r, G - 1);
+                for (int z = z0; z <= z1; z++)
+                    for (int y = y0; y <= y1; y++) {
+                        const int row = (z * G + y) * G;
+                        if (r == 1 || abs(z - cz) == r || abs(y - cy) == r) {
+                            scan(row + x0, row + x1);
+                        } else {
+                            if (cx - r >= 0) scan(row + cx - r, row + cx - r);
+                            if (cx + r <= G - 1) scan(row + cx + r, row + cx + r);
+                        }
+                    }
+                combine();
+                // (an axis of zero extent has all its points in cell 0 and nothing behind any face)
+                const bool allx = (x0 == 0 && x1 == G - 1) || !(ex > 0.f), ally = (y0 == 0 && y1 == G - 1) || !(ey > 0.f),
+                           allz = (z0 == 0 && z1 == G - 1) || !(ez > 0.f);
+                if (allx && ally && allz) break;
+                float gap = INF;                                       // to the nearest face with grid behind it
+                if (!allx && x0 > 0) gap = fminf(gap, qx - (mnx + x0 * hx));
+                if (!allx && x1 < G - 1) gap = fminf(gap, (mnx + (x1 + 1) * hx) - qx);
+                if (!ally && y0 > 0) gap = fminf(gap, qy - (mny + y0 * hy));
+                if (!ally && y1 < G - 1) gap = fminf(gap, (mny + (y1 + 1) * hy) - qy);
+                if (!allz && z0 > 0) gap = fminf(gap, qz - (mnz + z0 * hz));
+                if (!allz && z1 < G - 1) gap = fminf(gap, (mnz + (z1 + 1) * hz) - qz);
+                gap -= eps;
+                if (gap > 0.f && best <= gap * gap * (1.f - 1e-5f)) break;
+            }
+        }
+        if (sub == 0) {
+            idx[(size_t)b * nq + qi] = bi;
+            if (dist) dist[(size_t)b * nq + qi] = best;
+        }
+    }
+}
+
+template <int G>
+int launch_nn_grid(const float* q, const float* p, int B, int nq, int np, int32_t* idx, float* dist, cudaStream_t st) {
+    const int qpc = GQ * (GT / 4);
+    dim3 grid((nq + qpc - 1) / qpc, B);
+    auto kern = nn_grid_kernel<G>;
+    const size_t smem = GridSmem<G>::bytes(np);
+    if (int rc = pf_smem_optin(kern, smem)) return rc;
+    kern<<<grid, GT, smem, st>>>(q, p, nq, np, idx, dist);
+    return pf_launch_status("nn_grid_kernel");
+}
+
+// nearest candidate of every query: the grid kernel where it pays (enough candidates to prune, enough queries to amortise
+// the binning every CTA repeats), the brute-force kernel otherwise
+int launch_nn1(const float* q, const float* p, int B, int nq, int np, int32_t* idx, float* dist, cudaStream_t st) {
+    if (np >= PF_NN_GRID_MIN && np <= 8192 && nq >= 1024)
+        return np >= 1024 ? launch_nn_grid<PF_NN_G>(q, p, B, nq, np, idx, dist, st) : launch_nn_grid<8>(q, p, B, nq, np, idx, dist, st);
+    return launch_knn<1>(q, p, B, nq, np, 1, idx, dist, st);
+}
+
 }  // namespace
 
 extern "C" int pf_knn_topk(const float* q, const float* p, int B, int nq, int np, int K, int32_t* idx, float* dist,
@@ -348,7 +569,7 @@ extern "C" int pf_chamfer_nn(const float* a, int n, const float* b, int m, int B
     PF_CHECK_ARG(B >= 0 && n > 0 && m > 0 && B <= 65535, "pf_chamfer_nn: bad sizes B=%d n=%d m=%d", B, n, m);
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    int rc = launch_knn<1>(a, b, B, n, m, 1, idx1, dist1, st);
+    int rc = launch_nn1(a, b, B, n, m, idx1, dist1, st);
     if (rc || !dist2) return rc;          // dist2 == idx2 == NULL: a -> b direction only (what remove_outliers consumes)
-    return launch_knn<1>(b, a, B, m, n, 1, idx2, dist2, st);
+    return launch_nn1(b, a, B, m, n, idx2, dist2, st);
 }

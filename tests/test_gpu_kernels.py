@@ -113,6 +113,55 @@ def test_chamfer_bit_exact(ops, dev, B, n, m):
         assert np.array_equal(o.cpu().numpy(), r)
 
 
+@pytest.mark.parametrize("case", ["surface", "plane", "line", "one_point", "lattice", "far_queries", "clusters", "nonfinite",
+                                  "np256", "np1000", "np8192"])
+def test_chamfer_grid_pruning_is_exact(ops, dev, case):
+    """pf_chamfer_nn prunes with a grid from 256 candidates per cloud (csrc/nn.cu nn_grid_kernel); pf_knn_topk(K = 1) is the
+    brute-force kernel.  Same distances and indices, bit for bit (chamfer3D.cu:36-69,126: strict <, the lowest index wins),
+    on the geometries that stress the pruning bound: degenerate bounding boxes, exact ties, queries outside the box,
+    clustered candidates (empty cells), non-finite coordinates; and against the C oracle on the smaller ones."""
+    rng = np.random.default_rng(len(case))
+    B, n, m = 3, 4096, 2048
+    if case == "surface":
+        b = synth.make_clouds(B, m, seed=3)
+        a = np.repeat(b, 2, axis=1) + rng.normal(0, 0.01, (B, 2 * m, 3)).astype(np.float32)
+    elif case == "plane":
+        b = rng.uniform(-1, 1, (B, m, 3)).astype(np.float32); b[..., 2] = 0.25
+        a = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    elif case == "line":
+        b = np.zeros((B, m, 3), np.float32); b[..., 0] = rng.uniform(-1, 1, (B, m))
+        a = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    elif case == "one_point":
+        b = np.full((B, m, 3), 0.5, np.float32)
+        a = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32)
+    elif case == "lattice":                                   # equal distances everywhere: the tie order must survive the pruning
+        g = np.stack(np.meshgrid(*[np.arange(16)] * 3, indexing="ij"), -1).reshape(-1, 3).astype(np.float32)
+        b = np.stack([g[rng.permutation(4096)][:m] for _ in range(B)])
+        a = np.stack([g[rng.permutation(4096)] + np.float32(0.5) for _ in range(B)])
+    elif case == "far_queries":
+        b = rng.uniform(-1, 1, (B, m, 3)).astype(np.float32)
+        a = (rng.uniform(-1, 1, (B, n, 3)) * np.array([1000.0, 3.0, 1.0])).astype(np.float32)
+    elif case == "clusters":
+        c = rng.uniform(-1, 1, (B, 8, 1, 3)); b = (c + rng.normal(0, 0.01, (B, 8, m // 8, 3))).reshape(B, m, 3).astype(np.float32)
+        a = rng.uniform(-1.5, 1.5, (B, n, 3)).astype(np.float32)
+    elif case == "nonfinite":
+        b = rng.uniform(-1, 1, (B, m, 3)).astype(np.float32)
+        b[0, 5, 1] = np.nan; b[1, 7, 0] = np.inf                # cloud 0: a NaN candidate is never chosen; cloud 1: unbounded box
+        a = rng.uniform(-1, 1, (B, n, 3)).astype(np.float32); a[2, 3, 2] = np.nan
+    else:
+        m = int(case[2:])
+        b = rng.uniform(-1, 1, (B, m, 3)).astype(np.float32)
+        a = rng.uniform(-1, 1, (B, 1500, 3)).astype(np.float32)
+        a[:, :40] = b[:, :40]                                   # exact zeros
+    ta, tb = torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev)
+    d1, _, i1, _ = ops.chamfer_nn(ta, tb, both=False)
+    dk, ik = ops.knn_topk(ta, tb, 1)
+    assert torch.equal(i1, ik[..., 0]) and torch.equal(d1.view(torch.int32), dk[..., 0].view(torch.int32))
+    if case in ("surface", "lattice", "np256", "np1000"):
+        ref = po.chamfer_nn(a, b)
+        assert np.array_equal(d1.cpu().numpy(), ref[0]) and np.array_equal(i1.cpu().numpy(), ref[2])
+
+
 # ---- linear ----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("M,K,N,act", [(512, 3, 128, 0), (300, 32, 256, 0), (1000, 128, 512, 0), (256, 128, 64, 1),
                                        (130, 64, 16, 1), (257, 160, 192, 2), (128, 3, 640, 0), (1, 16, 32, 0)])
