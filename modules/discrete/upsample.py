@@ -60,16 +60,40 @@ def upsampling(data_paths: List[str], target_path: str, checkpoint_path: str, up
     by_size = {}
     for i, c in enumerate(clouds):
         by_size.setdefault(c.shape[0], []).append(i)
-    for n, members in by_size.items():
-        for j in range(0, len(members), batch_clouds):
-            chunk = members[j:j + batch_clouds]
-            pred = upsample_array(network, patch_helper, np.stack([clouds[i] for i in chunk], 0), up_ratio, num_outlier,
-                                  num_upsampling, device)
-            for i, p in zip(chunk, pred):
-                save_xyz(Path(target_path) / os.path.split(paths[i])[1], p)  # np.savetxt(..., fmt='%.6f'), upsample.py:57
+    chunks = [members[j:j + batch_clouds] for members in by_size.values() for j in range(0, len(members), batch_clouds)]
+    batches = (torch.from_numpy(np.stack([clouds[i] for i in chunk], 0)).pin_memory() for chunk in chunks)
+    # pipelined: batch i's result is copied out and its files are written while batch i + 1 is on the GPU
+    for chunk, pred in zip(chunks, upsample_arrays(network, patch_helper, batches, up_ratio, num_outlier, num_upsampling, device)):
+        for i, p in zip(chunk, pred):
+            save_xyz(Path(target_path) / os.path.split(paths[i])[1], p)  # np.savetxt(..., fmt='%.6f'), upsample.py:57
 
 
 # -----------------------------------------------------------------------------------------
+def _check_clouds(clouds, who):
+    src = torch.from_numpy(clouds) if isinstance(clouds, np.ndarray) else clouds
+    if src.dim() != 3 or src.shape[2] != 3 or src.dtype != torch.float32:
+        raise ValueError(f"{who}: expected fp32 clouds[B,N,3], got {tuple(src.shape)} {src.dtype}")
+    return src
+
+
+def _upsample_device(network, patch_helper, pt_input, up_ratio, num_outlier, num_upsampling, device, graph):
+    """The device part of the per-file body of the reference's loop (upsample.py:46-54) for clouds[B,N,3] on the device:
+    PatchHelper.upsample + remove_outliers, on the current stream; returns a device tensor the caller owns."""
+    n_pts = pt_input.shape[1] * up_ratio if num_upsampling is None else num_upsampling
+    n_drop = num_outlier or 0
+    eng = network.engine(device) if hasattr(network, "engine") else None
+    k = patch_helper.npoint_patch
+    n_patch = int(pt_input.shape[1] / k * patch_helper.patch_expand_ratio)
+    if eng is not None and eng.flow_tc and pt_input.shape[1] >= k >= 16 and 1 <= n_patch <= pt_input.shape[1] \
+            and not ops.per_launch_events_wanted():
+        # the whole per-file body of the reference's loop in one C call, replayed from a CUDA graph per shape
+        return eng.upsample_clouds(pt_input, up_ratio, n_pts + n_drop, n_drop, k, n_patch, graph=graph)
+    pred = patch_helper.upsample(network, pt_input, npoint=n_pts + n_drop, upratio=up_ratio, jitter=False)
+    if n_drop > 0:
+        pred = PatchHelper.remove_outliers(pred, pt_input, n_drop)
+    return pred
+
+
 @torch.no_grad()
 def upsample_array(network, patch_helper, clouds, up_ratio: int = 4, num_outlier: int = 24,
                    num_upsampling: int = None, device=None, out: torch.Tensor = None, graph: bool = True):
@@ -80,30 +104,67 @@ def upsample_array(network, patch_helper, clouds, up_ratio: int = 4, num_outlier
     returns after the result has landed in host memory.  With the drop-in PointInterpFlow the device part is ONE C call
     (pf_upsample_clouds) replayed from a CUDA graph captured per cloud shape (graph=False launches it directly)."""
     device = torch.device(device) if device is not None else next(network.parameters()).device
-    src = torch.from_numpy(clouds) if isinstance(clouds, np.ndarray) else clouds
-    if src.dim() != 3 or src.shape[2] != 3 or src.dtype != torch.float32:
-        raise ValueError(f"upsample_array: expected fp32 clouds[B,N,3], got {tuple(src.shape)} {src.dtype}")
+    src = _check_clouds(clouds, "upsample_array")
     pt_input = src.to(device, non_blocking=True).contiguous()
-
-    n_pts = pt_input.shape[1] * up_ratio if num_upsampling is None else num_upsampling
-    n_drop = num_outlier or 0
-    eng = network.engine(device) if hasattr(network, "engine") else None
-    k = patch_helper.npoint_patch
-    n_patch = int(pt_input.shape[1] / k * patch_helper.patch_expand_ratio)
-    if eng is not None and eng.flow_tc and pt_input.shape[1] >= k >= 16 and 1 <= n_patch <= pt_input.shape[1] \
-            and not ops.per_launch_events_wanted():
-        # the whole per-file body of the reference's loop in one C call, replayed from a CUDA graph per shape
-        pred = eng.upsample_clouds(pt_input, up_ratio, n_pts + n_drop, n_drop, k, n_patch, graph=graph)
-    else:
-        pred = patch_helper.upsample(network, pt_input, npoint=n_pts + n_drop, upratio=up_ratio, jitter=False)
-        if n_drop > 0:
-            pred = PatchHelper.remove_outliers(pred, pt_input, n_drop)
-
+    pred = _upsample_device(network, patch_helper, pt_input, up_ratio, num_outlier, num_upsampling, device, graph)
     if out is not None:
         out.copy_(pred, non_blocking=True)
         torch.cuda.current_stream(device).synchronize()
         return out
     return pred.cpu().numpy()
+
+
+@torch.no_grad()
+def upsample_arrays(network, patch_helper, batches, up_ratio: int = 4, num_outlier: int = 24, num_upsampling: int = None,
+                    device=None, outs=None, graph: bool = True):
+    """upsample_array over a sequence of host batches, pipelined: a generator that yields one result per batch, in order.
+    The kernels of batch i run on the current stream while batch i + 1's host->device copy and batch i - 1's
+    device->host copy run on two copy streams, so a loop over files / batches (the reference's, upsample.py:40-57) costs
+    the kernels alone once it is rolling.  `batches`: iterable of clouds[B,N,3] fp32 host arrays (pinned CPU tensors
+    overlap; pageable memory and numpy arrays work, their copies just synchronise).  `outs`: optional sequence of pinned
+    CPU tensors used round-robin for the results (at least two; a yielded tensor is overwritten `len(outs)` batches
+    later); without it every result is a fresh numpy array.  Results are identical to upsample_array's."""
+    device = torch.device(device) if device is not None else next(network.parameters()).device
+    cur = torch.cuda.current_stream(device)
+    s_in, s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    if outs is not None and len(outs) < 2:
+        raise ValueError("upsample_arrays: outs needs at least two buffers (one is being filled while the previous is read)")
+
+    def stage_in(clouds):
+        src = _check_clouds(clouds, "upsample_arrays")
+        with torch.cuda.stream(s_in):
+            t = src.to(device, non_blocking=True).contiguous()
+            ev = torch.cuda.Event()
+            ev.record(s_in)
+        return t, ev
+
+    it = iter(batches)
+    nxt = next(it, None)
+    staged = stage_in(nxt) if nxt is not None else None
+    pending, i = None, 0
+    while staged is not None:
+        pt_input, ev_in = staged
+        cur.wait_event(ev_in)
+        pt_input.record_stream(cur)
+        pred = _upsample_device(network, patch_helper, pt_input, up_ratio, num_outlier, num_upsampling, device, graph)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        nxt = next(it, None)                        # batch i + 1 goes up while batch i computes
+        staged = stage_in(nxt) if nxt is not None else None
+        host = outs[i % len(outs)] if outs is not None else torch.empty(pred.shape, dtype=pred.dtype, pin_memory=True)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ready)
+            host.copy_(pred, non_blocking=True)
+            pred.record_stream(s_out)
+            done = torch.cuda.Event()
+            done.record(s_out)
+        if pending is not None:
+            pending[0].synchronize()
+            yield pending[1] if outs is not None else pending[1].numpy()
+        pending, i = (done, host), i + 1
+    if pending is not None:
+        pending[0].synchronize()
+        yield pending[1] if outs is not None else pending[1].numpy()
 
 
 # -----------------------------------------------------------------------------------------

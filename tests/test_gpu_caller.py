@@ -134,6 +134,29 @@ def test_upsample_array_host_buffers(net):
     assert a.shape == (2, 2048, 3) and np.array_equal(a, b) and np.array_equal(a, out.numpy())
 
 
+def test_upsample_arrays_pipelined_loop(net):
+    """upsample_arrays (copies of neighbouring batches on copy streams under the kernels) yields, in order, exactly what
+    one synchronous upsample_array call per batch returns: different data per batch, two cloud sizes (two CUDA graphs),
+    pinned result buffers used round-robin, numpy results without them, an empty sequence."""
+    from modules.discrete.upsample import upsample_array, upsample_arrays
+    from modules.utils.patch import PatchHelper
+    ph = PatchHelper(256, patch_expand_ratio=4)
+    batches = [synth.make_clouds(2, 512, seed=s) for s in (1, 2, 3, 4, 5)] + [synth.make_clouds(2, 1024, seed=6)]
+    want = [upsample_array(net, ph, b, 4, 24, None, DEV) for b in batches]
+    got = [r.copy() for r in upsample_arrays(net, ph, batches, 4, 24, None, DEV)]
+    assert len(got) == len(want) and all(np.array_equal(g, w) for g, w in zip(got, want))
+    outs = [torch.empty((2, 2048, 3)).pin_memory() for _ in range(2)]
+    pinned = (torch.from_numpy(b).pin_memory() for b in batches[:5])
+    n = 0
+    for i, r in enumerate(upsample_arrays(net, ph, pinned, 4, 24, None, DEV, outs=outs)):
+        assert r is outs[i % 2] and np.array_equal(r.numpy(), want[i])       # valid until two batches later
+        n += 1
+    assert n == 5
+    assert list(upsample_arrays(net, ph, [], 4, 24, None, DEV)) == []
+    with pytest.raises(ValueError):
+        list(upsample_arrays(net, ph, batches[:1], 4, 24, None, DEV, outs=outs[:1]))
+
+
 def test_two_host_threads_two_streams(net):
     """One host thread per stream through pf_upsample_patches (profiling off): no shared scratch, no shared state
     (SURVEY.md section 8b 'kernels re-entrant'); both results equal the single-threaded one."""
