@@ -21,6 +21,7 @@ def tag_of(name):
     if "interp_tc_kernel" in name: return "interp_tc"
     m = re.search(r"knn_kernel<(\d+)>", name)
     if m: return "chamfer_nn" if m.group(1) == "1" else f"knn_topk_k{m.group(1)}"
+    if "nn_grid_kernel" in name: return "chamfer_nn"
     if "knn_patch_kernel" in name: return "knn_patch"
     if any(k in name for k in ("fps_bucket_kernel", "fps_queue_kernel", "fps_cqueue_kernel", "fps_cluster_kernel")): return "fps_n40960"
     if re.search(r"\bfps_kernel", name) or "fps_cta_kernel" in name: return "fps_n2048"
