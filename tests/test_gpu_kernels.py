@@ -164,7 +164,8 @@ def test_chamfer_grid_pruning_is_exact(ops, dev, case):
 
 # ---- linear ----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("M,K,N,act", [(512, 3, 128, 0), (300, 32, 256, 0), (1000, 128, 512, 0), (256, 128, 64, 1),
-                                       (130, 64, 16, 1), (257, 160, 192, 2), (128, 3, 640, 0), (1, 16, 32, 0)])
+                                       (130, 64, 16, 1), (257, 160, 192, 2), (128, 3, 640, 0), (1, 16, 32, 0),
+                                       (1001, 3, 128, 2), (77, 4, 32, 1), (300, 1, 8, 0), (65, 2, 1024, 0), (200000, 3, 128, 0)])
 def test_linear(ops, dev, M, K, N, act):
     gen = torch.Generator().manual_seed(M + K + N)
     a = torch.randn(M, K, generator=gen)
