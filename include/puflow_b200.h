@@ -37,7 +37,7 @@ extern "C" {
 #define PF_API
 #endif
 
-#define PF_ABI_VERSION 9
+#define PF_ABI_VERSION 10
 #define PF_EINVAL 10001
 #define PF_ENOMEM 10002
 
@@ -257,6 +257,14 @@ PF_API int pf_gather_points(const float* pc, const int32_t* idx, int B, int n, i
 PF_API int pf_denorm_concat(const float* x, const float* patches, const float* centroid, const float* radius, int items, int nx,
                      int np, float* out, void* stream);
 PF_API int pf_remove_outliers(const float* sr, const float* dist1, int B, int n, int num_outliers, float* out, void* stream);
+/* pf_fps_park_near_origin: the candidate rule of UPSTREAM pointnet2_ops.furthest_point_sample (what
+ * /root/reference/modules/utils/patch.py:102,156 imports; not vendored: `if (mag <= 1e-3) continue;` in its kernel), as a
+ * pre-pass for any pf_fps* entry point: out = xyz with every point i > 0 whose squared norm is <= thresh2 moved onto point 0.
+ * Such a point's running minimum is 0 after the first round, so it is never selected while any other candidate is left, and
+ * it is never a sample, so its coordinates influence nothing -- the indices are those of an FPS that skips it.  The default
+ * semantics of this library (and of the oracle and the golden fixtures) are the reference's own modules/utils/fps.py:40-73,
+ * which has no such rule; this is the opt-in (modules/utils/patch.py FPS_SKIP_NEAR_ORIGIN).  xyz, out: [B][n][3]. */
+PF_API int pf_fps_park_near_origin(const float* xyz, int B, int n, float thresh2, float* out, void* stream);
 
 /* ---- whole network in one call --------------------------------------------------------------------------------
  * pf_upsample_patches replaces PointInterpFlow.forward (/root/reference/modules/discrete/interpflow.py:327-337:

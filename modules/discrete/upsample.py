@@ -84,8 +84,9 @@ def _upsample_device(network, patch_helper, pt_input, up_ratio, num_outlier, num
     eng = network.engine(device) if hasattr(network, "engine") else None
     k = patch_helper.npoint_patch
     n_patch = int(pt_input.shape[1] / k * patch_helper.patch_expand_ratio)
+    from modules.utils import patch as _patch
     if eng is not None and eng.flow_tc and pt_input.shape[1] >= k >= 16 and 1 <= n_patch <= pt_input.shape[1] \
-            and not ops.per_launch_events_wanted():
+            and not ops.per_launch_events_wanted() and not _patch.FPS_SKIP_NEAR_ORIGIN:
         # the whole per-file body of the reference's loop in one C call, replayed from a CUDA graph per shape
         return eng.upsample_clouds(pt_input, up_ratio, n_pts + n_drop, n_drop, k, n_patch, graph=graph)
     pred = patch_helper.upsample(network, pt_input, npoint=n_pts + n_drop, upratio=up_ratio, jitter=False)

@@ -30,9 +30,16 @@ class KNN(object):
         return dist.transpose(1, 2).contiguous(), idx.transpose(1, 2).contiguous()
 
 
+# Upstream pointnet2_ops.furthest_point_sample never selects a candidate with |p|^2 <= 1e-3; the reference's own
+# modules/utils/fps.py (the semantics followed by default, by the oracle and by the golden fixtures) has no such rule.  Set
+# this to 1e-3 for the upstream rule: the FPS calls below then go through pf_fps_park_near_origin, and
+# PatchHelper.upsample / upsample_array take the staged path (the one-call C entry point has the default rule built in).
+FPS_SKIP_NEAR_ORIGIN = 0.0
+
+
 def furthest_point_sample(xyz: Tensor, npoint: int) -> Tensor:
     """pointnet2_ops signature: xyz[B,N,3] -> int32 [B,npoint]."""
-    return ops.fps(xyz.contiguous().float(), npoint)
+    return ops.fps(xyz.contiguous().float(), npoint, skip_near_origin=FPS_SKIP_NEAR_ORIGIN)
 
 
 def gather_operation(features: Tensor, idx: Tensor) -> Tensor:
@@ -67,6 +74,7 @@ class PatchHelper(object):
         # the upsampler is the drop-in PointInterpFlow and nothing below needs a Python hook
         eng = upsampler.engine(pc.device) if hasattr(upsampler, "engine") and pc.is_cuda else None
         if eng is not None and eng.flow_tc and not jitter and not kwargs and C == 3 and not ops.per_launch_events_wanted() \
+                and not FPS_SKIP_NEAR_ORIGIN \
                 and N >= self.__npoint_patch >= 16:
             n_patch = int(N / self.__npoint_patch * self.__patch_expand_ratio)
             if 1 <= n_patch <= N:

@@ -58,6 +58,7 @@ SIGNATURES = {
     "pf_gather_points": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp],
     "pf_denorm_concat": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp],
     "pf_remove_outliers": [_vp, _vp, _i, _i, _i, _vp, _vp],
+    "pf_fps_park_near_origin": [_vp, _i, _i, _f, _vp, _vp],
     "pf_upsample_clouds": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i64, _vp, _i, _vp],
     "pf_profile_enable": [_i],
     "pf_profile_intervals": [],
@@ -81,7 +82,7 @@ lib.pf_upsample_clouds_workspace_bytes.restype = ctypes.c_int64
 lib.pf_last_error.argtypes = []
 lib.pf_last_error.restype = ctypes.c_char_p
 
-PF_ABI_VERSION = 9
+PF_ABI_VERSION = 10
 PF_MODEL_ENTRIES = 27
 PF_FPS_STATIC_MAX_POINTS = 262144
 PF_COND_BLOB = 8840

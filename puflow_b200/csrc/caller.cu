@@ -278,6 +278,28 @@ extern "C" int pf_denorm_concat(const float* x, const float* patches, const floa
     return pf_launch_status("denorm_concat_kernel");
 }
 
+namespace {
+__global__ void __launch_bounds__(256) fps_park_near_origin_kernel(const float* __restrict__ xyz, int n, float thresh2,
+                                                                   float* __restrict__ out) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const float* pb = xyz + (size_t)blockIdx.y * n * 3;
+    float x = pb[3 * i], y = pb[3 * i + 1], z = pb[3 * i + 2];
+    if (i > 0 && x * x + y * y + z * z <= thresh2) x = pb[0], y = pb[1], z = pb[2];
+    float* ob = out + ((size_t)blockIdx.y * n + i) * 3;
+    ob[0] = x, ob[1] = y, ob[2] = z;
+}
+}  // namespace
+
+extern "C" int pf_fps_park_near_origin(const float* xyz, int B, int n, float thresh2, float* out, void* stream) {
+    PF_CHECK_ARG(B >= 0 && n > 0 && B <= 65535, "pf_fps_park_near_origin: bad sizes B=%d n=%d", B, n);
+    if (B == 0) return 0;
+    PF_CHECK_ARG(xyz && out && xyz != out, "pf_fps_park_near_origin: null pointer or in-place call (point 0 is read by every thread)");
+    PF_CHECK_ARG(thresh2 >= 0.f, "pf_fps_park_near_origin: thresh2=%g", (double)thresh2);
+    fps_park_near_origin_kernel<<<dim3((n + 255) / 256, B), 256, 0, (cudaStream_t)stream>>>(xyz, n, thresh2, out);
+    return pf_launch_status("fps_park_near_origin_kernel");
+}
+
 extern "C" int pf_remove_outliers(const float* sr, const float* dist1, int B, int n, int num_outliers, float* out, void* stream) {
     PF_CHECK_ARG(B >= 0 && n > 0 && num_outliers >= 0 && num_outliers < n && n < 65536 * 16,
                  "pf_remove_outliers: bad sizes B=%d n=%d num_outliers=%d", B, n, num_outliers);

@@ -488,8 +488,10 @@ def cloud_launches(Bp: int, num_outliers: int) -> int:
 
 
 # ---- caller side ---------------------------------------------------------------------------------
-def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
+def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto", skip_near_origin: float = 0.0):
     """xyz[B,n,3] -> idx[B,npoint] int32 (modules/utils/fps.py:40-73 semantics: starts at index 0).
+    skip_near_origin = t > 0: candidates with |p|^2 <= t are never selected (upstream pointnet2_ops' rule with t = 1e-3;
+    pf_fps_park_near_origin pre-pass, then the same kernels).
     mode: "brute" = cluster brute-force kernel, "bucket" = exact spatially pruned kernel (one CTA per cloud),
     "cluster" = the pruned kernel with a cloud's buckets spread over a thread-block cluster (few large clouds; falls back
     to "bucket" when the clusters of all clouds do not fit the device), "queue" = the threshold-queue kernel (one warp
@@ -500,6 +502,12 @@ def fps(xyz: torch.Tensor, npoint: int, mode: str = "auto"):
     idx = torch.empty((B, npoint), dtype=torch.int32, device=xyz.device)
     if B == 0:
         return idx
+    if skip_near_origin > 0.0:
+        parked = torch.empty_like(xyz)
+        with _dev(xyz), _launch("fps_park_near_origin"):
+            N.check(lib.pf_fps_park_near_origin(xyz.data_ptr(), B, n, float(skip_near_origin), parked.data_ptr(), _stream()),
+                    "pf_fps_park_near_origin")
+        xyz = parked
     with _dev(xyz), _launch(f"fps_n{n}"):
         if mode == "queue" or (mode == "auto" and n >= 4096):
             work = torch.empty((lib.pf_fps_work_floats(B, n),), dtype=torch.float32, device=xyz.device)

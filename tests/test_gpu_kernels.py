@@ -708,6 +708,33 @@ def test_fps_points_at_the_centroid_follow_fps_py(ops, dev):
         assert np.array_equal(ops.fps(x, 600, mode=mode).cpu().numpy(), ref)
 
 
+def test_fps_pointnet2_near_origin_rule_is_available(ops, dev):
+    """The opt-in: ops.fps(skip_near_origin=1e-3) (pf_fps_park_near_origin + the same kernels) selects what an FPS that skips
+    candidates with |p|^2 <= 1e-3 selects -- upstream pointnet2_ops' rule as restated in oracle.fps_pointnet2 (unpinned: the
+    package is not in the reference tree).  Same centred cloud as above: no near-origin point is ever chosen, every mode
+    agrees, and the default (fps.py) result differs.  modules.utils.patch.FPS_SKIP_NEAR_ORIGIN routes PatchHelper through it."""
+    rng = np.random.default_rng(3)
+    shell = rng.standard_normal((4056, 3))
+    shell /= np.linalg.norm(shell, axis=1, keepdims=True)
+    core = rng.uniform(-0.015, 0.015, (40, 3))
+    p = np.concatenate([core, shell], 0)[rng.permutation(4096)].astype(np.float32)[None]
+    p = np.concatenate([p, p[:, ::-1]], 0).copy()                      # a second cloud: another start point
+    ref = po.fps_pointnet2(p, 600)
+    x = torch.from_numpy(p).to(dev)
+    for mode in ("brute", "bucket", "cluster", "queue"):
+        got = ops.fps(x, 600, mode=mode, skip_near_origin=1e-3).cpu().numpy()
+        assert np.array_equal(got, ref)
+        assert (((p[np.arange(2)[:, None], got] ** 2).sum(-1) <= 1e-3)[:, 1:]).sum() == 0
+    assert not np.array_equal(ops.fps(x, 600).cpu().numpy(), ref)
+    from modules.utils import patch
+    assert patch.FPS_SKIP_NEAR_ORIGIN == 0.0                          # the default stays the reference's own fps.py
+    patch.FPS_SKIP_NEAR_ORIGIN = 1e-3
+    try:
+        assert np.array_equal(patch.furthest_point_sample(x, 600).cpu().numpy(), ref)
+    finally:
+        patch.FPS_SKIP_NEAR_ORIGIN = 0.0
+
+
 def test_fps_lattice_ties(ops, dev):
     p = np.stack([synth.make_cloud(1000, s, "lattice") for s in (1, 2)])
     assert np.array_equal(ops.fps(torch.from_numpy(p).to(dev), 200).cpu().numpy(), po.fps(p, 200))
