@@ -76,33 +76,33 @@ __device__ __forceinline__ float tanh_fast(float x) { return fmaf(-2.f, rcp_ftz(
 //
 // Code size matters here: the fully unrolled version (4,500 FFMA + 1,100 LDS + the activations, ~100 KB of SASS) ran out of
 // the 32 KB L1.5 instruction cache -- `stalled_no_instruction` was 2.5-3.3 warps per issue, the issue slots 22-41 % busy
-// (profiles/r02_cnf.md).  So the 64-output loops are real loops: the hidden layer four outputs per iteration (four independent
-// FFMA chains, its input h0 in registers with static indices), the output layer folded into it (h1 is never stored), and the
+// (profiles/r02_cnf.md).  So the 64-output loops are real loops: the hidden layer UNR outputs per iteration (independent
+// FFMA2 chains, its input h0 in registers with static indices), the output layer folded into it (h1 is never stored), and the
 // first layer HST outputs at a time through a private shared-memory column, because a rolled loop cannot index registers.
 constexpr int HST = 16;
+// Compile-time switches: the measured alternatives (profiles/r02_cnf.md); the defaults are what shipped.
 #ifndef PF_CNF_FFMA2
-#define PF_CNF_FFMA2 1
+#define PF_CNF_FFMA2 1            // hidden layer as packed fma.rn.f32x2 (0: scalar FFMA)
 #endif
 #ifndef PF_CNF_UNROLL
-#define PF_CNF_UNROLL 2
+#define PF_CNF_UNROLL 2           // hidden-layer outputs per pipelined group
+#endif
+#ifndef PF_CNF_U1
+#define PF_CNF_U1 4               // first-layer outputs per loop iteration
 #endif
 #ifndef PF_CNF_INV_NT
-#define PF_CNF_INV_NT 128
+#define PF_CNF_INV_NT 128         // inverse direction (rep >= 4): threads per CTA,
 #endif
 #ifndef PF_CNF_INV_OCC
-#define PF_CNF_INV_OCC 3
+#define PF_CNF_INV_OCC 3          //   CTAs per SM (register cap 65,536 / (NT * OCC)),
 #endif
 #ifndef PF_CNF_INV_SPLIT
-#define PF_CNF_INV_SPLIT 1
+#define PF_CNF_INV_SPLIT 1        //   lanes per point
 #endif
 #ifndef PF_CNF_FWD_SPLIT
-#define PF_CNF_FWD_SPLIT 2
+#define PF_CNF_FWD_SPLIT 2        // forward direction: lanes per point (128 points per CTA, one CTA per SM)
 #endif
-constexpr int UNR = PF_CNF_UNROLL;
-#ifndef PF_CNF_U1
-#define PF_CNF_U1 4
-#endif
-constexpr int U1 = PF_CNF_U1;
+constexpr int UNR = PF_CNF_UNROLL, U1 = PF_CNF_U1;
 // two FP32 FMAs per instruction (fma.rn.f32x2, FFMA2): the hidden layer's 64-term dot product runs as two 32-term partial
 // sums (even / odd inputs) in one register pair, halving the FMA issue slots of an evaluation.
 __device__ __forceinline__ unsigned long long ffma2(unsigned long long a, unsigned long long b, unsigned long long c) {
