@@ -106,6 +106,20 @@ def test_fps_and_patch_extraction_match_reference(golden):
         assert np.array_equal(pidx, e["patch_idx"].astype(np.int64))
 
 
+def test_fps_pointnet2_restatement_reduces_to_fps_py():
+    """oracle.fps_pointnet2 (upstream pointnet2_ops' candidate rule, unpinned) with the rule switched off is the pinned
+    fps.py restatement (nn_oracle.c); with it on, no candidate within the threshold is selected after the start point and
+    clouds without such points are unchanged."""
+    rng = np.random.default_rng(11)
+    p = rng.uniform(-1, 1, (2, 700, 3)).astype(np.float32)
+    assert np.array_equal(po.fps_pointnet2(p, 96, thresh2=-1.0), po.fps(p, 96))
+    p[:, 5:25] *= np.float32(0.01)                                   # twenty points within 0.0174 of the origin
+    sel = po.fps_pointnet2(p, 96)
+    assert ((p[np.arange(2)[:, None], sel[:, 1:]] ** 2).sum(-1) > 1e-3).all()
+    shell = p / np.linalg.norm(p, axis=-1, keepdims=True)
+    assert np.array_equal(po.fps_pointnet2(shell, 96), po.fps(shell, 96))
+
+
 def test_end_to_end_small_cloud(golden, state_dict):
     """FPS over the merged candidates is chaotic under 1e-7 perturbations (patches overlap, so the
     candidate set holds near-duplicate points): rows need not line up, the point SET must.
