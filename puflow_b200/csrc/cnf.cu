@@ -362,7 +362,9 @@ extern "C" int pf_cnf_flow(const float* y_in, const float* ctx, int ld_ctx, cons
     };
     if (int rc = rep >= 4 ? launch(cnf_flow_kernel<PF_CNF_INV_NT, PF_CNF_INV_OCC, PF_CNF_INV_SPLIT>, PF_CNF_INV_NT,
                                    PF_CNF_INV_NT / PF_CNF_INV_SPLIT)
-                          : launch(cnf_flow_kernel<128 * PF_CNF_FWD_SPLIT, 1, PF_CNF_FWD_SPLIT>, 128 * PF_CNF_FWD_SPLIT, 128))
+                          : (M <= 148 * 128 && PF_CNF_FWD_SPLIT == 2      // under one wave of 128-point CTAs: 64-point ones, two per SM
+                                 ? launch(cnf_flow_kernel<128, 2, 2>, 128, 64)
+                                 : launch(cnf_flow_kernel<128 * PF_CNF_FWD_SPLIT, 1, PF_CNF_FWD_SPLIT>, 128 * PF_CNF_FWD_SPLIT, 128)))
         return rc;
     return pf_launch_status("cnf_flow_kernel");
 }
